@@ -1,0 +1,18 @@
+"""dealii_multigrid_b200 -- B200-native hot path of peterrum/dealii-multigrid's multigrid_throughput.
+
+The product is the CUDA/C++ shared library csrc -> lib/libmgb200.so (C ABI: include/mgb200.h).  This
+package is its thin ctypes mirror of the reference's operator interface.  Importing it loads the shared
+library and raises ImportError if it has not been built: there is no CPU or pure-Python compute path.
+"""
+from . import _lib
+
+_lib.load()
+
+from .api import (  # noqa: E402
+    DOUBLE, FLOAT, FLAG_BIT, INDEX_MASK, MgbError, Mesh, DoFMap, TransferMap, Vector, Operator,
+    PreconditionChebyshev, MGTwoLevelTransfer, Problem, init, set_stream, synchronize, launch_count,
+    comm_unique_id, comm_init, comm_finalize, fe_1d, fe_p_embedding)
+
+__all__ = ["DOUBLE", "FLOAT", "FLAG_BIT", "INDEX_MASK", "MgbError", "Mesh", "DoFMap", "TransferMap", "Vector", "Operator",
+           "PreconditionChebyshev", "MGTwoLevelTransfer", "Problem", "init", "set_stream", "synchronize", "launch_count",
+           "comm_unique_id", "comm_init", "comm_finalize", "fe_1d", "fe_p_embedding"]

@@ -1,0 +1,507 @@
+"""Python mirror of the reference's operator interface over the C ABI (include/mgb200.h).
+
+Class and method names follow the deal.II concepts the reference composes:
+  Operator.vmult / Tvmult / vmult_interface_down / vmult_interface_up / compute_inverse_diagonal
+                                                    -> include/operator.h:152-242
+  PreconditionChebyshev.vmult / step                -> multigrid_throughput.cc:847-883
+  MGTwoLevelTransfer.prolongate_and_add / restrict_and_add -> multigrid_throughput.cc:1600-1604
+  Problem (JSON) .run / .solve_once / .vcycle       -> run() + solve_with_global_coarsening + mg_solve
+All compute happens in libmgb200.so on the GPU; errors surface as MgbError (the reference throws C++
+exceptions caught in main(), multigrid_throughput.cc:2444-2468).
+"""
+import ctypes as C
+import json
+
+import numpy as np
+
+from . import _lib
+
+DOUBLE, FLOAT = 0, 1
+FLAG_BIT = 0x80000000
+INDEX_MASK = 0x7FFFFFFF
+_NP = {DOUBLE: np.float64, FLOAT: np.float32}
+
+
+class MgbError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc != 0:
+        raise MgbError(_lib.load().mgb_last_error().decode())
+
+
+def _arr(ptr, n, dtype):
+    """copy n entries from a borrowed C pointer into a numpy array"""
+    if n == 0:
+        return np.zeros(0, dtype=dtype)
+    return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dtype, copy=True)
+
+
+def init(device=0):
+    _check(_lib.load().mgb_init(device))
+
+
+def set_stream(cuda_stream_ptr):
+    _check(_lib.load().mgb_set_stream(C.c_void_p(cuda_stream_ptr)))
+
+
+def synchronize():
+    _check(_lib.load().mgb_synchronize())
+
+
+def launch_count():
+    return int(_lib.load().mgb_launch_count())
+
+
+def comm_unique_id(libnccl_path=None):
+    buf = C.create_string_buffer(128)
+    _check(_lib.load().mgb_comm_unique_id(buf, libnccl_path.encode() if libnccl_path else None))
+    return buf.raw
+
+
+def comm_init(unique_id, rank, size, libnccl_path=None):
+    buf = C.create_string_buffer(bytes(unique_id), 128)
+    _check(_lib.load().mgb_comm_init(buf, rank, size, libnccl_path.encode() if libnccl_path else None))
+
+
+def comm_finalize():
+    _check(_lib.load().mgb_comm_finalize())
+
+
+def fe_1d(degree):
+    """1-D FE_Q(degree)/QGauss(degree+1) data of the product (for comparison with the oracle's own)."""
+    n = degree + 1
+    out = {k: np.zeros(s) for k, s in (("nodes", n), ("M", n * n), ("K", n * n), ("S0", n * n), ("S1", n * n),
+                                       ("Ph", (2 * degree + 1) * n))}
+    ptr = lambda a: a.ctypes.data_as(_lib.c_f64p)
+    _check(_lib.load().mgb_fe_1d(degree, ptr(out["nodes"]), ptr(out["M"]), ptr(out["K"]), ptr(out["S0"]), ptr(out["S1"]),
+                                 ptr(out["Ph"])))
+    for k in ("M", "K", "S0", "S1"):
+        out[k] = out[k].reshape(n, n)
+    out["Ph"] = out["Ph"].reshape(2 * degree + 1, n)
+    return out
+
+
+def fe_p_embedding(degree_fine, degree_coarse):
+    P = np.zeros((degree_fine + 1) * (degree_coarse + 1))
+    _check(_lib.load().mgb_fe_p_embedding(degree_fine, degree_coarse, P.ctypes.data_as(_lib.c_f64p)))
+    return P.reshape(degree_fine + 1, degree_coarse + 1)
+
+
+class Mesh:
+    """Octree stand-in for parallel::distributed::Triangulation (multigrid_throughput.cc:2041-2062)."""
+
+    def __init__(self, geometry_type=None, n_ref_global=0, n_ref_local=0, _handle=None):
+        self._lib = _lib.load()
+        if _handle is not None:
+            self._h = _handle
+        else:
+            h = C.c_void_p()
+            _check(self._lib.mgb_mesh_create(geometry_type.encode(), n_ref_global, n_ref_local, C.byref(h)))
+            self._h = h
+
+    def coarsen_global(self):
+        h = C.c_void_p()
+        _check(self._lib.mgb_mesh_coarsen(self._h, C.byref(h)))
+        return Mesh(_handle=h)
+
+    @property
+    def n_cells(self):
+        return int(self._lib.mgb_mesh_n_cells(self._h))
+
+    @property
+    def n_global_levels(self):
+        return int(self._lib.mgb_mesh_n_levels(self._h))
+
+    def cells(self):
+        """(n_cells, 4) array of (level, x, y, z) in Morton order"""
+        out = np.zeros((self.n_cells, 4), dtype=np.uint32)
+        _check(self._lib.mgb_mesh_get_cells(self._h, out.ctypes.data_as(_lib.c_u32p)))
+        return out
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.mgb_mesh_destroy(self._h)
+            self._h = None
+
+
+class DoFMap:
+    """FE_Q(degree) DoFs + constraints + partitioner (DoFHandler/AffineConstraints/MatrixFree stand-in)."""
+
+    def __init__(self, mesh=None, degree=1, n_ranks=1, rank=0, _handle=None, _owner=None):
+        self._lib = _lib.load()
+        self._owner = _owner  # keeps a Problem alive for borrowed handles
+        if _handle is not None:
+            self._h = _handle
+            self._borrowed = True
+        else:
+            h = C.c_void_p()
+            _check(self._lib.mgb_dofmap_create(mesh._h, degree, n_ranks, rank, C.byref(h)))
+            self._h = h
+            self._borrowed = False
+        v = _lib.DofmapView()
+        _check(self._lib.mgb_dofmap_view_get(self._h, C.byref(v)))
+        self.view = v
+        for name in ("degree", "n_ranks", "rank", "mesh_max_level", "n_cells_global", "cell_begin", "n_cells",
+                     "n_cells_hanging", "n_dofs_global", "owned_begin", "n_owned", "n_ghost", "n_constrained"):
+            setattr(self, name, int(getattr(v, name)))
+
+    # numpy copies of the maps (inputs shared by the product and the oracle)
+    def eval_table(self):
+        return _arr(self.view.eval_table, self.n_cells * 27, np.uint32).reshape(self.n_cells, 27)
+
+    def own_table(self):
+        return _arr(self.view.own_table, self.n_cells * 27, np.uint32).reshape(self.n_cells, 27)
+
+    def mask(self):
+        return _arr(self.view.mask, self.n_cells, np.uint16)
+
+    def cell_level(self):
+        return _arr(self.view.cell_level, self.n_cells, np.uint8)
+
+    def cell_xyz(self):
+        return _arr(self.view.cell_xyz, self.n_cells * 3, np.uint32).reshape(self.n_cells, 3)
+
+    def constrained(self):
+        return _arr(self.view.constrained, self.n_constrained, np.uint32)
+
+    def ghost_global(self):
+        return _arr(self.view.ghost_global, self.n_ghost, np.int64)
+
+    def partitioner(self):
+        v = self.view
+        return dict(
+            n_global=self.n_dofs_global, owned_begin=self.owned_begin, n_owned=self.n_owned, n_ghost=self.n_ghost,
+            ghost_global=self.ghost_global(),
+            ghost_ranks=_arr(v.ghost_ranks, v.n_ghost_ranks, np.int32),
+            ghost_offsets=_arr(v.ghost_offsets, v.n_ghost_ranks + 1, np.uint32),
+            import_ranks=_arr(v.import_ranks, v.n_import_ranks, np.int32),
+            import_offsets=_arr(v.import_offsets, v.n_import_ranks + 1, np.uint32),
+            import_indices=_arr(v.import_indices, v.n_import_indices, np.uint32))
+
+    def expand(self, which="eval"):
+        """lexicographic (p+1)^3 index map per cell, flag in bit 31 (MatrixFree's dof_indices)"""
+        n3 = (self.degree + 1) ** 3
+        out = np.zeros((self.n_cells, n3), dtype=np.uint32)
+        _check(self._lib.mgb_dofmap_expand(self._h, 0 if which == "eval" else 1, out.ctypes.data_as(_lib.c_u32p)))
+        return out
+
+    def __del__(self):
+        if getattr(self, "_h", None) and not self._borrowed:
+            self._lib.mgb_dofmap_destroy(self._h)
+        self._h = None
+
+
+class TransferMap:
+    def __init__(self, mesh_fine, dofs_fine, mesh_coarse, dofs_coarse):
+        self._lib = _lib.load()
+        h = C.c_void_p()
+        _check(self._lib.mgb_transfer_map_create(mesh_fine._h, dofs_fine._h, mesh_coarse._h, dofs_coarse._h, C.byref(h)))
+        self._h = h
+        v = _lib.TransferMapView()
+        _check(self._lib.mgb_transfer_map_view_get(self._h, C.byref(v)))
+        self.view = v
+        self.degree_fine, self.degree_coarse = int(v.degree_fine), int(v.degree_coarse)
+        self.n_coarse_cells, self.n_fine_cells = int(v.n_coarse_cells), int(v.n_fine_cells)
+
+    def fine_first(self):
+        return _arr(self.view.fine_first, self.n_coarse_cells, np.uint32)
+
+    def n_children(self):
+        return _arr(self.view.n_children, self.n_coarse_cells, np.uint8)
+
+    def weight_code(self):
+        return _arr(self.view.weight_code, self.n_fine_cells * 27, np.uint8).reshape(self.n_fine_cells, 27)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.mgb_transfer_map_destroy(self._h)
+            self._h = None
+
+
+class Vector:
+    """LinearAlgebra::distributed::Vector<Number> in device memory, [owned | ghost]."""
+
+    def __init__(self, n_owned=0, n_ghost=0, number_type=DOUBLE, _handle=None, _borrowed=False, _owner=None):
+        self._lib = _lib.load()
+        self.number_type = number_type
+        self._owner = _owner
+        self._borrowed = _borrowed
+        if _handle is not None:
+            self._h = _handle
+        else:
+            h = C.c_void_p()
+            _check(self._lib.mgb_vector_create(n_owned, n_ghost, number_type, C.byref(h)))
+            self._h = h
+        self.n_owned = int(self._lib.mgb_vector_n_owned(self._h))
+
+    @classmethod
+    def wrap(cls, device_ptr, n_owned, n_ghost=0, number_type=DOUBLE, keepalive=None):
+        lib = _lib.load()
+        h = C.c_void_p()
+        _check(lib.mgb_vector_wrap(C.c_void_p(device_ptr), n_owned, n_ghost, number_type, C.byref(h)))
+        return cls(number_type=number_type, _handle=h, _owner=keepalive)
+
+    @property
+    def data_ptr(self):
+        return int(self._lib.mgb_vector_data(self._h))
+
+    def from_numpy(self, a):
+        a = np.ascontiguousarray(a, dtype=_NP[self.number_type])
+        _check(self._lib.mgb_vector_copy_from_host(self._h, a.ctypes.data_as(C.c_void_p), a.size))
+        return self
+
+    def to_numpy(self, n=None):
+        n = self.n_owned if n is None else n
+        out = np.zeros(n, dtype=_NP[self.number_type])
+        _check(self._lib.mgb_vector_copy_to_host(self._h, out.ctypes.data_as(C.c_void_p), n))
+        return out
+
+    def set(self, a):
+        _check(self._lib.mgb_vector_set(self._h, a))
+
+    def add(self, a, x):
+        _check(self._lib.mgb_vector_add(self._h, a, x._h))
+
+    def sadd(self, s, a, x):
+        _check(self._lib.mgb_vector_sadd(self._h, s, a, x._h))
+
+    def equ(self, a, x):
+        _check(self._lib.mgb_vector_equ(self._h, a, x._h))
+
+    def dot(self, y):
+        r = C.c_double()
+        _check(self._lib.mgb_vector_dot(self._h, y._h, C.byref(r)))
+        return r.value
+
+    def l2_norm(self):
+        r = C.c_double()
+        _check(self._lib.mgb_vector_l2_norm(self._h, C.byref(r)))
+        return r.value
+
+    def add_and_dot(self, a, h):
+        r = C.c_double()
+        _check(self._lib.mgb_vector_add_and_dot(self._h, a, h._h, C.byref(r)))
+        return r.value
+
+    def update_ghost_values(self):
+        _check(self._lib.mgb_vector_update_ghost_values(self._h))
+
+    def compress_add(self):
+        _check(self._lib.mgb_vector_compress_add(self._h))
+
+    def zero_out_ghost_values(self):
+        _check(self._lib.mgb_vector_zero_out_ghost_values(self._h))
+
+    def __del__(self):
+        if getattr(self, "_h", None) and not self._borrowed:
+            self._lib.mgb_vector_destroy(self._h)
+        self._h = None
+
+
+def _ptr(a, ctype):
+    return a.ctypes.data_as(C.POINTER(ctype)) if a is not None and a.size else None
+
+
+class Operator:
+    """Operator<3,1,Number> of include/operator.h (matrix-free Laplace with identity rows on constrained DoFs)."""
+
+    def __init__(self, dofs=None, number_type=DOUBLE, _handle=None, _owner=None, **arrays):
+        self._lib = _lib.load()
+        self.number_type = number_type
+        self._owner = _owner
+        self._borrowed = _handle is not None
+        if _handle is not None:
+            self._h = _handle
+            return
+        h = C.c_void_p()
+        if dofs is not None and not arrays:
+            _check(self._lib.mgb_operator_create_from_dofmap(dofs._h, number_type, C.byref(h)))
+        else:
+            _check(self._lib.mgb_operator_create(C.byref(self._make_desc(number_type, **arrays)), C.byref(h)))
+        self._h = h
+
+    def _make_desc(self, number_type, degree, cell_level, n_owned, entity_table=None, dof_indices=None, mask=None,
+                   constrained=None, edge_constrained=None, has_edge_constrained_global=False, edge_cells=None,
+                   n_dofs_global=None, partitioner=None, root_length=2.0):
+        d = _lib.OperatorDesc()
+        keep = []
+
+        def arr(a, dtype):
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dtype=dtype)
+            keep.append(a)
+            return a
+
+        et, di = arr(entity_table, np.uint32), arr(dof_indices, np.uint32)
+        lv, mk = arr(cell_level, np.uint8), arr(mask, np.uint16)
+        cs, ec, ecl = arr(constrained, np.uint32), arr(edge_constrained, np.uint32), arr(edge_cells, np.uint32)
+        d.degree, d.number_type, d.n_cells = degree, number_type, lv.size
+        d.entity_table, d.dof_indices = _ptr(et, C.c_uint32), _ptr(di, C.c_uint32)
+        d.mask, d.cell_level, d.root_length = _ptr(mk, C.c_uint16), _ptr(lv, C.c_uint8), root_length
+        d.constrained, d.n_constrained = _ptr(cs, C.c_uint32), 0 if cs is None else cs.size
+        d.edge_constrained, d.n_edge_constrained = _ptr(ec, C.c_uint32), 0 if ec is None else ec.size
+        d.has_edge_constrained_global = int(has_edge_constrained_global)
+        d.edge_cells, d.n_edge_cells = _ptr(ecl, C.c_uint32), 0 if ecl is None else ecl.size
+        p = partitioner or {}
+        d.n_owned, d.n_ghost = n_owned, p.get("n_ghost", 0)
+        d.n_dofs_global = n_dofs_global if n_dofs_global is not None else n_owned
+        d.owned_begin = p.get("owned_begin", 0)
+        gg, gr, go = arr(p.get("ghost_global"), np.int64), arr(p.get("ghost_ranks"), np.int32), arr(p.get("ghost_offsets"), np.uint32)
+        ir, io, ii = arr(p.get("import_ranks"), np.int32), arr(p.get("import_offsets"), np.uint32), arr(p.get("import_indices"), np.uint32)
+        d.ghost_global = _ptr(gg, C.c_int64)
+        d.ghost_ranks, d.ghost_offsets, d.n_ghost_ranks = _ptr(gr, C.c_int32), _ptr(go, C.c_uint32), 0 if gr is None else gr.size
+        d.import_ranks, d.import_offsets, d.n_import_ranks = _ptr(ir, C.c_int32), _ptr(io, C.c_uint32), 0 if ir is None else ir.size
+        d.import_indices = _ptr(ii, C.c_uint32)
+        self._keep = keep
+        return d
+
+    def m(self):
+        return int(self._lib.mgb_operator_m(self._h))
+
+    def initialize_dof_vector(self):
+        h = C.c_void_p()
+        _check(self._lib.mgb_operator_initialize_dof_vector(self._h, C.byref(h)))
+        return Vector(number_type=self.number_type, _handle=h)
+
+    def vmult(self, dst, src):
+        _check(self._lib.mgb_operator_vmult(self._h, dst._h, src._h))
+
+    def Tvmult(self, dst, src):
+        _check(self._lib.mgb_operator_tvmult(self._h, dst._h, src._h))
+
+    def vmult_interface_down(self, dst, src):
+        _check(self._lib.mgb_operator_vmult_interface_down(self._h, dst._h, src._h))
+
+    def vmult_interface_up(self, dst, src):
+        _check(self._lib.mgb_operator_vmult_interface_up(self._h, dst._h, src._h))
+
+    def compute_inverse_diagonal(self, diag):
+        _check(self._lib.mgb_operator_compute_inverse_diagonal(self._h, diag._h))
+
+    def __del__(self):
+        if getattr(self, "_h", None) and not self._borrowed:
+            self._lib.mgb_operator_destroy(self._h)
+        self._h = None
+
+
+class PreconditionChebyshev:
+    """PreconditionChebyshev<Operator, Vector, DiagonalMatrix> (multigrid_throughput.cc:847-883)."""
+
+    def __init__(self, op=None, degree=3, smoothing_range=20.0, eig_cg_n_iterations=20, _handle=None, _owner=None):
+        self._lib = _lib.load()
+        self._owner = _owner if _owner is not None else op
+        self._borrowed = _handle is not None
+        if _handle is not None:
+            self._h = _handle
+        else:
+            h = C.c_void_p()
+            _check(self._lib.mgb_chebyshev_create(op._h, degree, smoothing_range, eig_cg_n_iterations, C.byref(h)))
+            self._h = h
+
+    def vmult(self, dst, rhs):
+        _check(self._lib.mgb_chebyshev_vmult(self._h, dst._h, rhs._h))
+
+    def step(self, dst, rhs):
+        _check(self._lib.mgb_chebyshev_step(self._h, dst._h, rhs._h))
+
+    def eigenvalues(self):
+        a, b = C.c_double(), C.c_double()
+        _check(self._lib.mgb_chebyshev_eigenvalues(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def __del__(self):
+        if getattr(self, "_h", None) and not self._borrowed:
+            self._lib.mgb_chebyshev_destroy(self._h)
+        self._h = None
+
+
+class MGTwoLevelTransfer:
+    """MGTwoLevelTransfer<3, Vector>: reinit(dof_fine, dof_coarse, constraints...) + prolongate/restrict."""
+
+    def __init__(self, dofs_fine=None, dofs_coarse=None, tmap=None, op_fine=None, op_coarse=None, _handle=None, _owner=None):
+        self._lib = _lib.load()
+        self._owner = _owner if _owner is not None else (dofs_fine, dofs_coarse, tmap, op_fine, op_coarse)
+        self._borrowed = _handle is not None
+        if _handle is not None:
+            self._h = _handle
+        else:
+            h = C.c_void_p()
+            _check(self._lib.mgb_transfer_create(dofs_fine._h, dofs_coarse._h, tmap._h, op_fine._h, op_coarse._h, C.byref(h)))
+            self._h = h
+
+    def prolongate_and_add(self, dst_fine, src_coarse):
+        _check(self._lib.mgb_transfer_prolongate_and_add(self._h, dst_fine._h, src_coarse._h))
+
+    def restrict_and_add(self, dst_coarse, src_fine):
+        _check(self._lib.mgb_transfer_restrict_and_add(self._h, dst_coarse._h, src_fine._h))
+
+    def __del__(self):
+        if getattr(self, "_h", None) and not self._borrowed:
+            self._lib.mgb_transfer_destroy(self._h)
+        self._h = None
+
+
+class Problem:
+    """One JSON input of multigrid_throughput (scripts/default.json schema): setup + V-cycle-preconditioned CG."""
+
+    def __init__(self, params, n_ranks=1, rank=0):
+        self._lib = _lib.load()
+        text = params if isinstance(params, str) else json.dumps(params)
+        h = C.c_void_p()
+        _check(self._lib.mgb_problem_create(text.encode(), n_ranks, rank, C.byref(h)))
+        self._h = h
+
+    @property
+    def n_levels(self):
+        return int(self._lib.mgb_problem_n_levels(self._h))
+
+    def level_n_dofs(self, l):
+        return int(self._lib.mgb_problem_level_n_dofs(self._h, l))
+
+    def level_n_cells(self, l):
+        return int(self._lib.mgb_problem_level_n_cells(self._h, l))
+
+    def level_degree(self, l):
+        return int(self._lib.mgb_problem_level_degree(self._h, l))
+
+    def level_dofmap(self, l):
+        return DoFMap(_handle=C.c_void_p(self._lib.mgb_problem_level_dofmap(self._h, l)), _owner=self)
+
+    def level_operator(self, l, number_type=DOUBLE):
+        return Operator(number_type=number_type, _handle=C.c_void_p(self._lib.mgb_problem_level_operator(self._h, l)), _owner=self)
+
+    def level_smoother(self, l):
+        return PreconditionChebyshev(_handle=C.c_void_p(self._lib.mgb_problem_level_smoother(self._h, l)), _owner=self)
+
+    def level_transfer(self, l):
+        return MGTwoLevelTransfer(_handle=C.c_void_p(self._lib.mgb_problem_level_transfer(self._h, l)), _owner=self)
+
+    def fine_operator(self):
+        return Operator(number_type=DOUBLE, _handle=C.c_void_p(self._lib.mgb_problem_fine_operator(self._h)), _owner=self)
+
+    def rhs(self):
+        return Vector(_handle=C.c_void_p(self._lib.mgb_problem_rhs(self._h)), _borrowed=True, _owner=self)
+
+    def solution(self):
+        return Vector(_handle=C.c_void_p(self._lib.mgb_problem_solution(self._h)), _borrowed=True, _owner=self)
+
+    def vcycle(self, dst, src):
+        _check(self._lib.mgb_problem_vcycle(self._h, dst._h, src._h))
+
+    def solve_once(self, with_stage_timers=False):
+        r = _lib.Result()
+        _check(self._lib.mgb_problem_solve_once(self._h, int(with_stage_timers), C.byref(r)))
+        return r.as_dict()
+
+    def run(self, n_repetitions=5):
+        r = _lib.Result()
+        _check(self._lib.mgb_problem_run(self._h, n_repetitions, C.byref(r)))
+        return r.as_dict()
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.mgb_problem_destroy(self._h)
+            self._h = None

@@ -1,0 +1,72 @@
+// Translation unit of all cell-wise kernels (they share the constant-memory 1-D matrices).
+#include "../host/fe1d.h"
+#include "operator.cuh"
+#include "transfer.cuh"
+
+#include <mutex>
+#include <stdexcept>
+
+namespace mgb
+{
+  void upload_fe_constants(int degree)
+  {
+    static std::mutex mtx;
+    static bool       done[MAX_DEGREE + 1] = {};
+    if (degree < 1 || degree > MAX_DEGREE)
+      throw std::runtime_error("degree out of range [1," + std::to_string(MAX_DEGREE) + "]");
+    std::lock_guard<std::mutex> lock(mtx);
+    if (done[degree])
+      return;
+    FE1D    fe(degree);
+    FEConst h{};
+    for (int i = 0; i < fe.n; ++i)
+      for (int j = 0; j < fe.n; ++j)
+        {
+          h.M[i * MAXN + j]    = fe.M[i * fe.n + j];
+          h.K[i * MAXN + j]    = fe.K[i * fe.n + j];
+          h.S[0][i * MAXN + j] = fe.S[0][i * fe.n + j];
+          h.S[1][i * MAXN + j] = fe.S[1][i * fe.n + j];
+        }
+    MGB_CUDA(cudaMemcpyToSymbol(c_fe, &h, sizeof(FEConst), sizeof(FEConst) * degree));
+    done[degree] = true;
+  }
+
+#define DISPATCH_DEGREE(deg, CALL)                                   \
+  switch (deg)                                                       \
+    {                                                                \
+      case 1: { constexpr int P = 1; CALL; break; }                  \
+      case 2: { constexpr int P = 2; CALL; break; }                  \
+      case 3: { constexpr int P = 3; CALL; break; }                  \
+      case 4: { constexpr int P = 4; CALL; break; }                  \
+      case 5: { constexpr int P = 5; CALL; break; }                  \
+      case 6: { constexpr int P = 6; CALL; break; }                  \
+      default: throw std::runtime_error("unsupported degree");      \
+    }
+
+  template <typename T>
+  void cell_laplace_apply(const CellData &cd, const T *src, T *dst, const uint32_t *cell_list, long long n_list, cudaStream_t s)
+  {
+    DISPATCH_DEGREE(cd.degree, (launch_apply<P, T>(cd, src, dst, cell_list, n_list, s)));
+  }
+  template <typename T> void cell_laplace_diagonal(const CellData &cd, T *diag, cudaStream_t s)
+  {
+    DISPATCH_DEGREE(cd.degree, (launch_diagonal<P, T>(cd, diag, s)));
+  }
+  template <typename T> void transfer_prolongate_add(const TransferData &td, T *dst_fine, const T *src_coarse, cudaStream_t s)
+  {
+    launch_transfer<T, true>(td, dst_fine, src_coarse, s);
+  }
+  template <typename T> void transfer_restrict_add(const TransferData &td, T *dst_coarse, const T *src_fine, cudaStream_t s)
+  {
+    launch_transfer<T, false>(td, dst_coarse, src_fine, s);
+  }
+
+  template void cell_laplace_apply<double>(const CellData &, const double *, double *, const uint32_t *, long long, cudaStream_t);
+  template void cell_laplace_apply<float>(const CellData &, const float *, float *, const uint32_t *, long long, cudaStream_t);
+  template void cell_laplace_diagonal<double>(const CellData &, double *, cudaStream_t);
+  template void cell_laplace_diagonal<float>(const CellData &, float *, cudaStream_t);
+  template void transfer_prolongate_add<double>(const TransferData &, double *, const double *, cudaStream_t);
+  template void transfer_prolongate_add<float>(const TransferData &, float *, const float *, cudaStream_t);
+  template void transfer_restrict_add<double>(const TransferData &, double *, const double *, cudaStream_t);
+  template void transfer_restrict_add<float>(const TransferData &, float *, const float *, cudaStream_t);
+} // namespace mgb

@@ -1,0 +1,90 @@
+// Launcher declarations for the sm_100a kernels (definitions in *.cu).  All launchers enqueue on the
+// stream passed in and never synchronise, except the reductions that return a scalar to the host.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mgb
+{
+  constexpr int MAX_DEGREE = 6;
+
+  void check_cuda(cudaError_t e, const char *what);
+#define MGB_CUDA(x) ::mgb::check_cuda((x), #x)
+
+  // upload the 1-D matrices of FE_Q(degree) to constant memory (idempotent)
+  void upload_fe_constants(int degree);
+
+  // ---------------------------------------------------------------- BLAS-1 (vector.cu)
+  template <typename T> void vec_set(T *x, T a, size_t n, cudaStream_t s);
+  template <typename T> void vec_scale(T *x, T a, size_t n, cudaStream_t s);
+  template <typename T> void vec_add(T *y, T a, const T *x, size_t n, cudaStream_t s);            // y += a x
+  template <typename T> void vec_sadd(T *y, T s_, T a, const T *x, size_t n, cudaStream_t s);     // y = s y + a x
+  template <typename T> void vec_equ(T *y, T a, const T *x, size_t n, cudaStream_t s);            // y = a x
+  template <typename T> void vec_add_scalar(T *y, T a, size_t n, cudaStream_t s);                 // y += a
+  template <typename T, typename U> void vec_convert(T *y, const U *x, size_t n, cudaStream_t s); // y = (T)x
+  // deterministic reductions; result is written to *result_dev (device) by the last block
+  template <typename T> void vec_dot(const T *x, const T *y, size_t n, double *result_dev, double *scratch,
+                                     unsigned *ticket, cudaStream_t s);
+  template <typename T> void vec_sum(const T *x, size_t n, double *result_dev, double *scratch, unsigned *ticket,
+                                     cudaStream_t s);
+  // g += a h; result = g.g   (SolverCG's add_and_dot with w == g)
+  template <typename T> void vec_add_and_dot(T *g, T a, const T *h, size_t n, double *result_dev, double *scratch,
+                                             unsigned *ticket, cudaStream_t s);
+  int reduction_scratch_size(); // number of doubles `scratch` must hold
+
+  // gather / scatter by index lists (identity rows, edge DoFs, ghost pack/unpack, copy_indices)
+  template <typename T> void idx_copy(T *dst, const T *src, const uint32_t *idx, uint32_t n, cudaStream_t s); // dst[idx]=src[idx]
+  template <typename T> void idx_gather(T *buf, const T *src, const uint32_t *idx, uint32_t n, cudaStream_t s); // buf[i]=src[idx[i]]
+  template <typename T> void idx_scatter(T *dst, const T *buf, const uint32_t *idx, uint32_t n, cudaStream_t s); // dst[idx[i]]=buf[i]
+  template <typename T> void idx_scatter_add(T *dst, const T *buf, const uint32_t *idx, uint32_t n, cudaStream_t s);
+  template <typename T> void idx_set(T *dst, T a, const uint32_t *idx, uint32_t n, cudaStream_t s);            // dst[idx[i]]=a
+  template <typename T, typename U>
+  void idx_pair_copy(T *dst, const uint32_t *dst_idx, const U *src, const uint32_t *src_idx, uint32_t n, cudaStream_t s);
+
+  // Chebyshev vector update (PreconditionChebyshev's vector_updates):
+  //   it==0: x = f2 dinv rhs
+  //   it==1: x_new = (1+f1) x + f2 dinv (rhs - t)
+  //   it>=2: x_new = (1+f1) x - f1 x_old + f2 dinv (rhs - t)
+  // x_new is written into x_old's storage (caller swaps pointers)
+  template <typename T>
+  void cheb_update(int it, T f1, T f2, const T *rhs, const T *dinv, const T *t, const T *x, T *x_old, size_t n,
+                   cudaStream_t s);
+  // d = (|d| > 1e-10) ? 1/d : 1   (include/operator.h:240-241)
+  template <typename T> void invert_diagonal(T *d, size_t n, cudaStream_t s);
+
+  // ---------------------------------------------------------------- cell kernels (operator.cu)
+  struct CellData
+  {
+    int             degree     = 1;
+    long long       n_cells    = 0;
+    const uint32_t *etab       = nullptr; // n_cells*27 entity table (local indices | FLAG_BIT)
+    const uint16_t *mask       = nullptr; // n_cells hanging-node masks (may be null)
+    const uint8_t  *level      = nullptr; // n_cells refinement levels; h = root_length / 2^level
+    double          root_length = 2.0;
+    int             any_hanging = 0;
+  };
+  // dst += A_cells src   (scatter-add with FP atomics); cell_list (optional) restricts to a subset of cells
+  template <typename T>
+  void cell_laplace_apply(const CellData &cd, const T *src, T *dst, const uint32_t *cell_list, long long n_list,
+                          cudaStream_t s);
+  // diag += diag(C^T A_e C) cell-wise (MatrixFreeTools::compute_diagonal)
+  template <typename T> void cell_laplace_diagonal(const CellData &cd, T *diag, cudaStream_t s);
+
+  // ---------------------------------------------------------------- transfers (transfer.cu)
+  struct TransferData
+  {
+    int             degree_fine = 1, degree_coarse = 1;
+    long long       n_coarse_cells = 0;
+    const uint32_t *coarse_etab    = nullptr; // eval table of the coarse cells
+    const uint16_t *coarse_mask    = nullptr;
+    int             coarse_any_hanging = 0;
+    const uint32_t *fine_own       = nullptr; // own table of the fine cells
+    const uint32_t *fine_first     = nullptr;
+    const uint8_t  *n_children     = nullptr;
+    const uint8_t  *weight_code    = nullptr; // per fine cell-entity
+    const double   *P_h            = nullptr; // device: (2pc+1) x (pc+1) h-embedding of the coarse degree
+    const double   *P_p            = nullptr; // device: (pf+1) x (pc+1) p-embedding (identity if pf==pc)
+  };
+  template <typename T> void transfer_prolongate_add(const TransferData &td, T *dst_fine, const T *src_coarse, cudaStream_t s);
+  template <typename T> void transfer_restrict_add(const TransferData &td, T *dst_coarse, const T *src_fine, cudaStream_t s);
+} // namespace mgb

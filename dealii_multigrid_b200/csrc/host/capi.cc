@@ -1,0 +1,822 @@
+// extern "C" boundary (include/mgb200.h): plain pointers and sizes in, opaque handles out.
+#include "mgb200.h"
+
+#include "comm.h"
+#include "problem.h"
+
+#include <cstring>
+#include <map>
+
+using namespace mgb;
+
+namespace
+{
+  thread_local std::string g_error;
+
+  template <class F> int guarded(F &&f)
+  {
+    try
+      {
+        f();
+        return 0;
+      }
+    catch (const std::exception &e)
+      {
+        g_error = e.what();
+        return 1;
+      }
+    catch (...)
+      {
+        g_error = "unknown exception";
+        return 2;
+      }
+  }
+} // namespace
+
+struct mgb_mesh
+{
+  Mesh m;
+};
+struct mgb_dofmap
+{
+  const DoFMap           *d = nullptr;
+  std::unique_ptr<DoFMap> owned;
+};
+struct mgb_transfer_map
+{
+  TransferMap t;
+  long long   n_fine_cells = 0;
+};
+struct mgb_vector
+{
+  int                           type = MGB_DOUBLE;
+  DVec<double>                 *pd   = nullptr;
+  DVec<float>                  *pf   = nullptr;
+  std::unique_ptr<DVec<double>> od;
+  std::unique_ptr<DVec<float>>  of;
+};
+struct mgb_operator
+{
+  int                                type = MGB_DOUBLE;
+  OperatorT<double>                 *pd   = nullptr;
+  OperatorT<float>                  *pf   = nullptr;
+  std::unique_ptr<OperatorT<double>> od;
+  std::unique_ptr<OperatorT<float>>  of;
+};
+struct mgb_chebyshev
+{
+  int                                 type = MGB_DOUBLE;
+  ChebyshevT<double>                 *pd   = nullptr;
+  ChebyshevT<float>                  *pf   = nullptr;
+  std::unique_ptr<ChebyshevT<double>> od;
+  std::unique_ptr<ChebyshevT<float>>  of;
+};
+struct mgb_transfer
+{
+  int                                        type = MGB_DOUBLE;
+  TwoLevelTransferT<double>                 *pd   = nullptr;
+  TwoLevelTransferT<float>                  *pf   = nullptr;
+  std::unique_ptr<TwoLevelTransferT<double>> od;
+  std::unique_ptr<TwoLevelTransferT<float>>  of;
+};
+struct mgb_problem
+{
+  std::unique_ptr<ProblemBase>                         p;
+  std::map<int, std::unique_ptr<mgb_dofmap>>           dofmaps;
+  std::map<int, std::unique_ptr<mgb_operator>>         operators;
+  std::map<int, std::unique_ptr<mgb_chebyshev>>        smoothers;
+  std::map<int, std::unique_ptr<mgb_transfer>>         transfers;
+  std::unique_ptr<mgb_operator>                        fine_op;
+  std::unique_ptr<mgb_vector>                          rhs, solution;
+};
+
+namespace
+{
+  void require_same_type(int a, int b)
+  {
+    if (a != b)
+      throw std::runtime_error("number types of the arguments differ");
+  }
+  void fill_result(const Result &r, mgb_result *o)
+  {
+    std::memset(o, 0, sizeof(*o));
+    o->dim               = r.dim;
+    o->degree            = r.degree;
+    o->n_ref_global      = r.n_ref_global;
+    o->n_ref_local       = r.n_ref_local;
+    o->n_levels          = r.n_levels;
+    o->n_iterations      = r.n_iterations;
+    o->sub_comm_size     = r.sub_comm_size;
+    o->n_cells           = r.n_cells;
+    o->n_cells_hn        = r.n_cells_hn;
+    o->n_cells_n         = r.n_cells_n;
+    o->n_dofs            = r.n_dofs;
+    o->time              = r.time;
+    o->time_cg           = r.time_cg;
+    o->throughput        = r.throughput;
+    o->time_pre          = r.stage[STAGE_PRE];
+    o->time_residuum     = r.stage[STAGE_RESIDUAL];
+    o->time_res          = r.stage[STAGE_RESTRICTION];
+    o->time_cs           = r.stage[STAGE_COARSE];
+    o->time_pro          = r.stage[STAGE_PROLONGATION];
+    o->time_edge_pro     = r.stage[STAGE_EDGE_PROLONGATION];
+    o->time_post         = r.stage[STAGE_POST];
+    o->time_to_mg        = r.stage[N_STAGES];
+    o->time_to_global    = r.stage[N_STAGES + 1];
+    o->initial_residual  = r.initial_residual;
+    o->final_residual    = r.final_residual;
+    o->coarse_iterations = r.coarse_iterations;
+  }
+} // namespace
+
+extern "C" {
+
+const char *mgb_last_error(void) { return g_error.c_str(); }
+const char *mgb_version(void) { return "mgb200 0.1 (sm_100a)"; }
+
+int mgb_init(int device)
+{
+  return guarded([&] {
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0)
+      throw std::runtime_error("mgb200: no CUDA device available (this library has no CPU path)");
+    MGB_CUDA(cudaSetDevice(device));
+    ctx().device = device;
+    ctx().ensure();
+  });
+}
+int mgb_set_stream(void *s)
+{
+  return guarded([&] { ctx().stream = (cudaStream_t)s; });
+}
+int mgb_synchronize(void)
+{
+  return guarded([&] { MGB_CUDA(cudaStreamSynchronize(ctx().stream)); });
+}
+int64_t mgb_launch_count(void) { return ctx().launches; }
+
+int mgb_comm_unique_id(void *out128, const char *libnccl_path)
+{
+  return guarded([&] { nccl_get_unique_id(out128, libnccl_path); });
+}
+int mgb_comm_init(const void *id, int rank, int size, const char *libnccl_path)
+{
+  return guarded([&] {
+    ctx().ensure();
+    if (ctx().comm)
+      throw std::runtime_error("communicator already initialised");
+    ctx().comm = create_nccl_comm(id, rank, size, libnccl_path);
+  });
+}
+int mgb_comm_finalize(void)
+{
+  return guarded([&] {
+    delete ctx().comm;
+    ctx().comm = nullptr;
+  });
+}
+
+int mgb_fe_1d(int degree, double *nodes, double *M, double *K, double *S0, double *S1, double *Ph)
+{
+  return guarded([&] {
+    FE1D         fe(degree);
+    const size_t n = fe.n;
+    if (nodes)
+      std::memcpy(nodes, fe.nodes.data(), n * sizeof(double));
+    if (M)
+      std::memcpy(M, fe.M.data(), n * n * sizeof(double));
+    if (K)
+      std::memcpy(K, fe.K.data(), n * n * sizeof(double));
+    if (S0)
+      std::memcpy(S0, fe.S[0].data(), n * n * sizeof(double));
+    if (S1)
+      std::memcpy(S1, fe.S[1].data(), n * n * sizeof(double));
+    if (Ph)
+      std::memcpy(Ph, fe.Ph.data(), fe.Ph.size() * sizeof(double));
+  });
+}
+int mgb_fe_p_embedding(int pf, int pc, double *Pp)
+{
+  return guarded([&] {
+    const auto P = p_embedding(pf, pc);
+    std::memcpy(Pp, P.data(), P.size() * sizeof(double));
+  });
+}
+
+// ---- mesh
+int mgb_mesh_create(const char *geometry, unsigned n_ref_global, unsigned n_ref_local, mgb_mesh **out)
+{
+  return guarded([&] {
+    auto h = std::make_unique<mgb_mesh>();
+    h->m   = Mesh::create(geometry, n_ref_global, n_ref_local);
+    h->m.rebuild_index();
+    *out = h.release();
+  });
+}
+int mgb_mesh_coarsen(const mgb_mesh *fine, mgb_mesh **out)
+{
+  return guarded([&] {
+    auto h = std::make_unique<mgb_mesh>();
+    h->m   = fine->m.coarsen_global();
+    h->m.rebuild_index();
+    *out = h.release();
+  });
+}
+int64_t mgb_mesh_n_cells(const mgb_mesh *m) { return (int64_t)m->m.cells.size(); }
+int     mgb_mesh_n_levels(const mgb_mesh *m) { return m->m.n_global_levels(); }
+int     mgb_mesh_get_cells(const mgb_mesh *m, uint32_t *o)
+{
+  return guarded([&] {
+    for (size_t i = 0; i < m->m.cells.size(); ++i)
+      {
+        o[4 * i + 0] = m->m.cells[i].level;
+        o[4 * i + 1] = m->m.cells[i].x;
+        o[4 * i + 2] = m->m.cells[i].y;
+        o[4 * i + 3] = m->m.cells[i].z;
+      }
+  });
+}
+void mgb_mesh_destroy(mgb_mesh *m) { delete m; }
+
+// ---- dofmap
+int mgb_dofmap_create(const mgb_mesh *m, int degree, int n_ranks, int rank, mgb_dofmap **out)
+{
+  return guarded([&] {
+    if (degree > MAX_DEGREE)
+      throw std::runtime_error("degree > MAX_DEGREE");
+    auto h   = std::make_unique<mgb_dofmap>();
+    h->owned = std::make_unique<DoFMap>(DoFMap::build(m->m, degree, n_ranks, rank));
+    h->d     = h->owned.get();
+    *out     = h.release();
+  });
+}
+int mgb_dofmap_view_get(const mgb_dofmap *h, mgb_dofmap_view *v)
+{
+  return guarded([&] {
+    const DoFMap &d     = *h->d;
+    v->degree           = d.degree;
+    v->n_ranks          = d.n_ranks;
+    v->rank             = d.rank;
+    v->mesh_max_level   = d.mesh_max_level;
+    v->n_cells_global   = d.n_cells_global;
+    v->cell_begin       = d.cell_begin;
+    v->n_cells          = d.n_cells;
+    v->n_cells_hanging  = d.n_cells_hanging;
+    v->n_dofs_global    = d.part.n_global;
+    v->owned_begin      = d.part.owned_begin;
+    v->n_owned          = d.part.n_owned;
+    v->n_ghost          = d.part.n_ghost;
+    v->n_constrained    = (uint32_t)d.constrained.size();
+    v->n_ghost_ranks    = (uint32_t)d.part.ghost_ranks.size();
+    v->n_import_ranks   = (uint32_t)d.part.import_ranks.size();
+    v->n_import_indices = (uint32_t)d.part.import_indices.size();
+    v->eval_table       = d.eval_table.data();
+    v->own_table        = d.own_table.data();
+    v->mask             = d.mask.data();
+    v->cell_level       = d.cell_level.data();
+    v->cell_xyz         = d.cell_xyz.data();
+    v->constrained      = d.constrained.data();
+    v->ghost_global     = d.part.ghost_global.data();
+    v->ghost_ranks      = d.part.ghost_ranks.data();
+    v->ghost_offsets    = d.part.ghost_offsets.data();
+    v->import_ranks     = d.part.import_ranks.data();
+    v->import_offsets   = d.part.import_offsets.data();
+    v->import_indices   = d.part.import_indices.data();
+  });
+}
+int mgb_dofmap_expand(const mgb_dofmap *h, int which, uint32_t *out)
+{
+  return guarded([&] {
+    std::vector<uint32_t> tmp;
+    h->d->expand(which == 0 ? h->d->eval_table : h->d->own_table, tmp);
+    std::memcpy(out, tmp.data(), tmp.size() * sizeof(uint32_t));
+  });
+}
+void mgb_dofmap_destroy(mgb_dofmap *d) { delete d; }
+
+int mgb_transfer_map_create(const mgb_mesh *mf, const mgb_dofmap *f, const mgb_mesh *mc, const mgb_dofmap *c, mgb_transfer_map **out)
+{
+  return guarded([&] {
+    auto h          = std::make_unique<mgb_transfer_map>();
+    h->t            = TransferMap::build(mf->m, *f->d, mc->m, *c->d);
+    h->n_fine_cells = f->d->n_cells;
+    *out            = h.release();
+  });
+}
+int mgb_transfer_map_view_get(const mgb_transfer_map *t, mgb_transfer_map_view *v)
+{
+  return guarded([&] {
+    v->degree_fine    = t->t.degree_fine;
+    v->degree_coarse  = t->t.degree_coarse;
+    v->n_coarse_cells = t->t.n_coarse_cells;
+    v->n_fine_cells   = t->n_fine_cells;
+    v->fine_first     = t->t.fine_first.data();
+    v->n_children     = t->t.n_children.data();
+    v->weight_code    = t->t.weight_code.data();
+  });
+}
+void mgb_transfer_map_destroy(mgb_transfer_map *t) { delete t; }
+
+// ---- vectors
+int mgb_vector_create(uint32_t n_owned, uint32_t n_ghost, int type, mgb_vector **out)
+{
+  return guarded([&] {
+    ctx().ensure();
+    auto h  = std::make_unique<mgb_vector>();
+    h->type = type;
+    if (type == MGB_DOUBLE)
+      {
+        h->od = std::make_unique<DVec<double>>();
+        h->od->reinit(n_owned, n_ghost);
+        h->pd = h->od.get();
+      }
+    else if (type == MGB_FLOAT)
+      {
+        h->of = std::make_unique<DVec<float>>();
+        h->of->reinit(n_owned, n_ghost);
+        h->pf = h->of.get();
+      }
+    else
+      throw std::runtime_error("unknown number type");
+    *out = h.release();
+  });
+}
+int mgb_vector_wrap(void *ptr, uint32_t n_owned, uint32_t n_ghost, int type, mgb_vector **out)
+{
+  return guarded([&] {
+    ctx().ensure();
+    auto h  = std::make_unique<mgb_vector>();
+    h->type = type;
+    if (type == MGB_DOUBLE)
+      {
+        h->od = std::make_unique<DVec<double>>();
+        h->od->wrap((double *)ptr, n_owned, n_ghost);
+        h->pd = h->od.get();
+      }
+    else if (type == MGB_FLOAT)
+      {
+        h->of = std::make_unique<DVec<float>>();
+        h->of->wrap((float *)ptr, n_owned, n_ghost);
+        h->pf = h->of.get();
+      }
+    else
+      throw std::runtime_error("unknown number type");
+    *out = h.release();
+  });
+}
+void     mgb_vector_destroy(mgb_vector *v) { delete v; }
+uint32_t mgb_vector_n_owned(const mgb_vector *v) { return v->type == MGB_DOUBLE ? v->pd->n_owned : v->pf->n_owned; }
+void    *mgb_vector_data(mgb_vector *v) { return v->type == MGB_DOUBLE ? (void *)v->pd->data : (void *)v->pf->data; }
+
+#define VEC_DISPATCH(v, EXPR_D, EXPR_F) \
+  do                                    \
+    {                                   \
+      if ((v)->type == MGB_DOUBLE)      \
+        {                               \
+          auto &V = *(v)->pd;           \
+          (void)V;                      \
+          EXPR_D;                       \
+        }                               \
+      else                              \
+        {                               \
+          auto &V = *(v)->pf;           \
+          (void)V;                      \
+          EXPR_F;                       \
+        }                               \
+    }                                   \
+  while (0)
+
+int mgb_vector_copy_from_host(mgb_vector *v, const void *host, uint32_t n)
+{
+  return guarded([&] {
+    VEC_DISPATCH(v,
+                 { if (n > V.size_local()) throw std::runtime_error("copy_from_host: n too large");
+                   MGB_CUDA(cudaMemcpyAsync(V.data, host, size_t(n) * sizeof(double), cudaMemcpyHostToDevice, ctx().stream)); },
+                 { if (n > V.size_local()) throw std::runtime_error("copy_from_host: n too large");
+                   MGB_CUDA(cudaMemcpyAsync(V.data, host, size_t(n) * sizeof(float), cudaMemcpyHostToDevice, ctx().stream)); });
+    MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+  });
+}
+int mgb_vector_copy_to_host(const mgb_vector *v, void *host, uint32_t n)
+{
+  return guarded([&] {
+    VEC_DISPATCH(v,
+                 { if (n > V.size_local()) throw std::runtime_error("copy_to_host: n too large");
+                   MGB_CUDA(cudaMemcpyAsync(host, V.data, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, ctx().stream)); },
+                 { if (n > V.size_local()) throw std::runtime_error("copy_to_host: n too large");
+                   MGB_CUDA(cudaMemcpyAsync(host, V.data, size_t(n) * sizeof(float), cudaMemcpyDeviceToHost, ctx().stream)); });
+    MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+  });
+}
+int mgb_vector_set(mgb_vector *v, double a)
+{
+  return guarded([&] { VEC_DISPATCH(v, V.set(a), V.set(float(a))); });
+}
+int mgb_vector_add(mgb_vector *y, double a, const mgb_vector *x)
+{
+  return guarded([&] {
+    require_same_type(y->type, x->type);
+    VEC_DISPATCH(y, V.add(a, *x->pd), V.add(float(a), *x->pf));
+  });
+}
+int mgb_vector_sadd(mgb_vector *y, double s, double a, const mgb_vector *x)
+{
+  return guarded([&] {
+    require_same_type(y->type, x->type);
+    VEC_DISPATCH(y, V.sadd(s, a, *x->pd), V.sadd(float(s), float(a), *x->pf));
+  });
+}
+int mgb_vector_equ(mgb_vector *y, double a, const mgb_vector *x)
+{
+  return guarded([&] {
+    require_same_type(y->type, x->type);
+    VEC_DISPATCH(y, V.equ(a, *x->pd), V.equ(float(a), *x->pf));
+  });
+}
+int mgb_vector_dot(const mgb_vector *x, const mgb_vector *y, double *result)
+{
+  return guarded([&] {
+    require_same_type(y->type, x->type);
+    VEC_DISPATCH(x, *result = V.dot(*y->pd), *result = V.dot(*y->pf));
+  });
+}
+int mgb_vector_l2_norm(const mgb_vector *x, double *result)
+{
+  return guarded([&] { VEC_DISPATCH(x, *result = V.l2_norm(), *result = V.l2_norm()); });
+}
+int mgb_vector_add_and_dot(mgb_vector *g, double a, const mgb_vector *h, double *result)
+{
+  return guarded([&] {
+    require_same_type(g->type, h->type);
+    VEC_DISPATCH(g, *result = V.add_and_dot(a, *h->pd), *result = V.add_and_dot(float(a), *h->pf));
+  });
+}
+int mgb_vector_update_ghost_values(const mgb_vector *v)
+{
+  return guarded([&] { VEC_DISPATCH(v, V.update_ghost_values(), V.update_ghost_values()); });
+}
+int mgb_vector_compress_add(mgb_vector *v)
+{
+  return guarded([&] { VEC_DISPATCH(v, V.compress_add(), V.compress_add()); });
+}
+int mgb_vector_zero_out_ghost_values(mgb_vector *v)
+{
+  return guarded([&] { VEC_DISPATCH(v, V.zero_out_ghost_values(), V.zero_out_ghost_values()); });
+}
+
+// ---- operator
+namespace
+{
+  std::unique_ptr<mgb_operator> make_operator(const OperatorSetup &s, int type)
+  {
+    auto h  = std::make_unique<mgb_operator>();
+    h->type = type;
+    if (type == MGB_DOUBLE)
+      {
+        h->od = std::make_unique<OperatorT<double>>(s);
+        h->pd = h->od.get();
+      }
+    else if (type == MGB_FLOAT)
+      {
+        h->of = std::make_unique<OperatorT<float>>(s);
+        h->pf = h->of.get();
+      }
+    else
+      throw std::runtime_error("unknown number type");
+    return h;
+  }
+
+  // compress a full lexicographic index map into the 27-entry entity table
+  std::vector<uint32_t> compress_dof_indices(const uint32_t *idx, long long n_cells, int p)
+  {
+    const int        n = p + 1, n3 = n * n * n;
+    std::vector<int> ent(n3), off(n3);
+    for (int k = 0; k < n; ++k)
+      for (int j = 0; j < n; ++j)
+        for (int i = 0; i < n; ++i)
+          node_entity(p, i, j, k, ent[(k * n + j) * n + i], off[(k * n + j) * n + i]);
+    std::vector<uint32_t> tab(size_t(n_cells) * 27, 0);
+    for (long long c = 0; c < n_cells; ++c)
+      {
+        for (int q = 0; q < n3; ++q)
+          if (off[q] == 0)
+            tab[c * 27 + ent[q]] = idx[c * n3 + q];
+        for (int q = 0; q < n3; ++q)
+          {
+            const uint32_t t = tab[c * 27 + ent[q]];
+            if (idx[c * n3 + q] != (((t & INDEX_MASK) + uint32_t(off[q])) | (t & FLAG_BIT)))
+              throw std::runtime_error("dof_indices of a cell are not contiguous per mesh entity; cannot build the entity table");
+          }
+      }
+    return tab;
+  }
+} // namespace
+
+int mgb_operator_create(const mgb_operator_desc *d, mgb_operator **out)
+{
+  return guarded([&] {
+    if ((d->entity_table == nullptr) == (d->dof_indices == nullptr))
+      throw std::runtime_error("exactly one of entity_table / dof_indices must be given");
+    if (d->degree < 1 || d->degree > MAX_DEGREE)
+      throw std::runtime_error("degree out of range");
+    std::vector<uint32_t> compressed;
+    OperatorSetup         s;
+    s.degree  = d->degree;
+    s.n_cells = d->n_cells;
+    if (d->entity_table)
+      s.entity_table = d->entity_table;
+    else
+      {
+        compressed     = compress_dof_indices(d->dof_indices, d->n_cells, d->degree);
+        s.entity_table = compressed.data();
+      }
+    s.mask                        = d->mask;
+    s.cell_level                  = d->cell_level;
+    s.root_length                 = d->root_length;
+    s.constrained                 = d->constrained;
+    s.n_constrained               = d->n_constrained;
+    s.edge_constrained            = d->edge_constrained;
+    s.n_edge_constrained          = d->n_edge_constrained;
+    s.has_edge_constrained_global = d->has_edge_constrained_global != 0;
+    s.edge_cells                  = d->edge_cells;
+    s.n_edge_cells                = d->n_edge_cells;
+    s.n_dofs_global               = d->n_dofs_global;
+    Partitioner part;
+    part.n_global    = d->n_dofs_global;
+    part.owned_begin = d->owned_begin;
+    part.n_owned     = d->n_owned;
+    part.n_ghost     = d->n_ghost;
+    if (d->n_ghost)
+      part.ghost_global.assign(d->ghost_global, d->ghost_global + d->n_ghost);
+    part.ghost_ranks.assign(d->ghost_ranks, d->ghost_ranks + d->n_ghost_ranks);
+    if (d->ghost_offsets)
+      part.ghost_offsets.assign(d->ghost_offsets, d->ghost_offsets + d->n_ghost_ranks + 1);
+    else
+      part.ghost_offsets.assign(1, 0u);
+    part.import_ranks.assign(d->import_ranks, d->import_ranks + d->n_import_ranks);
+    if (d->import_offsets)
+      part.import_offsets.assign(d->import_offsets, d->import_offsets + d->n_import_ranks + 1);
+    else
+      part.import_offsets.assign(1, 0u);
+    if (d->n_import_ranks)
+      part.import_indices.assign(d->import_indices, d->import_indices + part.import_offsets.back());
+    s.partitioner = &part;
+    *out          = make_operator(s, d->number_type).release();
+  });
+}
+int mgb_operator_create_from_dofmap(const mgb_dofmap *dm, int type, mgb_operator **out)
+{
+  return guarded([&] {
+    const DoFMap &d = *dm->d;
+    OperatorSetup s;
+    s.degree        = d.degree;
+    s.n_cells       = d.n_cells;
+    s.entity_table  = d.eval_table.data();
+    s.mask          = d.mask.data();
+    s.cell_level    = d.cell_level.data();
+    s.constrained   = d.constrained.data();
+    s.n_constrained = (uint32_t)d.constrained.size();
+    s.n_dofs_global = d.part.n_global;
+    s.partitioner   = &d.part;
+    *out            = make_operator(s, type).release();
+  });
+}
+void    mgb_operator_destroy(mgb_operator *op) { delete op; }
+int64_t mgb_operator_m(const mgb_operator *op) { return op->type == MGB_DOUBLE ? op->pd->m() : op->pf->m(); }
+
+int mgb_operator_initialize_dof_vector(const mgb_operator *op, mgb_vector **out)
+{
+  return guarded([&] {
+    auto h  = std::make_unique<mgb_vector>();
+    h->type = op->type;
+    if (op->type == MGB_DOUBLE)
+      {
+        h->od = std::make_unique<DVec<double>>();
+        op->pd->initialize_dof_vector(*h->od);
+        h->pd = h->od.get();
+      }
+    else
+      {
+        h->of = std::make_unique<DVec<float>>();
+        op->pf->initialize_dof_vector(*h->of);
+        h->pf = h->of.get();
+      }
+    *out = h.release();
+  });
+}
+
+#define OP_CALL(METHOD)                                                                \
+  return guarded([&] {                                                                 \
+    require_same_type(op->type, dst->type);                                            \
+    require_same_type(op->type, src->type);                                            \
+    if (op->type == MGB_DOUBLE)                                                        \
+      op->pd->METHOD(*dst->pd, *src->pd);                                              \
+    else                                                                               \
+      op->pf->METHOD(*dst->pf, *src->pf);                                              \
+  })
+
+int mgb_operator_vmult(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src) { OP_CALL(vmult); }
+int mgb_operator_tvmult(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src) { OP_CALL(Tvmult); }
+int mgb_operator_vmult_interface_down(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src) { OP_CALL(vmult_interface_down); }
+int mgb_operator_vmult_interface_up(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src) { OP_CALL(vmult_interface_up); }
+int mgb_operator_compute_inverse_diagonal(const mgb_operator *op, mgb_vector *diag)
+{
+  return guarded([&] {
+    require_same_type(op->type, diag->type);
+    if (op->type == MGB_DOUBLE)
+      op->pd->compute_inverse_diagonal(*diag->pd);
+    else
+      op->pf->compute_inverse_diagonal(*diag->pf);
+  });
+}
+
+// ---- Chebyshev
+int mgb_chebyshev_create(const mgb_operator *op, int degree, double smoothing_range, unsigned eig_its, mgb_chebyshev **out)
+{
+  return guarded([&] {
+    auto h  = std::make_unique<mgb_chebyshev>();
+    h->type = op->type;
+    if (op->type == MGB_DOUBLE)
+      {
+        h->od = std::make_unique<ChebyshevT<double>>(*op->pd, degree, smoothing_range, eig_its);
+        h->pd = h->od.get();
+      }
+    else
+      {
+        h->of = std::make_unique<ChebyshevT<float>>(*op->pf, degree, smoothing_range, eig_its);
+        h->pf = h->of.get();
+      }
+    *out = h.release();
+  });
+}
+void mgb_chebyshev_destroy(mgb_chebyshev *c) { delete c; }
+int  mgb_chebyshev_vmult(mgb_chebyshev *c, mgb_vector *dst, const mgb_vector *rhs)
+{
+  return guarded([&] {
+    require_same_type(c->type, dst->type);
+    require_same_type(c->type, rhs->type);
+    if (c->type == MGB_DOUBLE)
+      c->pd->vmult(*dst->pd, *rhs->pd);
+    else
+      c->pf->vmult(*dst->pf, *rhs->pf);
+  });
+}
+int mgb_chebyshev_step(mgb_chebyshev *c, mgb_vector *dst, const mgb_vector *rhs)
+{
+  return guarded([&] {
+    require_same_type(c->type, dst->type);
+    require_same_type(c->type, rhs->type);
+    if (c->type == MGB_DOUBLE)
+      c->pd->step(*dst->pd, *rhs->pd);
+    else
+      c->pf->step(*dst->pf, *rhs->pf);
+  });
+}
+int mgb_chebyshev_eigenvalues(mgb_chebyshev *c, double *lmin, double *lmax)
+{
+  return guarded([&] {
+    if (c->type == MGB_DOUBLE)
+      {
+        c->pd->estimate_eigenvalues();
+        *lmin = c->pd->lambda_min_estimate();
+        *lmax = c->pd->lambda_max();
+      }
+    else
+      {
+        c->pf->estimate_eigenvalues();
+        *lmin = c->pf->lambda_min_estimate();
+        *lmax = c->pf->lambda_max();
+      }
+  });
+}
+
+// ---- transfer
+int mgb_transfer_create(const mgb_dofmap *fine, const mgb_dofmap *coarse, const mgb_transfer_map *map, const mgb_operator *opf,
+                        const mgb_operator *opc, mgb_transfer **out)
+{
+  return guarded([&] {
+    require_same_type(opf->type, opc->type);
+    auto h  = std::make_unique<mgb_transfer>();
+    h->type = opf->type;
+    if (h->type == MGB_DOUBLE)
+      {
+        h->od = std::make_unique<TwoLevelTransferT<double>>(*fine->d, *coarse->d, map->t, *opf->pd, *opc->pd);
+        h->pd = h->od.get();
+      }
+    else
+      {
+        h->of = std::make_unique<TwoLevelTransferT<float>>(*fine->d, *coarse->d, map->t, *opf->pf, *opc->pf);
+        h->pf = h->of.get();
+      }
+    *out = h.release();
+  });
+}
+void mgb_transfer_destroy(mgb_transfer *t) { delete t; }
+int  mgb_transfer_prolongate_and_add(const mgb_transfer *t, mgb_vector *dst, const mgb_vector *src)
+{
+  return guarded([&] {
+    require_same_type(t->type, dst->type);
+    require_same_type(t->type, src->type);
+    if (t->type == MGB_DOUBLE)
+      t->pd->prolongate_and_add(*dst->pd, *src->pd);
+    else
+      t->pf->prolongate_and_add(*dst->pf, *src->pf);
+  });
+}
+int mgb_transfer_restrict_and_add(const mgb_transfer *t, mgb_vector *dst, const mgb_vector *src)
+{
+  return guarded([&] {
+    require_same_type(t->type, dst->type);
+    require_same_type(t->type, src->type);
+    if (t->type == MGB_DOUBLE)
+      t->pd->restrict_and_add(*dst->pd, *src->pd);
+    else
+      t->pf->restrict_and_add(*dst->pf, *src->pf);
+  });
+}
+
+// ---- problem
+int mgb_problem_create(const char *json_text, int n_ranks, int rank, mgb_problem **out)
+{
+  return guarded([&] {
+    ctx().ensure();
+    auto h = std::make_unique<mgb_problem>();
+    h->p.reset(create_problem(json_text, n_ranks, rank));
+    const int type = h->p->level_number_type();
+    for (int l = 0; l < h->p->n_levels(); ++l)
+      {
+        auto dm = std::make_unique<mgb_dofmap>();
+        dm->d   = &h->p->level_dofmap(l);
+        h->dofmaps[l] = std::move(dm);
+        auto op  = std::make_unique<mgb_operator>();
+        op->type = type;
+        if (type == MGB_DOUBLE)
+          op->pd = static_cast<OperatorT<double> *>(h->p->level_operator(l));
+        else
+          op->pf = static_cast<OperatorT<float> *>(h->p->level_operator(l));
+        h->operators[l] = std::move(op);
+        auto sm  = std::make_unique<mgb_chebyshev>();
+        sm->type = type;
+        if (type == MGB_DOUBLE)
+          sm->pd = static_cast<ChebyshevT<double> *>(h->p->level_smoother(l));
+        else
+          sm->pf = static_cast<ChebyshevT<float> *>(h->p->level_smoother(l));
+        h->smoothers[l] = std::move(sm);
+        if (l > 0)
+          {
+            auto tr  = std::make_unique<mgb_transfer>();
+            tr->type = type;
+            if (type == MGB_DOUBLE)
+              tr->pd = static_cast<TwoLevelTransferT<double> *>(h->p->level_transfer(l));
+            else
+              tr->pf = static_cast<TwoLevelTransferT<float> *>(h->p->level_transfer(l));
+            h->transfers[l] = std::move(tr);
+          }
+      }
+    h->fine_op       = std::make_unique<mgb_operator>();
+    h->fine_op->type = MGB_DOUBLE;
+    h->fine_op->pd   = &h->p->fine_operator();
+    h->rhs           = std::make_unique<mgb_vector>();
+    h->rhs->type     = MGB_DOUBLE;
+    h->rhs->pd       = &h->p->rhs();
+    h->solution      = std::make_unique<mgb_vector>();
+    h->solution->type = MGB_DOUBLE;
+    h->solution->pd  = &h->p->solution();
+    *out             = h.release();
+  });
+}
+void    mgb_problem_destroy(mgb_problem *p) { delete p; }
+int     mgb_problem_n_levels(const mgb_problem *p) { return p->p->n_levels(); }
+int64_t mgb_problem_level_n_dofs(const mgb_problem *p, int l) { return p->p->level_dofmap(l).part.n_global; }
+int64_t mgb_problem_level_n_cells(const mgb_problem *p, int l) { return p->p->level_dofmap(l).n_cells_global; }
+int     mgb_problem_level_degree(const mgb_problem *p, int l) { return p->p->level_dofmap(l).degree; }
+const mgb_dofmap   *mgb_problem_level_dofmap(const mgb_problem *p, int l) { return p->dofmaps.at(l).get(); }
+const mgb_operator *mgb_problem_level_operator(const mgb_problem *p, int l) { return p->operators.at(l).get(); }
+mgb_chebyshev      *mgb_problem_level_smoother(mgb_problem *p, int l) { return p->smoothers.at(l).get(); }
+const mgb_transfer *mgb_problem_level_transfer(const mgb_problem *p, int l)
+{
+  auto it = p->transfers.find(l);
+  return it == p->transfers.end() ? nullptr : it->second.get();
+}
+const mgb_operator *mgb_problem_fine_operator(const mgb_problem *p) { return p->fine_op.get(); }
+mgb_vector         *mgb_problem_rhs(mgb_problem *p) { return p->rhs.get(); }
+mgb_vector         *mgb_problem_solution(mgb_problem *p) { return p->solution.get(); }
+
+int mgb_problem_vcycle(mgb_problem *p, mgb_vector *dst, const mgb_vector *src)
+{
+  return guarded([&] {
+    if (dst->type != MGB_DOUBLE || src->type != MGB_DOUBLE)
+      throw std::runtime_error("vcycle: outer vectors are double");
+    p->p->vcycle(*dst->pd, *src->pd);
+  });
+}
+int mgb_problem_solve_once(mgb_problem *p, int with_timers, mgb_result *result)
+{
+  return guarded([&] { fill_result(p->p->solve_once(with_timers != 0), result); });
+}
+int mgb_problem_run(mgb_problem *p, int n_repetitions, mgb_result *result)
+{
+  return guarded([&] { fill_result(p->p->run((unsigned)n_repetitions), result); });
+}
+
+} // extern "C"

@@ -1,0 +1,433 @@
+#include "dofmap.h"
+
+#include <algorithm>
+#include <stdexcept>
+
+namespace mgb
+{
+  const int ENTITY_ORDER[27] = {
+    // vertices
+    0, 2, 6, 8, 18, 20, 24, 26,
+    // lines
+    1, 3, 5, 7, 9, 11, 15, 17, 19, 21, 23, 25,
+    // quads
+    4, 10, 12, 14, 16, 22,
+    // hex
+    13};
+
+  void node_entity(int p, int i, int j, int k, int &e, int &offset)
+  {
+    const int tx = i == 0 ? 0 : (i == p ? 2 : 1);
+    const int ty = j == 0 ? 0 : (j == p ? 2 : 1);
+    const int tz = k == 0 ? 0 : (k == p ? 2 : 1);
+    e            = tx + 3 * ty + 9 * tz;
+    int stride   = 1;
+    offset       = 0;
+    if (tx == 1)
+      {
+        offset += (i - 1) * stride;
+        stride *= (p - 1);
+      }
+    if (ty == 1)
+      {
+        offset += (j - 1) * stride;
+        stride *= (p - 1);
+      }
+    if (tz == 1)
+      offset += (k - 1) * stride;
+  }
+
+  namespace
+  {
+    inline int ipow(int b, int e)
+    {
+      int r = 1;
+      for (int i = 0; i < e; ++i)
+        r *= b;
+      return r;
+    }
+
+    struct EntityKeys
+    {
+      int Lmax;
+      // key of entity e of the cell (level,x,y,z): doubled-lattice centre coordinates + extension mask
+      uint64_t operator()(int level, uint32_t x, uint32_t y, uint32_t z, int e) const
+      {
+        const uint64_t U  = uint64_t(1) << (Lmax - level);
+        const int      tx = e % 3, ty = (e / 3) % 3, tz = e / 9;
+        const uint64_t cx = (2 * uint64_t(x) + tx) * U, cy = (2 * uint64_t(y) + ty) * U,
+                       cz  = (2 * uint64_t(z) + tz) * U;
+        const uint64_t ext = uint64_t(tx == 1) | (uint64_t(ty == 1) << 1) | (uint64_t(tz == 1) << 2);
+        return (ext << 60) | (cx << 40) | (cy << 20) | cz;
+      }
+      bool on_boundary(uint64_t key) const
+      {
+        const uint64_t top = uint64_t(2) << Lmax;
+        const uint64_t ext = key >> 60;
+        const uint64_t c[3] = {(key >> 40) & 0xfffff, (key >> 20) & 0xfffff, key & 0xfffff};
+        for (int d = 0; d < 3; ++d)
+          if (!((ext >> d) & 1) && (c[d] == 0 || c[d] == top))
+            return true;
+        return false;
+      }
+    };
+
+    // hanging-node analysis of one leaf; fills eval keys (own keys with constrained faces/edges replaced
+    // by the parent's entities) and the mask
+    void analyse_cell(const Mesh &mesh, const EntityKeys &K, const Cell &c, uint64_t own[27], uint64_t eval[27],
+                      uint16_t &mask)
+    {
+      for (int e = 0; e < 27; ++e)
+        own[e] = eval[e] = K(c.level, c.x, c.y, c.z, e);
+      mask = 0;
+      if (c.level == 0)
+        return;
+      const uint32_t co[3] = {c.x, c.y, c.z};
+      const int      s[3]  = {int(c.x & 1), int(c.y & 1), int(c.z & 1)};
+      mask                 = uint16_t(s[0] | (s[1] << 1) | (s[2] << 2));
+      const int64_t N      = int64_t(1) << c.level;
+      // is the same-level region at offset (o0,o1,o2) covered by a leaf one level coarser?
+      const auto coarser = [&](int o0, int o1, int o2) -> bool {
+        const int64_t n[3] = {int64_t(co[0]) + o0, int64_t(co[1]) + o1, int64_t(co[2]) + o2};
+        for (int d = 0; d < 3; ++d)
+          if (n[d] < 0 || n[d] >= N)
+            return false;
+        return mesh.leaf(c.level - 1, uint32_t(n[0] >> 1), uint32_t(n[1] >> 1), uint32_t(n[2] >> 1)) >= 0;
+      };
+      bool face[3];
+      for (int d = 0; d < 3; ++d)
+        {
+          int o[3] = {0, 0, 0};
+          o[d]     = s[d] ? 1 : -1;
+          face[d]  = coarser(o[0], o[1], o[2]);
+          if (face[d])
+            mask |= uint16_t(MASK_FACE_X << d);
+        }
+      bool edge[3];
+      for (int d = 0; d < 3; ++d)
+        {
+          const int a = (d + 1) % 3, b = (d + 2) % 3;
+          edge[d] = false;
+          if (!face[a] && !face[b])
+            {
+              int o[3] = {0, 0, 0};
+              o[a]     = s[a] ? 1 : -1;
+              o[b]     = s[b] ? 1 : -1;
+              edge[d]  = coarser(o[0], o[1], o[2]);
+              if (edge[d])
+                mask |= uint16_t(MASK_EDGE_X << d);
+            }
+        }
+      if ((mask >> 3) == 0)
+        return;
+      const uint32_t px = c.x >> 1, py = c.y >> 1, pz = c.z >> 1;
+      for (int e = 0; e < 27; ++e)
+        {
+          const int t[3]    = {e % 3, (e / 3) % 3, e / 9};
+          bool      replace = false;
+          for (int d = 0; d < 3; ++d)
+            {
+              if (face[d] && t[d] == 2 * s[d])
+                replace = true;
+              const int a = (d + 1) % 3, b = (d + 2) % 3;
+              if (edge[d] && t[a] == 2 * s[a] && t[b] == 2 * s[b])
+                replace = true;
+            }
+          if (replace)
+            eval[e] = K(c.level - 1, px, py, pz, e);
+        }
+    }
+  } // namespace
+
+  DoFMap DoFMap::build(const Mesh &mesh, int degree, int n_ranks, int rank)
+  {
+    if (degree < 1)
+      throw std::runtime_error("DoFMap: degree must be >= 1");
+    DoFMap dm;
+    dm.degree         = degree;
+    dm.n_ranks        = n_ranks;
+    dm.rank           = rank;
+    dm.mesh_max_level = mesh.max_level();
+    const int64_t nc  = (int64_t)mesh.cells.size();
+    dm.n_cells_global = nc;
+    const EntityKeys K{dm.mesh_max_level};
+    int              esize[27];
+    for (int e = 0; e < 27; ++e)
+      esize[e] = ipow(degree - 1, entity_dim(e));
+
+    std::vector<int64_t> cell_begin(n_ranks + 1);
+    for (int r = 0; r <= n_ranks; ++r)
+      cell_begin[r] = (nc * r) / n_ranks;
+    dm.cell_begin = cell_begin[rank];
+    dm.n_cells    = cell_begin[rank + 1] - cell_begin[rank];
+
+    // pass 1: global numbering, Morton first touch
+    FlatMap ent;
+    ent.reserve(size_t(nc) * (degree > 1 ? 9 : 2) + 64);
+    std::vector<int64_t> dof_begin(n_ranks + 1, 0);
+    int64_t              next = 0;
+    {
+      int r = 0;
+      for (int64_t i = 0; i < nc; ++i)
+        {
+          while (r < n_ranks && cell_begin[r] == i)
+            dof_begin[r++] = next;
+          const Cell &c = mesh.cells[i];
+          for (int k = 0; k < 27; ++k)
+            {
+              const int e = ENTITY_ORDER[k];
+              if (esize[e] == 0)
+                continue;
+              const uint64_t key = K(c.level, c.x, c.y, c.z, e);
+              if (ent.find(key) < 0)
+                {
+                  ent.insert(key, next);
+                  next += esize[e];
+                }
+            }
+        }
+      while (r <= n_ranks)
+        dof_begin[r++] = next;
+    }
+    if (next >= int64_t(INDEX_MASK))
+      throw std::runtime_error("DoFMap: more than 2^31 DoFs need 64-bit local indices");
+    const int64_t my_begin = dof_begin[rank], my_end = dof_begin[rank + 1];
+    dm.part.n_global    = next;
+    dm.part.owned_begin = my_begin;
+    dm.part.n_owned     = uint32_t(my_end - my_begin);
+
+    // pass 2: tables with global bases; ghosts; imports; constrained entities
+    struct Ent
+    {
+      int64_t base;
+      int     size;
+      bool    operator<(const Ent &o) const { return base < o.base; }
+      bool    operator==(const Ent &o) const { return base == o.base; }
+    };
+    std::vector<int64_t>          g_eval(size_t(dm.n_cells) * 27), g_own(size_t(dm.n_cells) * 27);
+    std::vector<uint8_t>          f_eval(size_t(dm.n_cells) * 27), f_own(size_t(dm.n_cells) * 27);
+    std::vector<Ent>              ghosts, constrained_ents;
+    std::vector<std::vector<Ent>> imports(n_ranks);
+    dm.mask.resize(dm.n_cells);
+    dm.cell_level.resize(dm.n_cells);
+    dm.cell_xyz.resize(size_t(dm.n_cells) * 3);
+
+    const int64_t pass_begin = n_ranks == 1 ? cell_begin[rank] : 0;
+    const int64_t pass_end   = n_ranks == 1 ? cell_begin[rank + 1] : nc;
+    int           q          = 0;
+    for (int64_t i = pass_begin; i < pass_end; ++i)
+      {
+        while (cell_begin[q + 1] <= i)
+          ++q;
+        const Cell &c = mesh.cells[i];
+        uint64_t    own[27], eval[27];
+        uint16_t    mask;
+        analyse_cell(mesh, K, c, own, eval, mask);
+        if (q == rank)
+          {
+            const int64_t l = i - cell_begin[rank];
+            dm.mask[l]      = mask;
+            if (mask >> 3)
+              ++dm.n_cells_hanging;
+            dm.cell_level[l]       = c.level;
+            dm.cell_xyz[3 * l + 0] = c.x;
+            dm.cell_xyz[3 * l + 1] = c.y;
+            dm.cell_xyz[3 * l + 2] = c.z;
+            for (int e = 0; e < 27; ++e)
+              {
+                if (esize[e] == 0)
+                  {
+                    g_eval[l * 27 + e] = g_own[l * 27 + e] = my_begin;
+                    f_eval[l * 27 + e] = f_own[l * 27 + e] = 0;
+                    continue;
+                  }
+                const int64_t bo = ent.find(own[e]);
+                const int64_t be = (eval[e] == own[e]) ? bo : ent.find(eval[e]);
+                if (bo < 0 || be < 0)
+                  throw std::runtime_error("DoFMap: entity lookup failed (mesh not 2:1 balanced?)");
+                const bool dir_o = K.on_boundary(own[e]), dir_e = K.on_boundary(eval[e]);
+                const bool hang  = eval[e] != own[e];
+                g_own[l * 27 + e]  = bo;
+                g_eval[l * 27 + e] = be;
+                f_own[l * 27 + e]  = (dir_o || hang) ? 1 : 0;
+                f_eval[l * 27 + e] = dir_e ? 1 : 0;
+                if (bo < my_begin || bo >= my_end)
+                  ghosts.push_back(Ent{bo, esize[e]});
+                else if (dir_o || hang)
+                  constrained_ents.push_back(Ent{bo, esize[e]});
+                if (hang && (be < my_begin || be >= my_end))
+                  ghosts.push_back(Ent{be, esize[e]});
+              }
+          }
+        else
+          {
+            for (int e = 0; e < 27; ++e)
+              {
+                if (esize[e] == 0)
+                  continue;
+                const int64_t bo = ent.find(own[e]);
+                if (bo >= my_begin && bo < my_end)
+                  imports[q].push_back(Ent{bo, esize[e]});
+                if (eval[e] != own[e])
+                  {
+                    const int64_t be = ent.find(eval[e]);
+                    if (be >= my_begin && be < my_end)
+                      imports[q].push_back(Ent{be, esize[e]});
+                  }
+              }
+          }
+      }
+    // a constrained entity owned by us may only be touched by cells of other ranks' ... no: the first
+    // touching cell is ours by construction of ownership, so the loop above has seen it.
+
+    const auto uniq = [](std::vector<Ent> &v) {
+      std::sort(v.begin(), v.end());
+      v.erase(std::unique(v.begin(), v.end()), v.end());
+    };
+    uniq(ghosts);
+    uniq(constrained_ents);
+
+    // ghost numbering: ascending global index => grouped by owner
+    std::vector<uint32_t> ghost_off(ghosts.size() + 1, 0);
+    for (size_t g = 0; g < ghosts.size(); ++g)
+      ghost_off[g + 1] = ghost_off[g] + uint32_t(ghosts[g].size);
+    dm.part.n_ghost = ghost_off.back();
+    dm.part.ghost_global.resize(dm.part.n_ghost);
+    {
+      int owner = -1;
+      for (size_t g = 0; g < ghosts.size(); ++g)
+        {
+          for (int k = 0; k < ghosts[g].size; ++k)
+            dm.part.ghost_global[ghost_off[g] + k] = ghosts[g].base + k;
+          const int o =
+            int(std::upper_bound(dof_begin.begin(), dof_begin.end(), ghosts[g].base) - dof_begin.begin()) - 1;
+          if (o != owner)
+            {
+              dm.part.ghost_ranks.push_back(o);
+              dm.part.ghost_offsets.push_back(ghost_off[g]);
+              owner = o;
+            }
+        }
+      dm.part.ghost_offsets.push_back(dm.part.n_ghost);
+    }
+    dm.part.import_offsets.push_back(0);
+    for (int r = 0; r < n_ranks; ++r)
+      {
+        if (imports[r].empty())
+          continue;
+        uniq(imports[r]);
+        dm.part.import_ranks.push_back(r);
+        for (const Ent &en : imports[r])
+          for (int k = 0; k < en.size; ++k)
+            dm.part.import_indices.push_back(uint32_t(en.base - my_begin + k));
+        dm.part.import_offsets.push_back(uint32_t(dm.part.import_indices.size()));
+      }
+
+    const auto to_local = [&](int64_t base) -> uint32_t {
+      if (base >= my_begin && base < my_end)
+        return uint32_t(base - my_begin);
+      const auto it = std::lower_bound(ghosts.begin(), ghosts.end(), Ent{base, 0});
+      return dm.part.n_owned + ghost_off[it - ghosts.begin()];
+    };
+    dm.eval_table.resize(g_eval.size());
+    dm.own_table.resize(g_own.size());
+    for (size_t k = 0; k < g_eval.size(); ++k)
+      {
+        dm.eval_table[k] = to_local(g_eval[k]) | (f_eval[k] ? FLAG_BIT : 0u);
+        dm.own_table[k]  = to_local(g_own[k]) | (f_own[k] ? FLAG_BIT : 0u);
+      }
+    for (const Ent &en : constrained_ents)
+      for (int k = 0; k < en.size; ++k)
+        dm.constrained.push_back(uint32_t(en.base - my_begin + k));
+    return dm;
+  }
+
+  void DoFMap::expand(const std::vector<uint32_t> &table, std::vector<uint32_t> &out) const
+  {
+    const int p = degree, n = p + 1, n3 = n * n * n;
+    out.resize(size_t(n_cells) * n3);
+    std::vector<int> ent(n3), off(n3);
+    for (int k = 0; k < n; ++k)
+      for (int j = 0; j < n; ++j)
+        for (int i = 0; i < n; ++i)
+          node_entity(p, i, j, k, ent[(k * n + j) * n + i], off[(k * n + j) * n + i]);
+    for (int64_t c = 0; c < n_cells; ++c)
+      for (int q = 0; q < n3; ++q)
+        {
+          const uint32_t t         = table[c * 27 + ent[q]];
+          out[size_t(c) * n3 + q] = ((t & INDEX_MASK) + uint32_t(off[q])) | (t & FLAG_BIT);
+        }
+  }
+
+  TransferMap TransferMap::build(const Mesh &mesh_fine, const DoFMap &df, const Mesh &mesh_coarse, const DoFMap &dc)
+  {
+    if (df.n_ranks != 1 || dc.n_ranks != 1)
+      throw std::runtime_error("TransferMap: multi-rank transfer maps are built by the distributed path");
+    TransferMap tm;
+    tm.degree_fine    = df.degree;
+    tm.degree_coarse  = dc.degree;
+    tm.n_coarse_cells = dc.n_cells;
+    tm.fine_first.resize(dc.n_cells);
+    tm.n_children.resize(dc.n_cells);
+    int64_t f = 0;
+    for (int64_t c = 0; c < dc.n_cells; ++c)
+      {
+        const Cell &cc = mesh_coarse.cells[c];
+        if (f >= df.n_cells)
+          throw std::runtime_error("TransferMap: fine mesh exhausted");
+        const Cell &fc = mesh_fine.cells[f];
+        if (fc.level == cc.level && fc.x == cc.x && fc.y == cc.y && fc.z == cc.z)
+          {
+            tm.fine_first[c] = uint32_t(f);
+            tm.n_children[c] = 1;
+            f += 1;
+          }
+        else
+          {
+            for (unsigned ch = 0; ch < 8; ++ch)
+              {
+                if (f + ch >= df.n_cells)
+                  throw std::runtime_error("TransferMap: fine mesh is not a one-level refinement of the coarse mesh");
+                const Cell &s = mesh_fine.cells[f + ch];
+                if (!(s.level == cc.level + 1 && s.x == 2 * cc.x + (ch & 1) && s.y == 2 * cc.y + ((ch >> 1) & 1) &&
+                      s.z == 2 * cc.z + ((ch >> 2) & 1)))
+                  throw std::runtime_error("TransferMap: fine mesh is not a one-level refinement of the coarse mesh");
+              }
+            tm.fine_first[c] = uint32_t(f);
+            tm.n_children[c] = 8;
+            f += 8;
+          }
+      }
+    if (f != df.n_cells)
+      throw std::runtime_error("TransferMap: fine cells left over");
+
+    // valence of every fine entity = number of coarse cells whose fine patch contains it
+    int esize[27];
+    for (int e = 0; e < 27; ++e)
+      esize[e] = ipow(df.degree - 1, entity_dim(e));
+    std::vector<uint8_t>  valence(size_t(df.part.n_owned) + df.part.n_ghost + 1, 0);
+    std::vector<uint32_t> patch;
+    for (int64_t c = 0; c < dc.n_cells; ++c)
+      {
+        patch.clear();
+        for (unsigned ch = 0; ch < tm.n_children[c]; ++ch)
+          for (int e = 0; e < 27; ++e)
+            if (esize[e] > 0)
+              patch.push_back(df.own_table[(size_t(tm.fine_first[c]) + ch) * 27 + e] & INDEX_MASK);
+        std::sort(patch.begin(), patch.end());
+        patch.erase(std::unique(patch.begin(), patch.end()), patch.end());
+        for (uint32_t b : patch)
+          ++valence[b];
+      }
+    tm.weight_code.assign(size_t(df.n_cells) * 27, 0);
+    for (size_t k = 0; k < tm.weight_code.size(); ++k)
+      {
+        const uint32_t t = df.own_table[k];
+        if (esize[k % 27] == 0 || (t & FLAG_BIT))
+          tm.weight_code[k] = 0;
+        else
+          tm.weight_code[k] = valence[t & INDEX_MASK];
+      }
+    return tm;
+  }
+} // namespace mgb

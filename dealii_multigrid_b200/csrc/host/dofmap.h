@@ -1,0 +1,106 @@
+// FE_Q(p) degrees of freedom on an octree mesh: the stand-in for what the reference obtains from
+// DoFHandler::distribute_dofs + AffineConstraints (Dirichlet id 0 + hanging nodes) + MatrixFree::reinit
+// (multigrid_throughput.cc:1578-1595, 2274, 2305-2316; include/operator.h:24-47).
+//
+// Numbering (documented, our own -- SURVEY.md A.2: deal.II's depends on refinement history):
+//   cells are walked in Morton order; each cell numbers its not-yet-numbered mesh entities in the
+//   order vertices(8), lines(12), quads(6), hex(1); the (p-1)^dim DoFs of an entity are consecutive,
+//   lexicographic in the entity's own axes (x fastest).  All cubes share the root orientation, so every
+//   cell sees an entity's DoFs in the same order; a cell's (p+1)^3 lexicographic DoF indices are
+//   therefore described exactly by 27 entity base offsets ("entity table", ternary index
+//   e = tx + 3 ty + 9 tz, t in {0: low, 1: interior, 2: high}).
+//
+//   `eval_table` is the table used in gather/scatter (MatrixFree's dof_indices): on a hanging face /
+//   edge the slots hold the COARSE neighbour's entities (the parent's face/edge), to be interpolated
+//   in place with the 1-D subface matrices selected by `mask` (deal.II "fast hanging-node algorithm",
+//   SURVEY.md A.3); bit 31 marks entities on the Dirichlet boundary (read as 0, never written).
+//   `own_table` holds the cell's own entities (DoFHandler::get_dof_indices); bit 31 marks entities
+//   whose DoFs are constrained (Dirichlet or hanging).
+//
+// Parallel layout: rank r owns a Morton-contiguous chunk of cells; an entity belongs to the rank of
+// the first cell (Morton order) touching it, which makes every rank's owned DoFs one contiguous global
+// range; local vectors are [owned | ghosts sorted by global index] (LinearAlgebra::distributed::Vector,
+// SURVEY.md A.9).
+#pragma once
+#include "octree.h"
+
+#include <cstdint>
+#include <vector>
+
+namespace mgb
+{
+  constexpr uint32_t FLAG_BIT  = 0x80000000u;
+  constexpr uint32_t INDEX_MASK = 0x7fffffffu;
+
+  // mask bits (same meaning as MatrixFree's hanging_node_constraint_masks)
+  enum : uint16_t
+  {
+    MASK_SUBCELL_X = 1,
+    MASK_SUBCELL_Y = 2,
+    MASK_SUBCELL_Z = 4,
+    MASK_FACE_X    = 8,
+    MASK_FACE_Y    = 16,
+    MASK_FACE_Z    = 32,
+    MASK_EDGE_X    = 64,
+    MASK_EDGE_Y    = 128,
+    MASK_EDGE_Z    = 256
+  };
+
+  struct Partitioner
+  {
+    int64_t               n_global = 0;
+    int64_t               owned_begin = 0; // global index of first owned DoF
+    uint32_t              n_owned = 0, n_ghost = 0;
+    std::vector<int64_t>  ghost_global;    // n_ghost, ascending
+    std::vector<int>      ghost_ranks;     // owners of ghost groups, ascending
+    std::vector<uint32_t> ghost_offsets;   // ghost_ranks.size()+1, offsets into the ghost tail
+    std::vector<int>      import_ranks;    // ranks that need owned entries of ours
+    std::vector<uint32_t> import_offsets;  // import_ranks.size()+1
+    std::vector<uint32_t> import_indices;  // owned local indices to send, grouped by import_ranks
+  };
+
+  struct DoFMap
+  {
+    int     degree  = 1;
+    int     n_ranks = 1, rank = 0;
+    int64_t n_cells_global = 0;
+    int64_t cell_begin     = 0; // first local cell in the global Morton order
+    int64_t n_cells        = 0; // local cells
+    int     mesh_max_level = 0;
+
+    std::vector<uint32_t> eval_table; // n_cells*27
+    std::vector<uint32_t> own_table;  // n_cells*27
+    std::vector<uint16_t> mask;       // n_cells
+    std::vector<uint8_t>  cell_level; // n_cells
+    std::vector<uint32_t> cell_xyz;   // n_cells*3, integer coordinates at the cell's level
+    std::vector<uint32_t> constrained; // owned local indices, ascending (Dirichlet + hanging)
+    int64_t               n_cells_hanging = 0; // local cells with a face/edge constraint
+    Partitioner           part;
+
+    // build the active-mesh DoFs of `mesh` for FE_Q(degree), partitioned over n_ranks (equal cell counts)
+    static DoFMap build(const Mesh &mesh, int degree, int n_ranks = 1, int rank = 0);
+
+    // expand to the lexicographic (p+1)^3 index map (what MatrixFree stores); flags kept in bit 31
+    void expand(const std::vector<uint32_t> &table, std::vector<uint32_t> &out) const;
+  };
+
+  // ternary entity index helpers
+  inline int entity_dim(int e) { return (e % 3 == 1) + ((e / 3) % 3 == 1) + (e / 9 == 1); }
+  extern const int ENTITY_ORDER[27]; // vertices, lines, quads, hex
+  // local offset of node (i,j,k) inside its entity and the entity index
+  void node_entity(int p, int i, int j, int k, int &e, int &offset);
+
+  // Two-level transfer description between two DoF maps (geometric: fine mesh = coarse mesh with some
+  // cells replaced by their 8 children; polynomial: same mesh) -- MGTwoLevelTransfer::reinit,
+  // multigrid_throughput.cc:1600-1604; SURVEY.md A.7.
+  struct TransferMap
+  {
+    int                   degree_fine = 1, degree_coarse = 1;
+    int64_t               n_coarse_cells = 0;
+    std::vector<uint32_t> fine_first;  // per coarse cell: first fine cell (Morton-contiguous children)
+    std::vector<uint8_t>  n_children;  // per coarse cell: 1 (same cell) or 8
+    std::vector<uint8_t>  weight_code; // n_fine_cells*27: 0 -> weight 0 (constrained fine entity), v -> 1/v
+    static TransferMap build(const Mesh &mesh_fine, const DoFMap &dofs_fine, const Mesh &mesh_coarse,
+                             const DoFMap &dofs_coarse);
+  };
+} // namespace mgb

@@ -1,0 +1,39 @@
+// 1-D finite element data for FE_Q(p) with QGauss(p+1), the pair the reference
+// instantiates (multigrid_throughput.cc:1560-1562, 2269-2270).
+//
+// Everything is defined on the unit interval [0,1]:
+//   nodes   : Gauss-Lobatto support points of FE_Q(p)            (n = p+1)
+//   M, K    : 1-D mass / stiffness matrices integrated with Gauss(n) -- the
+//             tensor factors of the Cartesian cell matrix
+//             A_e = h^(d-2) (K x M x M + M x K x M + M x M x K)
+//             (same operator as operator.h:461-472 on a cube)
+//   S[0|1]  : subface interpolation (parent 1-D basis at the child's nodes)
+//             used by the hanging-node gather/scatter
+//   Ph      : h-embedding (2p+1) x (p+1), parent basis at the union of the two
+//             children's nodes (MGTwoLevelTransfer)
+#pragma once
+#include <vector>
+
+namespace mgb
+{
+  std::vector<double> gauss_lobatto_nodes(int n); // on [0,1]
+  void                gauss_rule(int n, std::vector<double> &x, std::vector<double> &w); // on [0,1]
+
+  // value of the j-th Lagrange polynomial on `nodes` at x
+  double lagrange_value(const std::vector<double> &nodes, int j, double x);
+  double lagrange_derivative(const std::vector<double> &nodes, int j, double x);
+
+  struct FE1D
+  {
+    int                 degree = 0;
+    int                 n      = 0;  // degree+1
+    std::vector<double> nodes;       // n
+    std::vector<double> M, K;        // n*n row-major
+    std::vector<double> S[2];        // n*n row-major, S[c][i*n+j] = l_j(c/2 + x_i/2)
+    std::vector<double> Ph;          // (2p+1)*n row-major
+    explicit FE1D(int degree);
+  };
+
+  // p-embedding: (pf+1) x (pc+1), coarse basis at the fine nodes
+  std::vector<double> p_embedding(int degree_fine, int degree_coarse);
+} // namespace mgb

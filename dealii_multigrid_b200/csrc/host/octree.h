@@ -1,0 +1,78 @@
+// Octree mesh on the single root cube [-1,1]^3 -- the stand-in for the
+// p4est-backed parallel::distributed::Triangulation the reference builds in
+// multigrid_throughput.cc:2041-2062.  Every geometry of the reference is
+// hyper_cube(-1,1) + isotropic refinement (include/grid_generator.h:1-141), so
+// a linear octree with 2:1 balance over faces, edges and corners (what p4est
+// enforces) represents all of them.
+//
+// Leaves are stored in Morton (z-) order, child c at offsets
+// (c&1, (c>>1)&1, (c>>2)&1) -- the deal.II / p4est child order.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace mgb
+{
+  // open-addressing hash map uint64 -> int64 (keys never removed)
+  class FlatMap
+  {
+  public:
+    void    reserve(size_t n);
+    void    insert(uint64_t key, int64_t value);
+    int64_t find(uint64_t key) const; // -1 if absent
+    size_t  size() const { return n_; }
+    void    clear();
+
+  private:
+    static uint64_t      hash(uint64_t k);
+    void                 grow();
+    std::vector<uint64_t> keys_;
+    std::vector<int64_t>  vals_;
+    size_t                n_    = 0;
+    size_t                mask_ = 0;
+  };
+
+  struct Cell
+  {
+    uint32_t x, y, z; // integer coordinates at the cell's own level
+    uint8_t  level;
+  };
+
+  class Mesh
+  {
+  public:
+    std::vector<Cell> cells; // Morton-ordered leaves
+
+    static Mesh create(const std::string &geometry, unsigned n_ref_global, unsigned n_ref_local);
+
+    int  max_level() const;
+    int  n_global_levels() const { return max_level() + 1; }
+    bool uniform() const;
+
+    // refine flagged leaves, then restore 2:1 balance (faces+edges+corners)
+    void refine(const std::vector<char> &flags);
+    void refine_global(unsigned times = 1);
+    // one global coarsening step: every complete family of 8 leaves -> parent, then balance
+    // (MGTransferGlobalCoarseningTools::create_geometric_coarsening_sequence, ref :2219-2224)
+    Mesh coarsen_global() const;
+
+    void rebuild_index();
+    // leaf index of the cell (level,x,y,z); -1 if that cell is not a leaf
+    int64_t leaf(int level, uint32_t x, uint32_t y, uint32_t z) const;
+    // relation of the region (level,x,y,z) to the leaves:
+    //   returns leaf index and sets rel = 0 (is a leaf), -k (contained in a leaf k levels coarser),
+    //   +1 (subdivided further; returns -1)
+    int64_t locate(int level, uint32_t x, uint32_t y, uint32_t z, int &rel) const;
+
+    static uint64_t key(int level, uint32_t x, uint32_t y, uint32_t z)
+    {
+      return (uint64_t(level) << 57) | (uint64_t(x) << 38) | (uint64_t(y) << 19) | uint64_t(z);
+    }
+    void center(const Cell &c, double ctr[3]) const;
+
+  private:
+    void    balance();
+    FlatMap index_;
+  };
+} // namespace mgb

@@ -1,0 +1,627 @@
+#include "problem.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <sstream>
+
+namespace mgb
+{
+  // ------------------------------------------------------------------------------------------ JSON (flat object)
+  namespace
+  {
+    std::map<std::string, std::string> parse_flat_json(const std::string &s)
+    {
+      std::map<std::string, std::string> out;
+      size_t                             i = 0;
+      const auto skip_ws = [&]() {
+        while (i < s.size() && (s[i] == ' ' || s[i] == '\n' || s[i] == '\t' || s[i] == '\r' || s[i] == ','))
+          ++i;
+      };
+      const auto read_string = [&]() {
+        std::string r;
+        ++i; // opening quote
+        while (i < s.size() && s[i] != '"')
+          {
+            if (s[i] == '\\' && i + 1 < s.size())
+              ++i;
+            r += s[i++];
+          }
+        ++i;
+        return r;
+      };
+      skip_ws();
+      if (i >= s.size() || s[i] != '{')
+        throw std::runtime_error("JSON: expected '{'");
+      ++i;
+      while (true)
+        {
+          skip_ws();
+          if (i >= s.size())
+            throw std::runtime_error("JSON: unexpected end");
+          if (s[i] == '}')
+            break;
+          if (s[i] != '"')
+            throw std::runtime_error("JSON: expected key");
+          const std::string key = read_string();
+          skip_ws();
+          if (i >= s.size() || s[i] != ':')
+            throw std::runtime_error("JSON: expected ':'");
+          ++i;
+          skip_ws();
+          std::string val;
+          if (s[i] == '"')
+            val = read_string();
+          else if (s[i] == '{' || s[i] == '[')
+            throw std::runtime_error("JSON: nested values are not part of the input schema");
+          else
+            while (i < s.size() && s[i] != ',' && s[i] != '}' && s[i] != '\n' && s[i] != ' ')
+              val += s[i++];
+          out[key] = val;
+        }
+      return out;
+    }
+    bool to_bool(const std::string &v) { return v == "true" || v == "True" || v == "1" || v == "yes"; }
+  } // namespace
+
+  void RunParameters::parse_json(const std::string &text)
+  {
+    const auto kv  = parse_flat_json(text);
+    const auto has = [&](const char *k) { return kv.find(k) != kv.end(); };
+    if (has("Type"))
+      type = kv.at("Type");
+    if (has("GeometryType"))
+      geometry_type = kv.at("GeometryType");
+    if (has("NRefGlobal"))
+      n_ref_global = (unsigned)std::stoul(kv.at("NRefGlobal"));
+    if (has("NRefLocal"))
+      n_ref_local = (unsigned)std::stoul(kv.at("NRefLocal"));
+    if (has("Degree"))
+      fe_degree_fine = (unsigned)std::stoul(kv.at("Degree"));
+    if (has("Paraview"))
+      paraview = to_bool(kv.at("Paraview"));
+    if (has("Verbosity"))
+      verbose = to_bool(kv.at("Verbosity"));
+    if (has("Partitioner"))
+      p = (unsigned)std::stoul(kv.at("Partitioner"));
+    if (has("PartitionerName"))
+      policy_name = kv.at("PartitionerName");
+    if (has("MinLevel"))
+      min_level = std::stoi(kv.at("MinLevel"));
+    if (has("MinNCells"))
+      min_n_cells = std::stoi(kv.at("MinNCells"));
+    if (has("CoarseGridSolverType"))
+      mg_data.coarse_solver.type = kv.at("CoarseGridSolverType");
+    if (has("SmootherDegree"))
+      mg_data.smoother.degree = (unsigned)std::stoul(kv.at("SmootherDegree"));
+    if (has("CoarseSolverNCycles"))
+      mg_data.coarse_solver.n_cycles = (unsigned)std::stoul(kv.at("CoarseSolverNCycles"));
+    if (has("RelativeTolerance"))
+      mg_data.cg_normal.reltol = std::stod(kv.at("RelativeTolerance"));
+    if (has("MGNumberType"))
+      mg_number_type = kv.at("MGNumberType");
+    if (has("SimulationType"))
+      simulation_type = kv.at("SimulationType");
+  }
+
+  // ------------------------------------------------------------------------------------------ host cell helpers
+  namespace
+  {
+    struct HostCell
+    {
+      int                 p, n;
+      FE1D                fe;
+      std::vector<double> B, W, xq; // B[q*n+i] = l_i(x_q)
+      explicit HostCell(int degree)
+        : p(degree)
+        , n(degree + 1)
+        , fe(degree)
+      {
+        gauss_rule(n, xq, W);
+        B.resize(n * n);
+        for (int q = 0; q < n; ++q)
+          for (int i = 0; i < n; ++i)
+            B[q * n + i] = lagrange_value(fe.nodes, i, xq[q]);
+      }
+      static bool replaced(int e, unsigned mask)
+      {
+        const int t[3] = {e % 3, (e / 3) % 3, e / 9};
+        const int s[3] = {int(mask & 1), int((mask >> 1) & 1), int((mask >> 2) & 1)};
+        for (int d = 0; d < 3; ++d)
+          {
+            if (((mask >> (3 + d)) & 1) && t[d] == 2 * s[d])
+              return true;
+            const int a = (d + 1) % 3, b = (d + 2) % 3;
+            if (((mask >> (6 + d)) & 1) && t[a] == 2 * s[a] && t[b] == 2 * s[b])
+              return true;
+          }
+        return false;
+      }
+      void hn_sweeps(std::vector<double> &u, unsigned mask, bool transpose) const
+      {
+        const int n2 = n * n;
+        for (int dd = 0; dd < 3; ++dd)
+          {
+            const int  d  = transpose ? 2 - dd : dd;
+            const int  da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
+            const int  sa = (mask >> da) & 1, sb = (mask >> db) & 1, sd = (mask >> d) & 1;
+            const bool fa = (mask >> (3 + da)) & 1, fb = (mask >> (3 + db)) & 1, ed = (mask >> (6 + d)) & 1;
+            const std::vector<double> &S = fe.S[sd];
+            for (int b = 0; b < n; ++b)
+              for (int a = 0; a < n; ++a)
+                {
+                  const bool on_a = (a == sa * p), on_b = (b == sb * p);
+                  if (!((fa && on_a) || (fb && on_b) || (ed && on_a && on_b)))
+                    continue;
+                  const int           base   = d == 0 ? (b * n + a) * n : (d == 1 ? b * n2 + a : b * n + a);
+                  const int           stride = d == 0 ? 1 : (d == 1 ? n : n2);
+                  std::vector<double> v(n), r(n, 0.0);
+                  for (int i = 0; i < n; ++i)
+                    v[i] = u[base + i * stride];
+                  for (int i = 0; i < n; ++i)
+                    for (int j = 0; j < n; ++j)
+                      r[i] += (transpose ? S[j * n + i] : S[i * n + j]) * v[j];
+                  for (int i = 0; i < n; ++i)
+                    u[base + i * stride] = r[i];
+                }
+          }
+      }
+      // r = h (K x M x M + M x K x M + M x M x K) u
+      void laplace(const std::vector<double> &u, std::vector<double> &r, double h) const
+      {
+        const int n3 = n * n * n;
+        r.assign(n3, 0.0);
+        std::vector<double>        t1(n3), t2(n3);
+        const std::vector<double> *mats[2] = {&fe.M, &fe.K};
+        for (int term = 0; term < 3; ++term)
+          {
+            const std::vector<double> &Ax = *mats[term == 0], &Ay = *mats[term == 1], &Az = *mats[term == 2];
+            for (int k = 0; k < n; ++k)
+              for (int j = 0; j < n; ++j)
+                for (int i = 0; i < n; ++i)
+                  {
+                    double s = 0;
+                    for (int l = 0; l < n; ++l)
+                      s += Ax[i * n + l] * u[(k * n + j) * n + l];
+                    t1[(k * n + j) * n + i] = s;
+                  }
+            for (int k = 0; k < n; ++k)
+              for (int j = 0; j < n; ++j)
+                for (int i = 0; i < n; ++i)
+                  {
+                    double s = 0;
+                    for (int l = 0; l < n; ++l)
+                      s += Ay[j * n + l] * t1[(k * n + l) * n + i];
+                    t2[(k * n + j) * n + i] = s;
+                  }
+            for (int k = 0; k < n; ++k)
+              for (int j = 0; j < n; ++j)
+                for (int i = 0; i < n; ++i)
+                  {
+                    double s = 0;
+                    for (int l = 0; l < n; ++l)
+                      s += Az[k * n + l] * t2[(l * n + j) * n + i];
+                    r[(k * n + j) * n + i] += h * s;
+                  }
+          }
+      }
+    };
+
+    double gaussian_solution(const double x[3])
+    {
+      const double c[3] = {-0.5, -0.5, -0.5}, w = 0.1, pi = 3.14159265358979323846;
+      double       r2 = 0;
+      for (int d = 0; d < 3; ++d)
+        r2 += (x[d] - c[d]) * (x[d] - c[d]);
+      const double nrm = std::sqrt(2.0 * pi) * w;
+      return std::exp(-r2 / (w * w)) / (nrm * nrm * nrm);
+    }
+    double gaussian_rhs(const double x[3])
+    {
+      const double c[3] = {-0.5, -0.5, -0.5}, w = 0.1, pi = 3.14159265358979323846, coef = 1.0;
+      double       r2 = 0;
+      for (int d = 0; d < 3; ++d)
+        r2 += (x[d] - c[d]) * (x[d] - c[d]);
+      const double nrm = std::sqrt(2.0 * pi) * w;
+      return ((2 * 3 * coef - 4 * coef * r2 / (w * w)) / (w * w) * std::exp(-r2 / (w * w))) / (nrm * nrm * nrm);
+    }
+  } // namespace
+
+  void assemble_rhs(const Mesh &, const DoFMap &dm, const std::string &simulation_type, std::vector<double> &b)
+  {
+    const bool gaussian = simulation_type == "Gaussian";
+    if (!gaussian && simulation_type != "Constant")
+      throw std::runtime_error("unknown SimulationType '" + simulation_type + "'");
+    const HostCell hc(dm.degree);
+    const int      n = hc.n, n3 = n * n * n, p = hc.p;
+    b.assign(size_t(dm.part.n_owned) + dm.part.n_ghost, 0.0);
+    std::vector<int> ent(n3), off(n3);
+    for (int k = 0; k < n; ++k)
+      for (int j = 0; j < n; ++j)
+        for (int i = 0; i < n; ++i)
+          node_entity(p, i, j, k, ent[(k * n + j) * n + i], off[(k * n + j) * n + i]);
+    std::vector<double> fq(n3), t1(n3), t2(n3), r(n3), xd(n3), lift(n3);
+    for (long long c = 0; c < dm.n_cells; ++c)
+      {
+        const double   h    = 2.0 / double(1u << dm.cell_level[c]);
+        const double   o[3] = {-1.0 + h * dm.cell_xyz[3 * c], -1.0 + h * dm.cell_xyz[3 * c + 1], -1.0 + h * dm.cell_xyz[3 * c + 2]};
+        const unsigned mask = dm.mask[c];
+        // f at the quadrature points times JxW
+        for (int k = 0; k < n; ++k)
+          for (int j = 0; j < n; ++j)
+            for (int i = 0; i < n; ++i)
+              {
+                const double x[3] = {o[0] + h * hc.xq[i], o[1] + h * hc.xq[j], o[2] + h * hc.xq[k]};
+                const double f    = gaussian ? gaussian_rhs(x) : 1.0;
+                fq[(k * n + j) * n + i] = f * hc.W[i] * hc.W[j] * hc.W[k] * h * h * h;
+              }
+        // integrate: r = (B^T x B^T x B^T) fq
+        for (int k = 0; k < n; ++k)
+          for (int j = 0; j < n; ++j)
+            for (int i = 0; i < n; ++i)
+              {
+                double s = 0;
+                for (int q = 0; q < n; ++q)
+                  s += hc.B[q * n + i] * fq[(k * n + j) * n + q];
+                t1[(k * n + j) * n + i] = s;
+              }
+        for (int k = 0; k < n; ++k)
+          for (int j = 0; j < n; ++j)
+            for (int i = 0; i < n; ++i)
+              {
+                double s = 0;
+                for (int q = 0; q < n; ++q)
+                  s += hc.B[q * n + j] * t1[(k * n + q) * n + i];
+                t2[(k * n + j) * n + i] = s;
+              }
+        for (int k = 0; k < n; ++k)
+          for (int j = 0; j < n; ++j)
+            for (int i = 0; i < n; ++i)
+              {
+                double s = 0;
+                for (int q = 0; q < n; ++q)
+                  s += hc.B[q * n + k] * t2[(q * n + j) * n + i];
+                r[(k * n + j) * n + i] = s;
+              }
+        // inhomogeneous Dirichlet lift: r -= A_hn x_D (include/operator.h:415-446)
+        if (gaussian)
+          {
+            bool touches = false;
+            for (int e = 0; e < 27; ++e)
+              touches |= (dm.eval_table[c * 27 + e] & FLAG_BIT) != 0;
+            if (touches)
+              {
+                const double hp    = 2.0 * h;
+                const double op[3] = {-1.0 + hp * (dm.cell_xyz[3 * c] >> 1), -1.0 + hp * (dm.cell_xyz[3 * c + 1] >> 1),
+                                      -1.0 + hp * (dm.cell_xyz[3 * c + 2] >> 1)};
+                for (int q = 0; q < n3; ++q)
+                  {
+                    xd[q] = 0.0;
+                    if (dm.eval_table[c * 27 + ent[q]] & FLAG_BIT)
+                      {
+                        const int  i = q % n, j = (q / n) % n, k = q / (n * n);
+                        const bool rep = HostCell::replaced(ent[q], mask);
+                        const double x[3] = {(rep ? op[0] : o[0]) + (rep ? hp : h) * hc.fe.nodes[i],
+                                             (rep ? op[1] : o[1]) + (rep ? hp : h) * hc.fe.nodes[j],
+                                             (rep ? op[2] : o[2]) + (rep ? hp : h) * hc.fe.nodes[k]};
+                        xd[q] = gaussian_solution(x);
+                      }
+                  }
+                if (mask >> 3)
+                  hc.hn_sweeps(xd, mask, false);
+                hc.laplace(xd, lift, h);
+                for (int q = 0; q < n3; ++q)
+                  r[q] -= lift[q];
+              }
+          }
+        if (mask >> 3)
+          hc.hn_sweeps(r, mask, true);
+        for (int q = 0; q < n3; ++q)
+          {
+            const uint32_t t = dm.eval_table[c * 27 + ent[q]];
+            if (!(t & FLAG_BIT))
+              b[(t & INDEX_MASK) + off[q]] += r[q];
+          }
+      }
+  }
+
+  // ------------------------------------------------------------------------------------------ problem
+  namespace
+  {
+    std::vector<unsigned> polynomial_coarsening_sequence_bisect(unsigned degree)
+    {
+      // MGTransferGlobalCoarseningTools::create_polynomial_coarsening_sequence(degree, bisect), ref :1506-1510
+      std::vector<unsigned> d{degree};
+      while (d.back() > 1)
+        d.push_back(std::max(d.back() / 2, 1u));
+      std::reverse(d.begin(), d.end());
+      return d;
+    }
+
+    OperatorSetup setup_from_dofmap(const DoFMap &dm)
+    {
+      OperatorSetup s;
+      s.degree        = dm.degree;
+      s.n_cells       = dm.n_cells;
+      s.entity_table  = dm.eval_table.data();
+      s.mask          = dm.mask.data();
+      s.cell_level    = dm.cell_level.data();
+      s.root_length   = 2.0;
+      s.constrained   = dm.constrained.data();
+      s.n_constrained = (uint32_t)dm.constrained.size();
+      s.n_dofs_global = dm.part.n_global;
+      s.partitioner   = &dm.part;
+      return s;
+    }
+
+    template <typename LT> class Problem : public ProblemBase
+    {
+    public:
+      struct Level
+      {
+        int                             mesh_index = 0;
+        int                             degree     = 1;
+        std::unique_ptr<DoFMap>         dofs;
+        std::unique_ptr<OperatorT<LT>>  op;
+        std::unique_ptr<ChebyshevT<LT>> smoother;
+      };
+      std::vector<Mesh>                  meshes; // coarse -> fine
+      std::vector<Level>                 levels;
+      std::vector<TransferMap>           tmaps;
+      GCTransferT<LT>                    transfer;
+      std::unique_ptr<OperatorT<double>> fine_op_own;
+      OperatorT<double>                 *fine_op = nullptr;
+      DVec<double>                       rhs_, solution_;
+      MultigridT<LT>                     mg;
+      PreconditionMGT<LT>                precond;
+      std::unique_ptr<ChebyshevT<LT>>    coarse_cheb;
+      std::unique_ptr<CoarseCGT<LT>>     coarse;
+      StageTimers                        timers;
+      CGWork<double>                     cgw;
+      long long                          n_cells_hn = 0, n_cells_n = 0;
+      int                                n_ranks = 1, rank = 0;
+
+      Problem(const RunParameters &prm_, int n_ranks_, int rank_)
+        : n_ranks(n_ranks_)
+        , rank(rank_)
+      {
+        prm = prm_;
+        build();
+      }
+
+      void build()
+      {
+        const std::string &type = prm.type;
+        if (type == "AMG" || type == "AMGPETSc")
+          throw std::runtime_error("Type '" + type + "' (Trilinos ML / hypre BoomerAMG) is out of scope of the B200 hot path");
+        if (type == "HMG-local" || type == "HPMG-local")
+          throw std::runtime_error("Type '" + type + "': local smoothing is not available in this build yet");
+        if (type != "PMG" && type != "HMG-global" && type != "HPMG")
+          throw std::runtime_error("unknown Type '" + type + "'");
+        const std::string &cs = prm.mg_data.coarse_solver.type;
+        if (cs != "cg" && cs != "cg_with_chebyshev")
+          throw std::runtime_error("CoarseGridSolverType '" + cs +
+                                   "' needs Trilinos/PETSc AMG (out of scope); use \"cg\" or \"cg_with_chebyshev\"");
+
+        // geometric coarsening sequence (ref :2219-2224), then MinLevel / MinNCells trimming (ref :2227-2260)
+        {
+          std::vector<Mesh> seq;
+          seq.push_back(Mesh::create(prm.geometry_type, prm.n_ref_global, prm.n_ref_local));
+          while (seq.back().n_global_levels() > 1)
+            seq.push_back(seq.back().coarsen_global());
+          std::reverse(seq.begin(), seq.end());
+          size_t first = 0;
+          if (seq.size() > 1)
+            for (first = 0; first + 1 < seq.size(); ++first)
+              {
+                if (prm.min_level != -1)
+                  {
+                    if (prm.min_level <= seq[first].n_global_levels())
+                      break;
+                  }
+                else if (prm.min_n_cells != -1)
+                  {
+                    if ((long long)seq[first].cells.size() >= prm.min_n_cells)
+                      break;
+                  }
+                else
+                  break;
+              }
+          for (size_t i = first; i < seq.size(); ++i)
+            meshes.push_back(std::move(seq[i]));
+          for (auto &m : meshes)
+            m.rebuild_index();
+        }
+        const auto     level_degrees = polynomial_coarsening_sequence_bisect(prm.fe_degree_fine);
+        const unsigned n_trias       = (unsigned)meshes.size();
+        unsigned       max_level     = 0;
+        if (type == "PMG")
+          max_level = (unsigned)level_degrees.size() - 1;
+        else if (type == "HMG-global")
+          max_level = n_trias - 1;
+        else
+          max_level = (unsigned)level_degrees.size() + n_trias - 2;
+
+        levels.resize(max_level + 1);
+        for (unsigned l = 0; l <= max_level; ++l)
+          {
+            Level &L = levels[l];
+            if (type == "PMG")
+              {
+                L.degree     = level_degrees[l];
+                L.mesh_index = n_trias - 1;
+              }
+            else if (type == "HMG-global")
+              {
+                L.degree     = level_degrees.back();
+                L.mesh_index = l;
+              }
+            else
+              {
+                L.degree     = level_degrees[std::max<int>(0, int(l) - int(n_trias) + 1)];
+                L.mesh_index = std::min(l, n_trias - 1);
+              }
+            L.dofs = std::make_unique<DoFMap>(DoFMap::build(meshes[L.mesh_index], L.degree, n_ranks, rank));
+            L.op   = std::make_unique<OperatorT<LT>>(setup_from_dofmap(*L.dofs));
+          }
+        // two-level transfers (ref :1600-1604)
+        transfer.min_level = 0;
+        transfer.transfers.resize(max_level + 1);
+        transfer.operators.resize(max_level + 1);
+        tmaps.resize(max_level + 1);
+        for (unsigned l = 0; l <= max_level; ++l)
+          transfer.operators[l] = levels[l].op.get();
+        for (unsigned l = 0; l < max_level; ++l)
+          {
+            tmaps[l + 1] = TransferMap::build(meshes[levels[l + 1].mesh_index], *levels[l + 1].dofs, meshes[levels[l].mesh_index],
+                                              *levels[l].dofs);
+            transfer.transfers[l + 1] =
+              std::make_unique<TwoLevelTransferT<LT>>(*levels[l + 1].dofs, *levels[l].dofs, tmaps[l + 1], *levels[l + 1].op, *levels[l].op);
+          }
+        // smoothers (ref :866-883)
+        for (unsigned l = 0; l <= max_level; ++l)
+          levels[l].smoother = std::make_unique<ChebyshevT<LT>>(*levels[l].op, (int)prm.mg_data.smoother.degree,
+                                                                prm.mg_data.smoother.smoothing_range,
+                                                                prm.mg_data.smoother.eig_cg_n_iterations);
+        // coarse solver (ref :887-944)
+        if (cs == "cg_with_chebyshev")
+          coarse_cheb = std::make_unique<ChebyshevT<LT>>(*levels[0].op, (int)prm.mg_data.smoother.degree,
+                                                         prm.mg_data.smoother.smoothing_range, prm.mg_data.smoother.eig_cg_n_iterations);
+        coarse = std::make_unique<CoarseCGT<LT>>(*levels[0].op, coarse_cheb.get(), prm.mg_data.coarse_solver.maxiter,
+                                                 prm.mg_data.coarse_solver.abstol, prm.mg_data.coarse_solver.reltol);
+        // multigrid + preconditioner (ref :1117-1133); GC transfers never set edge_in (ref :1126-1130)
+        mg.min_level = 0;
+        mg.max_level = max_level;
+        for (unsigned l = 0; l <= max_level; ++l)
+          {
+            mg.matrices.push_back(levels[l].op.get());
+            mg.smoothers.push_back(levels[l].smoother.get());
+          }
+        mg.transfer      = &transfer;
+        mg.coarse        = coarse.get();
+        mg.edge_in       = false;
+        mg.timers        = &timers;
+        precond.mg       = &mg;
+        precond.transfer = &transfer;
+        precond.timers   = &timers;
+
+        // outer FP64 operator on the finest level (ref :2262-2316) and right-hand side (ref :2324)
+        const DoFMap &fd = *levels.back().dofs;
+        if constexpr (std::is_same<LT, double>::value)
+          fine_op = levels.back().op.get();
+        else
+          {
+            fine_op_own = std::make_unique<OperatorT<double>>(setup_from_dofmap(fd));
+            fine_op     = fine_op_own.get();
+          }
+        fine_op->initialize_dof_vector(rhs_);
+        fine_op->initialize_dof_vector(solution_);
+        {
+          std::vector<double> b;
+          assemble_rhs(meshes.back(), fd, prm.simulation_type, b);
+          MGB_CUDA(cudaMemcpy(rhs_.data, b.data(), b.size() * sizeof(double), cudaMemcpyHostToDevice));
+          rhs_.compress_add();
+        }
+        n_cells_hn = fd.n_cells_hanging;
+        n_cells_n  = fd.n_cells - fd.n_cells_hanging;
+      }
+
+      int               n_levels() const override { return (int)levels.size(); }
+      const DoFMap     &level_dofmap(int l) const override { return *levels.at(l).dofs; }
+      const Mesh       &level_mesh(int l) const override { return meshes.at(levels.at(l).mesh_index); }
+      void             *level_operator(int l) override { return levels.at(l).op.get(); }
+      void             *level_smoother(int l) override { return levels.at(l).smoother.get(); }
+      void             *level_transfer(int l) override { return transfer.transfers.at(l).get(); }
+      OperatorT<double> &fine_operator() override { return *fine_op; }
+      DVec<double>     &rhs() override { return rhs_; }
+      DVec<double>     &solution() override { return solution_; }
+      int               level_number_type() const override { return std::is_same<LT, double>::value ? 0 : 1; }
+      void              vcycle(DVec<double> &dst, const DVec<double> &src) override { precond.vmult(dst, src); }
+
+      Result solve_once(bool with_timers) override
+      {
+        Result r;
+        timers.enabled = with_timers;
+        SolverControl ctl;
+        ctl.kind    = SolverControl::Reduction;
+        ctl.maxiter = prm.mg_data.cg_normal.maxiter;
+        ctl.abstol  = prm.mg_data.cg_normal.abstol;
+        ctl.reltol  = prm.mg_data.cg_normal.reltol;
+        const auto A = [this](DVec<double> &d, const DVec<double> &s) { fine_op->vmult(d, s); };
+        const auto P = [this](DVec<double> &d, const DVec<double> &s) { precond.vmult(d, s); };
+        solution_.zero();
+        coarse->total_iterations = 0;
+        MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+        const auto t0 = std::chrono::steady_clock::now();
+        cg_solve<double>(A, P, false, solution_, rhs_, ctl, cgw, /*x_is_zero=*/true);
+        MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+        const auto t1 = std::chrono::steady_clock::now();
+        r.time        = std::chrono::duration<double>(t1 - t0).count();
+        r.n_iterations      = (int)ctl.last_step;
+        r.initial_residual  = ctl.initial_value;
+        r.final_residual    = ctl.last_value;
+        r.coarse_iterations = coarse->total_iterations;
+        std::vector<std::array<double, N_STAGES + 2>> st(levels.size());
+        for (auto &a : st)
+          a.fill(0.0);
+        if (with_timers)
+          timers.collect(st, 0);
+        timers.enabled = false;
+        fill_result(r, st);
+        return r;
+      }
+
+      void fill_result(Result &r, const std::vector<std::array<double, N_STAGES + 2>> &st) const
+      {
+        r.degree       = (int)prm.fe_degree_fine;
+        r.n_ref_global = (int)prm.n_ref_global;
+        r.n_ref_local  = (int)prm.n_ref_local;
+        r.n_levels     = (int)levels.size();
+        r.n_cells      = levels.back().dofs->n_cells_global;
+        r.n_cells_hn   = n_cells_hn;
+        r.n_cells_n    = n_cells_n;
+        r.n_dofs       = levels.back().dofs->part.n_global;
+        r.sub_comm_size = n_ranks;
+        const int its  = std::max(1, r.n_iterations);
+        double    sum  = 0;
+        for (int s = 0; s < N_STAGES + 2; ++s)
+          {
+            double v = 0;
+            for (const auto &a : st)
+              v += a[s];
+            r.stage[s] = v / its;
+            sum += v;
+          }
+        r.time_cg    = (r.time - sum) / its;
+        r.throughput = double(r.n_dofs) * r.n_iterations / r.time;
+      }
+
+      Result run(unsigned n_repetitions) override
+      {
+        // warm-up solve (also triggers the lazy Chebyshev eigenvalue estimation), ref :1140-1147
+        solve_once(false);
+        Result best;
+        best.time = 1e300;
+        for (unsigned rep = 0; rep < n_repetitions; ++rep)
+          {
+            Result r = solve_once(true);
+            if (r.time < best.time)
+              best = r;
+          }
+        return best;
+      }
+    };
+  } // namespace
+
+  ProblemBase *create_problem(const std::string &json_text, int n_ranks, int rank)
+  {
+    RunParameters prm;
+    prm.parse_json(json_text);
+    if (prm.mg_number_type == "double")
+      return new Problem<double>(prm, n_ranks, rank);
+    else if (prm.mg_number_type == "float")
+      return new Problem<float>(prm, n_ranks, rank);
+    throw std::runtime_error("unknown MGNumberType '" + prm.mg_number_type + "'");
+  }
+} // namespace mgb

@@ -1,0 +1,623 @@
+#include "solver.h"
+
+#include "comm.h"
+
+#include <algorithm>
+#include <cstring>
+
+namespace mgb
+{
+  // ------------------------------------------------------------------------------------------ context
+  Context &ctx()
+  {
+    static Context c;
+    return c;
+  }
+
+  void Context::ensure()
+  {
+    if (red_result)
+      return;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0)
+      throw std::runtime_error("mgb200: no CUDA device available (this library has no CPU path)");
+    if (device < 0)
+      {
+        device = 0;
+        MGB_CUDA(cudaSetDevice(device));
+      }
+    MGB_CUDA(cudaMalloc((void **)&red_result, 8 * sizeof(double)));
+    MGB_CUDA(cudaMalloc((void **)&red_scratch, reduction_scratch_size() * sizeof(double)));
+    MGB_CUDA(cudaMalloc((void **)&red_ticket, sizeof(unsigned)));
+    MGB_CUDA(cudaMemset(red_ticket, 0, sizeof(unsigned)));
+    MGB_CUDA(cudaMallocHost((void **)&host_result, 8 * sizeof(double)));
+  }
+
+  DevicePartitioner::DevicePartitioner(const Partitioner &p)
+    : host(p)
+  {
+    ctx().ensure();
+    if (!p.import_indices.empty())
+      {
+        import_indices.upload(p.import_indices.data(), p.import_indices.size());
+        send_buf.alloc(std::max<size_t>(p.import_indices.size(), p.n_ghost));
+        recv_buf.alloc(std::max<size_t>(p.import_indices.size(), p.n_ghost));
+      }
+    else if (p.n_ghost)
+      {
+        send_buf.alloc(p.n_ghost);
+        recv_buf.alloc(p.n_ghost);
+      }
+  }
+
+  // ------------------------------------------------------------------------------------------ vector
+  namespace
+  {
+    double finish_reduction()
+    {
+      Context &c = ctx();
+      if (c.comm && c.comm->size() > 1)
+        c.comm->allreduce_sum(c.red_result, 1, c.stream);
+      MGB_CUDA(cudaMemcpyAsync(c.host_result, c.red_result, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+      MGB_CUDA(cudaStreamSynchronize(c.stream));
+      return c.host_result[0];
+    }
+  } // namespace
+
+  template <typename T> double DVec<T>::dot(const DVec &y) const
+  {
+    Context &c = ctx();
+    vec_dot<T>(data, y.data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    ++c.launches;
+    return finish_reduction();
+  }
+  template <typename T> double DVec<T>::add_and_dot(T a, const DVec &h)
+  {
+    Context &c = ctx();
+    vec_add_and_dot<T>(data, a, h.data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    ++c.launches;
+    return finish_reduction();
+  }
+  template <typename T> double DVec<T>::mean_value(long long n_global) const
+  {
+    Context &c = ctx();
+    vec_sum<T>(data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    ++c.launches;
+    return finish_reduction() / double(n_global);
+  }
+
+  template <typename T> void DVec<T>::update_ghost_values() const
+  {
+    if (!part || part->trivial())
+      return;
+    Context &c = ctx();
+    if (!c.comm)
+      throw std::runtime_error("update_ghost_values: vector has ghosts but no communicator is set");
+    const Partitioner &p   = part->host;
+    T                 *snd = reinterpret_cast<T *>(part->send_buf.ptr);
+    if (!p.import_indices.empty())
+      {
+        idx_gather<T>(snd, data, part->import_indices.ptr, (uint32_t)p.import_indices.size(), c.stream);
+        ++c.launches;
+      }
+    std::vector<Msg> sends, recvs;
+    for (size_t i = 0; i < p.import_ranks.size(); ++i)
+      sends.push_back(Msg{p.import_ranks[i], snd + p.import_offsets[i], size_t(p.import_offsets[i + 1] - p.import_offsets[i]) * sizeof(T)});
+    for (size_t i = 0; i < p.ghost_ranks.size(); ++i)
+      recvs.push_back(
+        Msg{p.ghost_ranks[i], data + n_owned + p.ghost_offsets[i], size_t(p.ghost_offsets[i + 1] - p.ghost_offsets[i]) * sizeof(T)});
+    c.comm->exchange(sends, recvs, c.stream);
+  }
+
+  template <typename T> void DVec<T>::compress_add()
+  {
+    if (!part || part->trivial())
+      return;
+    Context &c = ctx();
+    if (!c.comm)
+      throw std::runtime_error("compress: vector has ghosts but no communicator is set");
+    const Partitioner &p   = part->host;
+    T                 *rcv = reinterpret_cast<T *>(part->recv_buf.ptr);
+    std::vector<Msg>   sends, recvs;
+    for (size_t i = 0; i < p.ghost_ranks.size(); ++i)
+      sends.push_back(
+        Msg{p.ghost_ranks[i], data + n_owned + p.ghost_offsets[i], size_t(p.ghost_offsets[i + 1] - p.ghost_offsets[i]) * sizeof(T)});
+    for (size_t i = 0; i < p.import_ranks.size(); ++i)
+      recvs.push_back(Msg{p.import_ranks[i], rcv + p.import_offsets[i], size_t(p.import_offsets[i + 1] - p.import_offsets[i]) * sizeof(T)});
+    c.comm->exchange(sends, recvs, c.stream);
+    if (!p.import_indices.empty())
+      {
+        idx_scatter_add<T>(data, rcv, part->import_indices.ptr, (uint32_t)p.import_indices.size(), c.stream);
+        ++c.launches;
+      }
+    zero_out_ghost_values();
+  }
+
+  // ------------------------------------------------------------------------------------------ tridiagonal eigenvalues
+  namespace
+  {
+    // number of eigenvalues of the symmetric tridiagonal matrix smaller than x (Sturm count)
+    int sturm_count(const std::vector<double> &d, const std::vector<double> &e, double x)
+    {
+      int    count = 0;
+      double q     = 1.0;
+      for (size_t i = 0; i < d.size(); ++i)
+        {
+          const double e2 = (i == 0) ? 0.0 : e[i - 1] * e[i - 1];
+          q               = d[i] - x - (i == 0 ? 0.0 : e2 / q);
+          if (q == 0.0)
+            q = 1e-300;
+          if (q < 0)
+            ++count;
+        }
+      return count;
+    }
+    double kth_eigenvalue(const std::vector<double> &d, const std::vector<double> &e, int k)
+    {
+      double lo = 1e300, hi = -1e300;
+      for (size_t i = 0; i < d.size(); ++i)
+        {
+          const double r = (i > 0 ? std::fabs(e[i - 1]) : 0.0) + (i + 1 < d.size() ? std::fabs(e[i]) : 0.0);
+          lo             = std::min(lo, d[i] - r);
+          hi             = std::max(hi, d[i] + r);
+        }
+      for (int it = 0; it < 200; ++it)
+        {
+          const double mid = 0.5 * (lo + hi);
+          if (mid <= lo || mid >= hi)
+            break;
+          if (sturm_count(d, e, mid) > k)
+            hi = mid;
+          else
+            lo = mid;
+        }
+      return 0.5 * (lo + hi);
+    }
+  } // namespace
+
+  double tridiagonal_max_eigenvalue(const std::vector<double> &diag, const std::vector<double> &offdiag)
+  {
+    return kth_eigenvalue(diag, offdiag, int(diag.size()) - 1);
+  }
+  double tridiagonal_min_eigenvalue(const std::vector<double> &diag, const std::vector<double> &offdiag)
+  {
+    return kth_eigenvalue(diag, offdiag, 0);
+  }
+
+  // ------------------------------------------------------------------------------------------ operator
+  template <typename T> OperatorT<T>::OperatorT(const OperatorSetup &s)
+  {
+    ctx().ensure();
+    upload_fe_constants(s.degree);
+    etab_.upload(s.entity_table, size_t(s.n_cells) * 27);
+    level_.upload(s.cell_level, size_t(s.n_cells));
+    int any_hanging = 0;
+    if (s.mask)
+      {
+        for (long long c = 0; c < s.n_cells; ++c)
+          any_hanging |= (s.mask[c] >> 3) != 0;
+        mask_.upload(s.mask, size_t(s.n_cells));
+      }
+    cd_.degree      = s.degree;
+    cd_.n_cells     = s.n_cells;
+    cd_.etab        = etab_.ptr;
+    cd_.mask        = mask_.ptr;
+    cd_.level       = level_.ptr;
+    cd_.root_length = s.root_length;
+    cd_.any_hanging = any_hanging;
+    constrained_.upload(s.constrained, s.n_constrained);
+    edge_.upload(s.edge_constrained, s.n_edge_constrained);
+    edge_cells_.upload(s.edge_cells, s.n_edge_cells);
+    edge_src_vals_.alloc(s.n_edge_constrained);
+    has_edge_global_ = s.has_edge_constrained_global;
+    n_dofs_global_   = s.n_dofs_global;
+    if (!s.partitioner)
+      throw std::runtime_error("Operator: partitioner required");
+    part_ = std::make_shared<DevicePartitioner>(*s.partitioner);
+  }
+
+  template <typename T> void OperatorT<T>::cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_only) const
+  {
+    Context &c = ctx();
+    src.update_ghost_values();
+    if (zero_dst)
+      dst.zero();
+    if (edge_only)
+      {
+        if (edge_cells_.n)
+          cell_laplace_apply<T>(cd_, src.data, dst.data, edge_cells_.ptr, (long long)edge_cells_.n, c.stream), ++c.launches;
+      }
+    else
+      cell_laplace_apply<T>(cd_, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
+    dst.compress_add();
+    src.zero_out_ghost_values();
+  }
+
+  template <typename T> void OperatorT<T>::vmult(DVec<T> &dst, const DVec<T> &src) const
+  {
+    Context       &c  = ctx();
+    const uint32_t ne = (uint32_t)edge_.n;
+    if (ne)
+      {
+        // save values for edge constrained dofs and set them to 0 in src vector (operator.h:156-164)
+        idx_gather<T>(edge_src_vals_.ptr, src.data, edge_.ptr, ne, c.stream);
+        idx_set<T>(const_cast<T *>(src.data), T(0), edge_.ptr, ne, c.stream);
+        c.launches += 2;
+      }
+    cell_loop(dst, src, true, false);
+    if (constrained_.n)
+      idx_copy<T>(dst.data, src.data, constrained_.ptr, (uint32_t)constrained_.n, c.stream), ++c.launches;
+    if (ne)
+      {
+        idx_scatter<T>(const_cast<T *>(src.data), edge_src_vals_.ptr, edge_.ptr, ne, c.stream);
+        idx_scatter<T>(dst.data, edge_src_vals_.ptr, edge_.ptr, ne, c.stream);
+        c.launches += 2;
+      }
+  }
+
+  template <typename T> void OperatorT<T>::vmult_interface_down(DVec<T> &dst, const DVec<T> &src) const
+  {
+    Context &c = ctx();
+    cell_loop(dst, src, true, false);
+    if (constrained_.n)
+      idx_copy<T>(dst.data, src.data, constrained_.ptr, (uint32_t)constrained_.n, c.stream), ++c.launches;
+  }
+
+  template <typename T> void OperatorT<T>::vmult_interface_up(DVec<T> &dst, const DVec<T> &src) const
+  {
+    Context &c = ctx();
+    dst.zero();
+    if (!has_edge_global_)
+      return;
+    if (src_copy_.n_owned != src.n_owned || src_copy_.n_ghost != src.n_ghost)
+      src_copy_.reinit_like(src);
+    else
+      src_copy_.zero();
+    src_copy_.part = src.part;
+    if (edge_.n)
+      idx_copy<T>(src_copy_.data, src.data, edge_.ptr, (uint32_t)edge_.n, c.stream), ++c.launches;
+    cell_loop(dst, src_copy_, false, true);
+  }
+
+  template <typename T> void OperatorT<T>::compute_inverse_diagonal(DVec<T> &diag) const
+  {
+    Context &c = ctx();
+    initialize_dof_vector(diag);
+    cell_laplace_diagonal<T>(cd_, diag.data, c.stream);
+    ++c.launches;
+    diag.compress_add();
+    if (edge_.n)
+      idx_set<T>(diag.data, T(0), edge_.ptr, (uint32_t)edge_.n, c.stream), ++c.launches;
+    invert_diagonal<T>(diag.data, diag.n_owned, c.stream);
+    ++c.launches;
+  }
+
+  // ------------------------------------------------------------------------------------------ Chebyshev
+  template <typename T>
+  ChebyshevT<T>::ChebyshevT(const OperatorT<T> &op, int degree, double smoothing_range, unsigned eig_its)
+    : op_(op)
+    , degree_(degree)
+    , smoothing_range_(smoothing_range)
+    , eig_its_(eig_its)
+  {
+    op_.compute_inverse_diagonal(dinv_);
+  }
+
+  template <typename T> void ChebyshevT<T>::estimate_eigenvalues()
+  {
+    if (eig_done_)
+      return;
+    Context &c = ctx();
+    op_.initialize_dof_vector(solution_old_);
+    op_.initialize_dof_vector(temp1_);
+    op_.initialize_dof_vector(temp2_);
+    // initial guess (i + first_local_range) % 11 minus its mean (PreconditionChebyshev::set_initial_guess)
+    {
+      const Partitioner &p = op_.partitioner()->host;
+      std::vector<T>     h(p.n_owned);
+      for (uint32_t i = 0; i < p.n_owned; ++i)
+        h[i] = T((i + p.owned_begin) % 11);
+      if (p.n_owned)
+        MGB_CUDA(cudaMemcpyAsync(temp1_.data, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, c.stream));
+      MGB_CUDA(cudaStreamSynchronize(c.stream));
+      const double mean = temp1_.mean_value(op_.m());
+      temp1_.add_scalar(T(-mean));
+    }
+    SolverControl ctl;
+    ctl.kind    = SolverControl::IterationNumber;
+    ctl.maxiter = eig_its_;
+    ctl.abstol  = 1e-10;
+    std::vector<double> diag, off;
+    const auto          A = [this](DVec<T> &d, const DVec<T> &s) { op_.vmult(d, s); };
+    const auto          P = [this, &c](DVec<T> &d, const DVec<T> &s) {
+      cheb_update<T>(0, T(0), T(1), s.data, dinv_.data, nullptr, nullptr, d.data, d.n_owned, c.stream);
+      ++c.launches;
+    };
+    cg_solve<T>(A, P, false, solution_old_, temp1_, ctl, cgw_, /*x_is_zero=*/true, &diag, &off);
+    if (diag.empty())
+      lambda_min_est_ = lambda_max_ = 1.0;
+    else
+      {
+        off.resize(diag.size() - 1);
+        lambda_min_est_ = tridiagonal_min_eigenvalue(diag, off);
+        // include a safety factor since the CG method will in general not be converged
+        lambda_max_ = 1.2 * tridiagonal_max_eigenvalue(diag, off);
+      }
+    const double alpha = smoothing_range_ > 1.0 ? lambda_max_ / smoothing_range_ : std::min(0.9 * lambda_max_, lambda_min_est_);
+    delta_             = (lambda_max_ - alpha) * 0.5;
+    theta_             = (lambda_max_ + alpha) * 0.5;
+    solution_old_.zero();
+    temp1_.zero();
+    eig_done_ = true;
+  }
+
+  template <typename T> void ChebyshevT<T>::vmult(DVec<T> &dst, const DVec<T> &rhs)
+  {
+    estimate_eigenvalues();
+    Context     &c = ctx();
+    const size_t n = dst.n_owned;
+    // iteration_index 0: dst = (1/theta) D^-1 rhs
+    cheb_update<T>(0, T(0), T(1.0 / theta_), rhs.data, dinv_.data, nullptr, nullptr, dst.data, n, c.stream);
+    ++c.launches;
+    if (degree_ < 2 || std::fabs(delta_) < 1e-40)
+      return;
+    double rhok = delta_ / theta_, sigma = theta_ / delta_;
+    for (int k = 0; k < degree_ - 1; ++k)
+      {
+        op_.vmult(temp1_, dst);
+        const double rhokp = 1.0 / (2.0 * sigma - rhok);
+        const double f1 = rhokp * rhok, f2 = 2.0 * rhokp / delta_;
+        rhok = rhokp;
+        cheb_update<T>(k + 1, T(f1), T(f2), rhs.data, dinv_.data, temp1_.data, dst.data, solution_old_.data, n, c.stream);
+        ++c.launches;
+        dst.swap_data(solution_old_);
+      }
+  }
+
+  template <typename T> void ChebyshevT<T>::step(DVec<T> &dst, const DVec<T> &rhs)
+  {
+    estimate_eigenvalues();
+    Context     &c = ctx();
+    const size_t n = dst.n_owned;
+    op_.vmult(temp1_, dst);
+    cheb_update<T>(1, T(0), T(1.0 / theta_), rhs.data, dinv_.data, temp1_.data, dst.data, solution_old_.data, n, c.stream);
+    ++c.launches;
+    dst.swap_data(solution_old_);
+    if (degree_ < 2 || std::fabs(delta_) < 1e-40)
+      return;
+    double rhok = delta_ / theta_, sigma = theta_ / delta_;
+    for (int k = 0; k < degree_ - 1; ++k)
+      {
+        op_.vmult(temp1_, dst);
+        const double rhokp = 1.0 / (2.0 * sigma - rhok);
+        const double f1 = rhokp * rhok, f2 = 2.0 * rhokp / delta_;
+        rhok = rhokp;
+        cheb_update<T>(k + 2, T(f1), T(f2), rhs.data, dinv_.data, temp1_.data, dst.data, solution_old_.data, n, c.stream);
+        ++c.launches;
+        dst.swap_data(solution_old_);
+      }
+  }
+
+  // ------------------------------------------------------------------------------------------ transfers
+  template <typename T>
+  TwoLevelTransferT<T>::TwoLevelTransferT(const DoFMap &fine, const DoFMap &coarse, const TransferMap &tm, const OperatorT<T> &op_fine,
+                                          const OperatorT<T> &op_coarse)
+    : op_fine_(op_fine)
+    , op_coarse_(op_coarse)
+  {
+    ctx().ensure();
+    upload_fe_constants(coarse.degree);
+    fine_own_.upload(fine.own_table.data(), fine.own_table.size());
+    fine_first_.upload(tm.fine_first.data(), tm.fine_first.size());
+    n_children_.upload(tm.n_children.data(), tm.n_children.size());
+    weight_code_.upload(tm.weight_code.data(), tm.weight_code.size());
+    FE1D fec(coarse.degree);
+    Ph_.upload(fec.Ph.data(), fec.Ph.size());
+    const auto pp = p_embedding(fine.degree, coarse.degree);
+    Pp_.upload(pp.data(), pp.size());
+    td_.degree_fine        = fine.degree;
+    td_.degree_coarse      = coarse.degree;
+    td_.n_coarse_cells     = tm.n_coarse_cells;
+    td_.coarse_etab        = op_coarse.cell_data().etab;
+    td_.coarse_mask        = op_coarse.cell_data().mask;
+    td_.coarse_any_hanging = op_coarse.cell_data().any_hanging;
+    td_.fine_own           = fine_own_.ptr;
+    td_.fine_first         = fine_first_.ptr;
+    td_.n_children         = n_children_.ptr;
+    td_.weight_code        = weight_code_.ptr;
+    td_.P_h                = Ph_.ptr;
+    td_.P_p                = Pp_.ptr;
+    if (fine.degree != coarse.degree)
+      for (uint8_t nchild : tm.n_children)
+        if (nchild != 1)
+          throw std::runtime_error("TwoLevelTransfer: simultaneous h- and p-coarsening is not supported (deal.II neither)");
+  }
+
+  template <typename T> void TwoLevelTransferT<T>::prolongate_and_add(DVec<T> &dst_fine, const DVec<T> &src_coarse) const
+  {
+    Context &c = ctx();
+    src_coarse.update_ghost_values();
+    transfer_prolongate_add<T>(td_, dst_fine.data, src_coarse.data, c.stream);
+    ++c.launches;
+    dst_fine.compress_add();
+    src_coarse.zero_out_ghost_values();
+  }
+
+  template <typename T> void TwoLevelTransferT<T>::restrict_and_add(DVec<T> &dst_coarse, const DVec<T> &src_fine) const
+  {
+    Context &c = ctx();
+    src_fine.update_ghost_values();
+    transfer_restrict_add<T>(td_, dst_coarse.data, src_fine.data, c.stream);
+    ++c.launches;
+    dst_coarse.compress_add();
+    src_fine.zero_out_ghost_values();
+  }
+
+  template <typename T>
+  void GCTransferT<T>::copy_to_mg(std::vector<DVec<T>> &defect, unsigned minl, unsigned maxl, const DVec<double> &src) const
+  {
+    Context &c = ctx();
+    for (unsigned l = minl; l <= maxl; ++l)
+      operators[l - min_level]->initialize_dof_vector(defect[l - minl]);
+    DVec<T> &top = defect[maxl - minl];
+    vec_convert<T, double>(top.data, src.data, top.n_owned, c.stream);
+    ++c.launches;
+  }
+
+  template <typename T>
+  void GCTransferT<T>::copy_from_mg(DVec<double> &dst, const std::vector<DVec<T>> &solution, unsigned minl, unsigned maxl) const
+  {
+    Context       &c   = ctx();
+    const DVec<T> &top = solution[maxl - minl];
+    vec_convert<double, T>(dst.data, top.data, top.n_owned, c.stream);
+    ++c.launches;
+  }
+
+  // ------------------------------------------------------------------------------------------ timers
+  cudaEvent_t StageTimers::get()
+  {
+    if (pool_next == pool.size())
+      {
+        cudaEvent_t e;
+        MGB_CUDA(cudaEventCreate(&e));
+        pool.push_back(e);
+      }
+    return pool[pool_next++];
+  }
+  void StageTimers::begin(int level, int stage)
+  {
+    if (!enabled)
+      return;
+    Rec r{get(), get(), level, stage};
+    MGB_CUDA(cudaEventRecord(r.a, ctx().stream));
+    recs.push_back(r);
+  }
+  void StageTimers::end()
+  {
+    if (!enabled)
+      return;
+    MGB_CUDA(cudaEventRecord(recs.back().b, ctx().stream));
+  }
+  void StageTimers::collect(std::vector<std::array<double, N_STAGES + 2>> &times, int min_level)
+  {
+    MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+    for (const Rec &r : recs)
+      {
+        float ms = 0;
+        MGB_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+        times[r.level - min_level][r.stage] += ms * 1e-3;
+      }
+    recs.clear();
+    pool_next = 0;
+  }
+  StageTimers::~StageTimers()
+  {
+    for (cudaEvent_t e : pool)
+      cudaEventDestroy(e);
+  }
+
+  // ------------------------------------------------------------------------------------------ multigrid
+  template <typename T> void MultigridT<T>::cycle()
+  {
+    // The defect vector has been initialized by copy_to_mg. Now adjust the other vectors.
+    for (unsigned l = min_level; l <= max_level; ++l)
+      {
+        solution[l - min_level].reinit_like(defect[l - min_level]);
+        t[l - min_level].reinit_like(defect[l - min_level]);
+      }
+    level_v_step(max_level);
+  }
+
+  template <typename T> void MultigridT<T>::level_v_step(unsigned level)
+  {
+    const unsigned i = level - min_level;
+    const auto     tb = [&](int stage) {
+      if (timers)
+        timers->begin(int(level), stage);
+    };
+    const auto te = [&]() {
+      if (timers)
+        timers->end();
+    };
+    if (level == min_level)
+      {
+        tb(STAGE_COARSE);
+        (*coarse)(level, solution[i], defect[i]);
+        te();
+        return;
+      }
+    tb(STAGE_PRE);
+    smoothers[i]->vmult(solution[i], defect[i]); // pre_smooth->apply (zero initial guess)
+    te();
+    tb(STAGE_RESIDUAL);
+    matrices[i]->vmult_interface_down(t[i], solution[i]);
+    t[i].sadd(T(-1), T(1), defect[i]);
+    te();
+    tb(STAGE_RESTRICTION);
+    transfer->restrict_and_add(level, defect[i - 1], t[i]);
+    te();
+    level_v_step(level - 1);
+    tb(STAGE_PROLONGATION);
+    transfer->prolongate_and_add(level, solution[i], solution[i - 1]);
+    te();
+    if (edge_in)
+      {
+        tb(STAGE_EDGE_PROLONGATION);
+        matrices[i]->vmult_interface_up(t[i], solution[i]);
+        defect[i].add(T(-1), t[i]);
+        te();
+      }
+    tb(STAGE_POST);
+    smoothers[i]->step(solution[i], defect[i]); // post_smooth->smooth
+    te();
+  }
+
+  template <typename T> void PreconditionMGT<T>::vmult(DVec<double> &dst, const DVec<double> &src)
+  {
+    mg->resize_levels();
+    if (timers)
+      timers->begin(int(mg->min_level), N_STAGES);
+    transfer->copy_to_mg(mg->defect, mg->min_level, mg->max_level, src);
+    if (timers)
+      timers->end();
+    mg->cycle();
+    if (timers)
+      timers->begin(int(mg->min_level), N_STAGES + 1);
+    transfer->copy_from_mg(dst, mg->solution, mg->min_level, mg->max_level);
+    if (timers)
+      timers->end();
+  }
+
+  template <typename T> void CoarseApplyMGT<T>::operator()(unsigned, DVec<T> &dst, const DVec<T> &src)
+  {
+    // MGCoarseGridApplyPreconditioner (multigrid_throughput.cc:528-550): cast to double, apply, cast back
+    Context &c = ctx();
+    if (src_d.n_owned != src.n_owned)
+      {
+        src_d.reinit(src.n_owned, src.n_ghost, src.part);
+        dst_d.reinit(src.n_owned, src.n_ghost, src.part);
+      }
+    vec_convert<double, T>(src_d.data, src.data, src.n_owned, c.stream);
+    ++c.launches;
+    pmg->vmult(dst_d, src_d);
+    vec_convert<T, double>(dst.data, dst_d.data, dst.n_owned, c.stream);
+    ++c.launches;
+  }
+
+  template struct DVec<double>;
+  template struct DVec<float>;
+  template class OperatorT<double>;
+  template class OperatorT<float>;
+  template class ChebyshevT<double>;
+  template class ChebyshevT<float>;
+  template class TwoLevelTransferT<double>;
+  template class TwoLevelTransferT<float>;
+  template class GCTransferT<double>;
+  template class GCTransferT<float>;
+  template class MultigridT<double>;
+  template class MultigridT<float>;
+  template class PreconditionMGT<double>;
+  template class PreconditionMGT<float>;
+  template class CoarseApplyMGT<double>;
+  template class CoarseApplyMGT<float>;
+} // namespace mgb

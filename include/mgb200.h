@@ -1,0 +1,224 @@
+/* mgb200 -- C ABI of the B200-native matrix-free multigrid hot path.
+ *
+ * Drop-in boundary for the deal.II-style concepts peterrum/dealii-multigrid composes (the reference has no
+ * FFI; these entry points are what a thin header adapter around its C++ classes binds -- INTEGRATION.md):
+ *
+ *   mgb_operator_*      <->  Operator<dim,1,Number>               include/operator.h:11-557
+ *                            vmult :152-183, Tvmult :185-189, vmult_interface_down :191-201,
+ *                            vmult_interface_up :203-226, compute_inverse_diagonal :228-242,
+ *                            initialize_dof_vector :140-144, m :123-131
+ *   mgb_chebyshev_*     <->  PreconditionChebyshev<Operator,Vector,DiagonalMatrix> as configured in
+ *                            multigrid_throughput.cc:847-883 (vmult = pre-smoothing, step = post-smoothing)
+ *   mgb_transfer_*      <->  MGTwoLevelTransfer::reinit / prolongate_and_add / restrict_and_add
+ *                            multigrid_throughput.cc:1600-1604, 1809-1812
+ *   mgb_vector_*        <->  LinearAlgebra::distributed::Vector<Number> (BLAS-1, update_ghost_values,
+ *                            compress(add)) used implicitly by all of the above
+ *   mgb_problem_*       <->  run<3,1,double,LevelNumber>() + solve_with_global_coarsening /
+ *                            solve_with_local_smoothing + mg_solve   multigrid_throughput.cc:817-1404,
+ *                            1443-1873, 2019-2396 (JSON keys of RunParameters::parse :1989-2014)
+ *   mgb_mesh_*, mgb_dofmap_*, mgb_transfer_map_*
+ *                       <->  stand-in for the deal.II setup objects (Triangulation, DoFHandler,
+ *                            AffineConstraints, MatrixFree::reinit) that produce the index maps consumed by
+ *                            the device objects; with deal.II present an adapter passes deal.II's own maps.
+ *
+ * Conventions: every function returns 0 on success, non-zero on error (message: mgb_last_error()).
+ * Host arrays passed to *_create are copied; handles are destroyed with the matching *_destroy.
+ * Vectors live in device memory ([owned | ghost] layout).  One CUDA stream per process (mgb_set_stream);
+ * handles are not thread-safe (the reference runs 1 thread per rank, multigrid_throughput.cc:2403).
+ * There is NO CPU fallback: every compute entry point fails if no CUDA device is available.
+ */
+#ifndef MGB200_H
+#define MGB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGB_DOUBLE 0
+#define MGB_FLOAT 1
+#define MGB_FLAG_BIT 0x80000000u /* entity-table flag: Dirichlet (eval table) / constrained (own table) */
+
+typedef struct mgb_mesh         mgb_mesh;
+typedef struct mgb_dofmap       mgb_dofmap;
+typedef struct mgb_transfer_map mgb_transfer_map;
+typedef struct mgb_vector       mgb_vector;
+typedef struct mgb_operator     mgb_operator;
+typedef struct mgb_chebyshev    mgb_chebyshev;
+typedef struct mgb_transfer     mgb_transfer;
+typedef struct mgb_problem      mgb_problem;
+
+const char *mgb_last_error(void);
+const char *mgb_version(void);
+
+/* ---- device / stream / communicator ------------------------------------------------------------ */
+int mgb_init(int device);                 /* cudaSetDevice + scratch allocation; fails without a GPU */
+int mgb_set_stream(void *cuda_stream);    /* all subsequent kernels are enqueued on this cudaStream_t */
+int mgb_synchronize(void);
+int64_t mgb_launch_count(void);           /* kernels enqueued by the library so far */
+/* NCCL communicator for ghost exchange and reductions; unique_id = 128-byte ncclUniqueId */
+int mgb_comm_unique_id(void *out128, const char *libnccl_path);
+int mgb_comm_init(const void *unique_id128, int rank, int size, const char *libnccl_path);
+int mgb_comm_finalize(void);
+
+/* ---- 1-D finite element data (host; FE_Q(degree) + QGauss(degree+1) on [0,1]) ------------------- */
+/* nodes[n], M[n*n], K[n*n], S0[n*n], S1[n*n], Ph[(2p+1)*n]; any pointer may be NULL */
+int mgb_fe_1d(int degree, double *nodes, double *M, double *K, double *S0, double *S1, double *Ph);
+/* Pp[(pf+1)*(pc+1)] */
+int mgb_fe_p_embedding(int degree_fine, int degree_coarse, double *Pp);
+
+/* ---- stand-in setup: octree mesh (include/grid_generator.h, multigrid_throughput.cc:2048-2062) --- */
+int     mgb_mesh_create(const char *geometry_type, unsigned n_ref_global, unsigned n_ref_local, mgb_mesh **out);
+int     mgb_mesh_coarsen(const mgb_mesh *fine, mgb_mesh **out); /* one global-coarsening step (:2219-2224) */
+int64_t mgb_mesh_n_cells(const mgb_mesh *m);
+int     mgb_mesh_n_levels(const mgb_mesh *m);
+int     mgb_mesh_get_cells(const mgb_mesh *m, uint32_t *level_x_y_z /* n_cells*4 */);
+void    mgb_mesh_destroy(mgb_mesh *m);
+
+/* ---- stand-in setup: FE_Q DoFs, constraints, partitioner ----------------------------------------- */
+typedef struct
+{
+  int32_t  degree, n_ranks, rank, mesh_max_level;
+  int64_t  n_cells_global, cell_begin, n_cells, n_cells_hanging;
+  int64_t  n_dofs_global, owned_begin;
+  uint32_t n_owned, n_ghost, n_constrained;
+  uint32_t n_ghost_ranks, n_import_ranks, n_import_indices;
+  /* borrowed pointers, valid until mgb_dofmap_destroy */
+  const uint32_t *eval_table;   /* n_cells*27, local index | MGB_FLAG_BIT(Dirichlet)   -- MatrixFree dof_indices */
+  const uint32_t *own_table;    /* n_cells*27, local index | MGB_FLAG_BIT(constrained) -- DoFHandler cell dofs  */
+  const uint16_t *mask;         /* n_cells hanging-node masks                                                   */
+  const uint8_t  *cell_level;   /* n_cells                                                                      */
+  const uint32_t *cell_xyz;     /* n_cells*3                                                                    */
+  const uint32_t *constrained;  /* n_constrained owned local indices (Dirichlet + hanging), ascending           */
+  const int64_t  *ghost_global; /* n_ghost                                                                      */
+  const int32_t  *ghost_ranks;  const uint32_t *ghost_offsets;  /* n_ghost_ranks (+1)                           */
+  const int32_t  *import_ranks; const uint32_t *import_offsets; /* n_import_ranks (+1)                          */
+  const uint32_t *import_indices;                               /* n_import_indices                             */
+} mgb_dofmap_view;
+
+int  mgb_dofmap_create(const mgb_mesh *m, int degree, int n_ranks, int rank, mgb_dofmap **out);
+int  mgb_dofmap_view_get(const mgb_dofmap *d, mgb_dofmap_view *view);
+/* expand an entity table to the lexicographic (p+1)^3 index map per cell (flag kept in bit 31) */
+int  mgb_dofmap_expand(const mgb_dofmap *d, int which /*0 eval, 1 own*/, uint32_t *out /* n_cells*(p+1)^3 */);
+void mgb_dofmap_destroy(mgb_dofmap *d);
+
+typedef struct
+{
+  int32_t         degree_fine, degree_coarse;
+  int64_t         n_coarse_cells, n_fine_cells;
+  const uint32_t *fine_first;  /* n_coarse_cells */
+  const uint8_t  *n_children;  /* n_coarse_cells: 1 or 8 */
+  const uint8_t  *weight_code; /* n_fine_cells*27: 0 -> weight 0, v -> 1/v */
+} mgb_transfer_map_view;
+int  mgb_transfer_map_create(const mgb_mesh *mesh_fine, const mgb_dofmap *fine, const mgb_mesh *mesh_coarse, const mgb_dofmap *coarse,
+                             mgb_transfer_map **out);
+int  mgb_transfer_map_view_get(const mgb_transfer_map *t, mgb_transfer_map_view *view);
+void mgb_transfer_map_destroy(mgb_transfer_map *t);
+
+/* ---- vectors ----------------------------------------------------------------------------------- */
+int  mgb_vector_create(uint32_t n_owned, uint32_t n_ghost, int number_type, mgb_vector **out);
+int  mgb_vector_wrap(void *device_ptr, uint32_t n_owned, uint32_t n_ghost, int number_type, mgb_vector **out);
+void mgb_vector_destroy(mgb_vector *v);
+uint32_t mgb_vector_n_owned(const mgb_vector *v);
+void *mgb_vector_data(mgb_vector *v); /* device pointer */
+int  mgb_vector_copy_from_host(mgb_vector *v, const void *host, uint32_t n); /* first n local entries */
+int  mgb_vector_copy_to_host(const mgb_vector *v, void *host, uint32_t n);
+int  mgb_vector_set(mgb_vector *v, double a);
+int  mgb_vector_add(mgb_vector *y, double a, const mgb_vector *x);           /* y += a x      */
+int  mgb_vector_sadd(mgb_vector *y, double s, double a, const mgb_vector *x); /* y = s y + a x */
+int  mgb_vector_equ(mgb_vector *y, double a, const mgb_vector *x);           /* y = a x       */
+int  mgb_vector_dot(const mgb_vector *x, const mgb_vector *y, double *result);
+int  mgb_vector_l2_norm(const mgb_vector *x, double *result);
+int  mgb_vector_add_and_dot(mgb_vector *g, double a, const mgb_vector *h, double *result); /* g += a h; g.g */
+int  mgb_vector_update_ghost_values(const mgb_vector *v);
+int  mgb_vector_compress_add(mgb_vector *v);
+int  mgb_vector_zero_out_ghost_values(mgb_vector *v);
+
+/* ---- operator (include/operator.h) ---------------------------------------------------------------- */
+typedef struct
+{
+  int32_t         degree, number_type;
+  int64_t         n_cells;
+  const uint32_t *entity_table; /* n_cells*27 compressed dof_indices (see mgb_dofmap_view.eval_table) ...      */
+  const uint32_t *dof_indices;  /* ... or the full lexicographic map n_cells*(p+1)^3 (compressed on the host;
+                                   fails if a cell's entities are not contiguous). Exactly one is non-NULL.   */
+  const uint16_t *mask;         /* hanging-node masks or NULL                                                  */
+  const uint8_t  *cell_level;   /* cell size h = root_length / 2^level (all reference meshes are Cartesian)    */
+  double          root_length;
+  const uint32_t *constrained;  uint32_t n_constrained;          /* operator.h:44-47  */
+  const uint32_t *edge_constrained; uint32_t n_edge_constrained; /* operator.h:49-66  */
+  int32_t         has_edge_constrained_global;                   /* operator.h:67-69  */
+  const uint32_t *edge_cells;   uint32_t n_edge_cells;           /* operator.h:71-99  */
+  int64_t         n_dofs_global;
+  /* vector partitioner (MatrixFree::get_vector_partitioner) */
+  int64_t         owned_begin;
+  uint32_t        n_owned, n_ghost;
+  const int64_t  *ghost_global;
+  const int32_t  *ghost_ranks;  const uint32_t *ghost_offsets;  uint32_t n_ghost_ranks;
+  const int32_t  *import_ranks; const uint32_t *import_offsets; uint32_t n_import_ranks;
+  const uint32_t *import_indices;
+} mgb_operator_desc;
+
+int  mgb_operator_create(const mgb_operator_desc *desc, mgb_operator **out);
+int  mgb_operator_create_from_dofmap(const mgb_dofmap *d, int number_type, mgb_operator **out);
+void mgb_operator_destroy(mgb_operator *op);
+int64_t mgb_operator_m(const mgb_operator *op);
+int  mgb_operator_initialize_dof_vector(const mgb_operator *op, mgb_vector **out);
+int  mgb_operator_vmult(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
+int  mgb_operator_tvmult(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
+int  mgb_operator_vmult_interface_down(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
+int  mgb_operator_vmult_interface_up(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
+int  mgb_operator_compute_inverse_diagonal(const mgb_operator *op, mgb_vector *diag);
+
+/* ---- Chebyshev smoother ---------------------------------------------------------------------------- */
+int  mgb_chebyshev_create(const mgb_operator *op, int degree, double smoothing_range, unsigned eig_cg_n_iterations,
+                          mgb_chebyshev **out);
+void mgb_chebyshev_destroy(mgb_chebyshev *c);
+int  mgb_chebyshev_vmult(mgb_chebyshev *c, mgb_vector *dst, const mgb_vector *rhs); /* zero initial guess     */
+int  mgb_chebyshev_step(mgb_chebyshev *c, mgb_vector *dst, const mgb_vector *rhs);  /* non-zero initial guess */
+int  mgb_chebyshev_eigenvalues(mgb_chebyshev *c, double *lambda_min_estimate, double *lambda_max);
+
+/* ---- two-level transfer ------------------------------------------------------------------------------ */
+int  mgb_transfer_create(const mgb_dofmap *fine, const mgb_dofmap *coarse, const mgb_transfer_map *map, const mgb_operator *op_fine,
+                         const mgb_operator *op_coarse, mgb_transfer **out);
+void mgb_transfer_destroy(mgb_transfer *t);
+int  mgb_transfer_prolongate_and_add(const mgb_transfer *t, mgb_vector *dst_fine, const mgb_vector *src_coarse);
+int  mgb_transfer_restrict_and_add(const mgb_transfer *t, mgb_vector *dst_coarse, const mgb_vector *src_fine);
+
+/* ---- JSON-driven problem: run() + solve_with_* + mg_solve -------------------------------------------- */
+typedef struct
+{
+  int32_t  dim, degree, n_ref_global, n_ref_local, n_levels, n_iterations, sub_comm_size;
+  int64_t  n_cells, n_cells_hn, n_cells_n, n_dofs;
+  double   time, time_cg, throughput;
+  double   time_pre, time_residuum, time_res, time_cs, time_pro, time_edge_pro, time_post, time_to_mg, time_to_global;
+  double   initial_residual, final_residual;
+  int64_t  coarse_iterations; /* total coarse-grid CG iterations of the reported solve */
+} mgb_result;
+
+int  mgb_problem_create(const char *json_text, int n_ranks, int rank, mgb_problem **out);
+void mgb_problem_destroy(mgb_problem *p);
+int  mgb_problem_n_levels(const mgb_problem *p);
+int64_t mgb_problem_level_n_dofs(const mgb_problem *p, int level);
+int64_t mgb_problem_level_n_cells(const mgb_problem *p, int level);
+int  mgb_problem_level_degree(const mgb_problem *p, int level);
+/* borrowed handles of the objects the solver uses */
+const mgb_dofmap   *mgb_problem_level_dofmap(const mgb_problem *p, int level);
+const mgb_operator *mgb_problem_level_operator(const mgb_problem *p, int level);
+mgb_chebyshev      *mgb_problem_level_smoother(mgb_problem *p, int level);
+const mgb_transfer *mgb_problem_level_transfer(const mgb_problem *p, int level); /* between level-1 and level */
+const mgb_operator *mgb_problem_fine_operator(const mgb_problem *p);           /* outer FP64 operator        */
+mgb_vector         *mgb_problem_rhs(mgb_problem *p);
+mgb_vector         *mgb_problem_solution(mgb_problem *p);
+/* PreconditionMG::vmult: one V-cycle, dst = M^-1 src (double vectors of the fine operator's layout) */
+int  mgb_problem_vcycle(mgb_problem *p, mgb_vector *dst, const mgb_vector *src);
+/* SolverCG with the V-cycle preconditioner: one solve from a zero initial guess (no timing protocol) */
+int  mgb_problem_solve_once(mgb_problem *p, int with_stage_timers, mgb_result *result);
+/* the reference's protocol: 1 warm-up + n_repetitions timed solves, best one reported (:1140-1283) */
+int  mgb_problem_run(mgb_problem *p, int n_repetitions, mgb_result *result);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

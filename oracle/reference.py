@@ -1,0 +1,522 @@
+"""ORACLE (test infrastructure, not product code): CPU restatement of the reference's hot path.
+
+Restates, in numpy/scipy, what peterrum/dealii-multigrid computes through deal.II on the path
+  Operator::vmult & co.        include/operator.h:152-242, 450-493
+  PreconditionChebyshev        multigrid_throughput.cc:847-883       (deal.II lac/precondition.h)
+  MGTwoLevelTransfer           multigrid_throughput.cc:1600-1621     (deal.II mg_transfer_global_coarsening)
+  Multigrid / PreconditionMG   multigrid_throughput.cc:1091-1133     (deal.II multigrid.h)
+  SolverCG + ReductionControl  multigrid_throughput.cc:1143-1144, 1625-1635
+following SURVEY.md Appendix A.  deal.II is a third-party dependency that is NOT vendored in
+/root/reference (README.md:26 clones deal.II master, ~9.4); it cannot be compiled or imported here, and
+the reference ships no tests or golden vectors for this path => PARITY UNPINNED against deal.II binaries.
+Substitute pins live in tests/: assembled-matrix cross-checks, polynomial reproduction,
+symmetry, R = P^T, explicit Chebyshev polynomials, scipy eigenvalues.
+
+The index maps (cell -> DoF entity tables, hanging-node masks, constrained lists, transfer cell maps)
+are INPUTS shared with the product, exactly as they would be taken from deal.II's MatrixFree in a real
+integration; this module verifies them through geometry (polynomial reproduction), never by trust.
+
+Formulations here are deliberately different from the CUDA kernels: dense element matrices from Gauss
+quadrature, per-node Kronecker constraint rows, explicit scipy sparse matrices, deal.II's 12-sweep
+collocation evaluation for the matrix-free variant.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline may import this package.
+"""
+import numpy as np
+import scipy.sparse as sp
+
+from .fe import FE1D, p_embedding
+
+FLAG_BIT = np.uint32(0x80000000)
+INDEX_MASK = np.uint32(0x7FFFFFFF)
+
+
+# ----------------------------------------------------------------------------------------- index maps
+def node_entity_tables(p):
+    """entity index (ternary) and offset inside the entity for every lexicographic node of FE_Q(p)"""
+    n = p + 1
+    ent = np.zeros(n ** 3, dtype=np.int64)
+    off = np.zeros(n ** 3, dtype=np.int64)
+    for k in range(n):
+        for j in range(n):
+            for i in range(n):
+                t = [0 if a == 0 else (2 if a == p else 1) for a in (i, j, k)]
+                stride, o = 1, 0
+                for a, ta in zip((i, j, k), t):
+                    if ta == 1:
+                        o += (a - 1) * stride
+                        stride *= (p - 1)
+                ent[(k * n + j) * n + i] = t[0] + 3 * t[1] + 9 * t[2]
+                off[(k * n + j) * n + i] = o
+    return ent, off
+
+
+def expand_table(table, p):
+    """(n_cells, 27) entity table -> (index (n_cells, n^3) int64, flag (n_cells, n^3) bool)"""
+    ent, off = node_entity_tables(p)
+    t = np.asarray(table, dtype=np.uint32)[:, ent]
+    return (t & INDEX_MASK).astype(np.int64) + off[None, :], (t & FLAG_BIT) != 0
+
+
+def cell_constraint_matrix(mask, fe):
+    """dense C_e (n^3 x n^3): local nodal values = C_e @ slot values, for one hanging-node mask.
+
+    Per-node Kronecker rows: along direction d the 1-D subface matrix S[subcell_d]
+    applies to a node iff the node lies in a constrained face whose normal is not d, or on the
+    constrained edge along d."""
+    p, n = fe.degree, fe.n
+    s = [(mask >> d) & 1 for d in range(3)]
+    face = [(mask >> (3 + d)) & 1 for d in range(3)]
+    edge = [(mask >> (6 + d)) & 1 for d in range(3)]
+    eye = np.eye(n)
+    C = np.zeros((n ** 3, n ** 3))
+    for k in range(n):
+        for j in range(n):
+            for i in range(n):
+                idx = (i, j, k)
+                rows = []
+                for d in range(3):
+                    a, b = [x for x in range(3) if x != d]
+                    on_a, on_b = idx[a] == s[a] * p, idx[b] == s[b] * p
+                    applies = (face[a] and on_a) or (face[b] and on_b) or (edge[d] and on_a and on_b)
+                    rows.append(fe.S[s[d]][idx[d]] if applies else eye[idx[d]])
+                C[(k * n + j) * n + i] = np.einsum("k,j,i->kji", rows[2], rows[1], rows[0]).ravel()
+    return C
+
+
+def slot_replaced(mask, p):
+    """bool (27,): entity slots that hold the coarse neighbour's (parent's) entity for this mask"""
+    s = [(mask >> d) & 1 for d in range(3)]
+    out = np.zeros(27, dtype=bool)
+    for e in range(27):
+        t = (e % 3, (e // 3) % 3, e // 9)
+        for d in range(3):
+            a, b = (d + 1) % 3, (d + 2) % 3
+            if ((mask >> (3 + d)) & 1) and t[d] == 2 * s[d]:
+                out[e] = True
+            if ((mask >> (6 + d)) & 1) and t[a] == 2 * s[a] and t[b] == 2 * s[b]:
+                out[e] = True
+    return out
+
+
+class LevelMaps:
+    """Index maps of one level (inputs): what MatrixFree::reinit would provide."""
+
+    def __init__(self, degree, eval_table, own_table, mask, cell_level, cell_xyz, constrained, n_dofs, root_length=2.0):
+        self.degree = degree
+        self.fe = FE1D(degree)
+        self.n_cells = len(cell_level)
+        self.n_dofs = int(n_dofs)
+        self.eval_table = np.asarray(eval_table, dtype=np.uint32)
+        self.own_table = np.asarray(own_table, dtype=np.uint32)
+        self.eval_idx, self.eval_flag = expand_table(eval_table, degree)
+        self.own_idx, self.own_flag = expand_table(own_table, degree)
+        self.mask = np.asarray(mask, dtype=np.int64)
+        self.cell_level = np.asarray(cell_level, dtype=np.int64)
+        self.cell_xyz = np.asarray(cell_xyz, dtype=np.int64)
+        self.h = root_length / (2.0 ** self.cell_level)
+        self.constrained = np.asarray(constrained, dtype=np.int64)
+        self._C = {}
+
+    @classmethod
+    def from_dofmap(cls, d):
+        return cls(d.degree, d.eval_table(), d.own_table(), d.mask(), d.cell_level(), d.cell_xyz(), d.constrained(),
+                   d.n_owned + d.n_ghost)
+
+    def C(self, mask):
+        mask = int(mask)
+        if mask not in self._C:
+            self._C[mask] = cell_constraint_matrix(mask, self.fe)
+        return self._C[mask]
+
+    def node_coordinates(self):
+        """(n_cells, n^3, 3): coordinates of each cell's own nodes"""
+        n = self.fe.n
+        x1 = self.fe.nodes
+        ref = np.stack(np.meshgrid(x1, x1, x1, indexing="ij"), axis=-1)  # [i,j,k,:]
+        ref = ref.transpose(2, 1, 0, 3).reshape(n ** 3, 3)               # lexicographic, x fastest
+        origin = -1.0 + self.h[:, None] * self.cell_xyz
+        return origin[:, None, :] + self.h[:, None, None] * ref[None, :, :]
+
+    def dof_coordinates(self):
+        """(n_dofs, 3) support point of every DoF, from the cells' own tables"""
+        xyz = np.full((self.n_dofs, 3), np.nan)
+        xyz[self.own_idx.ravel()] = self.node_coordinates().reshape(-1, 3)
+        return xyz
+
+
+# ----------------------------------------------------------------------------------------- operator
+def element_matrix_reference(fe):
+    """dense Laplace element matrix on the unit cube from Gauss quadrature of grad phi_i . grad phi_j"""
+    B, G, w = fe.B, fe.G, fe.wq
+    n = fe.n
+    W = np.einsum("a,b,c->abc", w, w, w).ravel()  # weights, z slowest
+    # values of d/dx, d/dy, d/dz of basis (k,j,i) at quadrature point (c,b,a)
+    dx = np.einsum("ck,bj,ai->cbakji", B, B, G).reshape(n ** 3, n ** 3)
+    dy = np.einsum("ck,bj,ai->cbakji", B, G, B).reshape(n ** 3, n ** 3)
+    dz = np.einsum("ck,bj,ai->cbakji", G, B, B).reshape(n ** 3, n ** 3)
+    return dx.T @ (W[:, None] * dx) + dy.T @ (W[:, None] * dy) + dz.T @ (W[:, None] * dz)
+
+
+def assemble_matrix(maps, identity_rows=True):
+    """scipy CSR of the constrained operator: sum_e C_e^T (h A_ref) C_e on unconstrained DoFs (+ identity
+    rows on constrained DoFs as Operator::vmult adds them, include/operator.h:170-172)"""
+    A_ref = element_matrix_reference(maps.fe)
+    n3 = maps.fe.n ** 3
+    rows, cols, vals = [], [], []
+    for m in np.unique(maps.mask):
+        cells = np.nonzero(maps.mask == m)[0]
+        Ae = A_ref if (m >> 3) == 0 else maps.C(m).T @ A_ref @ maps.C(m)
+        idx = maps.eval_idx[cells]
+        keep = ~maps.eval_flag[cells]
+        blk = maps.h[cells][:, None, None] * Ae[None, :, :] * (keep[:, :, None] & keep[:, None, :])
+        rows.append(np.repeat(idx, n3, axis=1).ravel())
+        cols.append(np.tile(idx, (1, n3)).ravel())
+        vals.append(blk.ravel())
+    A = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(maps.n_dofs, maps.n_dofs)).tocsr()
+    if identity_rows:
+        d = np.zeros(maps.n_dofs)
+        d[maps.constrained] = 1.0
+        A = A + sp.diags(d)
+    A.eliminate_zeros()
+    return A
+
+
+def cell_apply_collocation(fe, u):
+    """deal.II's evaluate(gradients) -> quadrature loop -> integrate(gradients) on the unit cube, for a batch
+    u[c, k, j, i]: 12 one-dimensional sweeps, returns A_ref u without the h factor."""
+    B, Dc, w = fe.B, fe.Dc, fe.wq
+    v = np.einsum("ai,ckji->ckja", B, u)
+    v = np.einsum("bj,ckja->ckba", B, v)
+    v = np.einsum("dk,ckba->cdba", B, v)
+    gx = np.einsum("qa,cdba->cdbq", Dc, v)
+    gy = np.einsum("qb,cdba->cdqa", Dc, v)
+    gz = np.einsum("qd,cdba->cqba", Dc, v)
+    W = np.einsum("d,b,a->dba", w, w, w)
+    gx, gy, gz = gx * W, gy * W, gz * W
+    r = np.einsum("qa,cdbq->cdba", Dc, gx) + np.einsum("qb,cdqa->cdba", Dc, gy) + np.einsum("qd,cqba->cdba", Dc, gz)
+    r = np.einsum("dk,cdba->ckba", B, r)
+    r = np.einsum("bj,ckba->ckja", B, r)
+    r = np.einsum("ai,ckja->ckji", B, r)
+    return r
+
+
+class Operator:
+    """Operator<3,1,double> restated (include/operator.h).  edge_* only for local-smoothing levels."""
+
+    def __init__(self, maps, edge_constrained=None, edge_cells=None, has_edge_global=False):
+        self.maps = maps
+        self.edge = np.zeros(0, dtype=np.int64) if edge_constrained is None else np.asarray(edge_constrained, dtype=np.int64)
+        self.edge_cells = None if edge_cells is None else np.asarray(edge_cells, dtype=np.int64)
+        self.has_edge_global = has_edge_global
+
+    def m(self):
+        return self.maps.n_dofs
+
+    def cell_loop(self, src, cells=None):
+        """dst = sum over cells of scatter(C^T A_e C gather(src)) -- MatrixFree::cell_loop + do_cell_integral_global"""
+        mp = self.maps
+        n = mp.fe.n
+        dst = np.zeros(mp.n_dofs)
+        sel = np.arange(mp.n_cells) if cells is None else cells
+        for m in np.unique(mp.mask[sel]):
+            c = sel[mp.mask[sel] == m]
+            idx, flag = mp.eval_idx[c], mp.eval_flag[c]
+            u = np.where(flag, 0.0, src[idx])                      # gather, Dirichlet -> 0
+            if m >> 3:
+                u = u @ mp.C(m).T                                  # hanging-node interpolation
+            r = cell_apply_collocation(mp.fe, u.reshape(-1, n, n, n)).reshape(-1, n ** 3) * mp.h[c][:, None]
+            if m >> 3:
+                r = r @ mp.C(m)                                    # transposed interpolation
+            np.add.at(dst, idx[~flag], r[~flag])
+        return dst
+
+    def vmult_interface_down(self, src):
+        dst = self.cell_loop(src)
+        dst[self.maps.constrained] = src[self.maps.constrained]    # include/operator.h:198-200
+        return dst
+
+    def vmult(self, src):
+        src = src.copy()
+        saved = src[self.edge].copy()
+        src[self.edge] = 0.0                                       # :156-164
+        dst = self.cell_loop(src)
+        dst[self.maps.constrained] = src[self.maps.constrained]    # :170-172
+        dst[self.edge] = saved                                     # :175-182
+        return dst
+
+    Tvmult = vmult
+
+    def vmult_interface_up(self, src):
+        if not self.has_edge_global:
+            return np.zeros(self.maps.n_dofs)                      # :206-210
+        cpy = np.zeros_like(src)
+        cpy[self.edge] = src[self.edge]                            # :216-221
+        return self.cell_loop(cpy, self.edge_cells)                # :224-225
+
+    def compute_inverse_diagonal(self):
+        """MatrixFreeTools::compute_diagonal + threshold inversion (include/operator.h:228-242)"""
+        mp = self.maps
+        A_ref = element_matrix_reference(mp.fe)
+        diag = np.zeros(mp.n_dofs)
+        for m in np.unique(mp.mask):
+            c = np.nonzero(mp.mask == m)[0]
+            Ae = A_ref if (m >> 3) == 0 else mp.C(m).T @ A_ref @ mp.C(m)
+            idx, flag = mp.eval_idx[c], mp.eval_flag[c]
+            contrib = mp.h[c][:, None] * np.diag(Ae)[None, :]
+            np.add.at(diag, idx[~flag], contrib[~flag])
+        diag[self.edge] = 0.0
+        return np.where(np.abs(diag) > 1.0e-10, 1.0 / np.where(diag == 0, 1.0, diag), 1.0)
+
+
+# ----------------------------------------------------------------------------------------- solver control / CG
+class ReductionControl:
+    def __init__(self, maxiter=10000, abstol=1e-20, reltol=1e-4):
+        self.maxiter, self.abstol, self.reltol = maxiter, abstol, reltol
+        self.last_step, self.last_value, self.initial_value = 0, 0.0, 0.0
+
+    def check(self, step, value):
+        self.last_step, self.last_value = step, value
+        if step == 0:
+            self.initial_value, self.reduced_tol = value, value * self.reltol
+        if value <= self.reduced_tol or value <= self.abstol:
+            return "success"
+        if step >= self.maxiter or np.isnan(value):
+            return "failure"
+        return "iterate"
+
+
+class IterationNumberControl:
+    def __init__(self, maxiter, tol=1e-10):
+        self.maxiter, self.tol = maxiter, tol
+        self.last_step, self.last_value = 0, 0.0
+
+    def check(self, step, value):
+        self.last_step, self.last_value = step, value
+        if step >= self.maxiter or value <= self.tol:
+            return "success"
+        return "iterate"
+
+
+def solver_cg(A, x, b, P, control, lanczos=None):
+    """SolverCG::solve. A, P: callables (P None = PreconditionIdentity). x modified in place.
+    lanczos: optional (diag, offdiag) lists receiving the projected tridiagonal matrix entries."""
+    if np.any(x != 0):
+        g = A(x) - b
+    else:
+        g = -b.copy()
+    res = np.sqrt(g @ g)
+    if control.check(0, res) != "iterate":
+        return 0
+    it, gh, eba, prev_alpha = 0, 0.0, 0.0, 0.0
+    d = None
+    while True:
+        it += 1
+        if it > 1:
+            gh_old = gh
+            if P is not None:
+                h = P(g)
+                gh = g @ h
+            else:
+                h = g
+                gh = res * res
+            beta = gh / gh_old
+            d = -h + beta * d
+            if lanczos is not None:
+                lanczos[0].append(1.0 / prev_alpha + eba)
+                lanczos[1].append(np.sqrt(beta) / prev_alpha)
+                eba = beta / prev_alpha
+        else:
+            if P is not None:
+                h = P(g)
+                d = -h
+                gh = g @ h
+            else:
+                d = -g
+                gh = res * res
+        h = A(d)
+        alpha = gh / (d @ h)
+        prev_alpha = alpha
+        x += alpha * d
+        g += alpha * h
+        res = np.sqrt(abs(g @ g))
+        if control.check(it, res) != "iterate":
+            return it
+
+
+# ----------------------------------------------------------------------------------------- Chebyshev
+class PreconditionChebyshev:
+    """PreconditionChebyshev<Operator, Vector, DiagonalMatrix>"""
+
+    def __init__(self, op, degree=3, smoothing_range=20.0, eig_cg_n_iterations=20, owned_begin=0):
+        self.op, self.degree, self.smoothing_range, self.eig_its = op, degree, smoothing_range, eig_cg_n_iterations
+        self.dinv = op.compute_inverse_diagonal()
+        self.owned_begin = owned_begin
+        self.done = False
+
+    def estimate_eigenvalues(self):
+        if self.done:
+            return
+        n = self.op.m()
+        z = ((np.arange(n) + self.owned_begin) % 11).astype(float)
+        z -= z.sum() / n
+        diag, off = [], []
+        x = np.zeros(n)
+        solver_cg(self.op.vmult, x, z, lambda g: self.dinv * g, IterationNumberControl(self.eig_its, 1e-10), (diag, off))
+        if not diag:
+            self.lmin = self.lmax = 1.0
+        else:
+            T = np.diag(diag) + np.diag(off[:len(diag) - 1], 1) + np.diag(off[:len(diag) - 1], -1)
+            ev = np.linalg.eigvalsh(T)
+            self.lmin, self.lmax = ev[0], 1.2 * ev[-1]
+        alpha = self.lmax / self.smoothing_range if self.smoothing_range > 1 else min(0.9 * self.lmax, self.lmin)
+        self.delta, self.theta = 0.5 * (self.lmax - alpha), 0.5 * (self.lmax + alpha)
+        self.done = True
+
+    def vmult(self, rhs):
+        self.estimate_eigenvalues()
+        x = (1.0 / self.theta) * (self.dinv * rhs)
+        if self.degree < 2 or abs(self.delta) < 1e-40:
+            return x
+        x_old = np.zeros_like(x)
+        rhok, sigma = self.delta / self.theta, self.theta / self.delta
+        for k in range(self.degree - 1):
+            t = self.op.vmult(x)
+            rhokp = 1.0 / (2.0 * sigma - rhok)
+            f1, f2 = rhokp * rhok, 2.0 * rhokp / self.delta
+            rhok = rhokp
+            if k == 0:
+                new = (1.0 + f1) * x + f2 * (self.dinv * (rhs - t))
+            else:
+                new = (1.0 + f1) * x - f1 * x_old + f2 * (self.dinv * (rhs - t))
+            x_old, x = x, new
+        return x
+
+    def step(self, x, rhs):
+        self.estimate_eigenvalues()
+        t = self.op.vmult(x)
+        new = x + (1.0 / self.theta) * (self.dinv * (rhs - t))
+        x_old, x = x, new
+        if self.degree < 2 or abs(self.delta) < 1e-40:
+            return x
+        rhok, sigma = self.delta / self.theta, self.theta / self.delta
+        for k in range(self.degree - 1):
+            t = self.op.vmult(x)
+            rhokp = 1.0 / (2.0 * sigma - rhok)
+            f1, f2 = rhokp * rhok, 2.0 * rhokp / self.delta
+            rhok = rhokp
+            new = (1.0 + f1) * x - f1 * x_old + f2 * (self.dinv * (rhs - t))
+            x_old, x = x, new
+        return x
+
+
+# ----------------------------------------------------------------------------------------- transfers
+class MGTwoLevelTransfer:
+    """MGTwoLevelTransfer as an explicit sparse prolongation matrix P; restriction = P^T."""
+
+    def __init__(self, fine, coarse, fine_first, n_children, weights=None):
+        pf, pc = fine.degree, coarse.degree
+        nc, nf = pc + 1, pf + 1
+        fec = coarse.fe
+        if weights is None:
+            weights = transfer_weights(fine, coarse, fine_first, n_children)
+        self.weights = weights  # per fine DoF
+        rows, cols, vals = [], [], []
+        P1 = {8: fec.Ph, 1: (np.eye(nc) if pf == pc else p_embedding(pf, pc))}
+        for c in range(coarse.n_cells):
+            nch = int(n_children[c])
+            P = P1[nch]
+            P3 = np.einsum("Kk,Jj,Ii->KJIkji", P, P, P).reshape(P.shape[0] ** 3, nc ** 3)
+            if coarse.mask[c] >> 3:
+                P3 = P3 @ coarse.C(coarse.mask[c])
+            cidx, cflag = coarse.eval_idx[c], coarse.eval_flag[c]
+            NF = P.shape[0]
+            if nch == 1:
+                fidx = fine.own_idx[fine_first[c]]
+            else:
+                fidx = np.zeros(NF ** 3, dtype=np.int64)
+                for K in range(NF):
+                    for J in range(NF):
+                        for I in range(NF):
+                            cx, cy, cz = int(I > pf), int(J > pf), int(K > pf)
+                            i, j, k = I - cx * pf, J - cy * pf, K - cz * pf
+                            fidx[(K * NF + J) * NF + I] = fine.own_idx[fine_first[c] + cx + 2 * cy + 4 * cz][(k * nf + j) * nf + i]
+            blk = weights[fidx][:, None] * P3 * (~cflag)[None, :]
+            rows.append(np.repeat(fidx, nc ** 3))
+            cols.append(np.tile(cidx, fidx.size))
+            vals.append(blk.ravel())
+        self.P = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))),
+                               shape=(fine.n_dofs, coarse.n_dofs)).tocsr()
+
+    def prolongate_and_add(self, dst_fine, src_coarse):
+        dst_fine += self.P @ src_coarse
+
+    def restrict_and_add(self, dst_coarse, src_fine):
+        dst_coarse += self.P.T @ src_fine
+
+
+def transfer_weights(fine, coarse, fine_first, n_children):
+    """1/valence per fine DoF (number of coarse cells whose fine patch contains it), 0 on constrained fine DoFs"""
+    val = np.zeros(fine.n_dofs)
+    for c in range(coarse.n_cells):
+        cells = np.arange(fine_first[c], fine_first[c] + n_children[c])
+        val[np.unique(fine.own_idx[cells].ravel())] += 1
+    w = np.where(val > 0, 1.0 / np.maximum(val, 1), 0.0)
+    w[fine.constrained] = 0.0
+    return w
+
+
+# ----------------------------------------------------------------------------------------- multigrid
+class Multigrid:
+    """Multigrid<Vector>::cycle / level_v_step + PreconditionMG::vmult for a global-coarsening hierarchy
+    (multigrid_throughput.cc:1091-1133)."""
+
+    def __init__(self, operators, smoothers, transfers, coarse, edge_in=False):
+        self.ops, self.smoothers, self.transfers, self.coarse, self.edge_in = operators, smoothers, transfers, coarse, edge_in
+        self.max_level = len(operators) - 1
+
+    def vmult(self, src):
+        """PreconditionMG::vmult with MGTransferGlobalCoarsening::copy_to_mg / copy_from_mg"""
+        self.defect = [np.zeros(op.m()) for op in self.ops]
+        self.defect[-1][:] = src
+        self.solution = [np.zeros(op.m()) for op in self.ops]
+        self.t = [np.zeros(op.m()) for op in self.ops]
+        self.level_v_step(self.max_level)
+        return self.solution[-1].copy()
+
+    def level_v_step(self, l):
+        if l == 0:
+            self.solution[0] = self.coarse(self.defect[0])
+            return
+        self.solution[l] = self.smoothers[l].vmult(self.defect[l])
+        self.t[l] = self.defect[l] - self.ops[l].vmult_interface_down(self.solution[l])
+        self.transfers[l].restrict_and_add(self.defect[l - 1], self.t[l])
+        self.level_v_step(l - 1)
+        self.transfers[l].prolongate_and_add(self.solution[l], self.solution[l - 1])
+        if self.edge_in:
+            self.t[l] = self.ops[l].vmult_interface_up(self.solution[l])
+            self.defect[l] -= self.t[l]
+        self.solution[l] = self.smoothers[l].step(self.solution[l], self.defect[l])
+
+
+class CoarseGridCG:
+    """MGCoarseGridIterativeSolver<SolverCG, Operator, Identity|Chebyshev> (multigrid_throughput.cc:911-944)"""
+
+    def __init__(self, op, precond=None, maxiter=10000, abstol=1e-20, reltol=1e-4):
+        self.op, self.precond = op, precond
+        self.ctl_args = (maxiter, abstol, reltol)
+        self.total_iterations = 0
+
+    def __call__(self, rhs):
+        x = np.zeros_like(rhs)
+        ctl = ReductionControl(*self.ctl_args)
+        P = None if self.precond is None else self.precond.vmult
+        self.total_iterations += solver_cg(self.op.vmult, x, rhs, P, ctl)
+        return x
+
+
+def polynomial_coarsening_sequence_bisect(degree):
+    d = [degree]
+    while d[-1] > 1:
+        d.append(max(d[-1] // 2, 1))
+    return d[::-1]

@@ -1,0 +1,210 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bar (north_star): index maps bit-exact (shared inputs), vmult and one V-cycle within 1e-12 relative l2 (FP64),
+CG iteration counts identical."""
+import numpy as np
+import pytest
+
+from oracle import reference as ref
+from util import OracleHierarchy, PARITY_RTOL, mesh_sequence, params, rel_l2, seeded
+
+pytestmark = pytest.mark.gpu
+
+OP_CASES = [("hypercube", 2, 1), ("hypercube", 3, 2), ("hypercube", 2, 3), ("hypercube", 3, 4), ("hypercube", 1, 5), ("hypercube", 1, 6),
+            ("quadrant", 4, 1), ("quadrant", 3, 2), ("quadrant", 4, 4), ("annulus", 5, 3), ("annulus", 6, 4), ("circle", 4, 4)]
+
+
+@pytest.mark.parametrize("geometry,L,p", OP_CASES)
+def test_vmult_and_diagonal(gpu, geometry, L, p):
+    mg = gpu
+    d = mg.DoFMap(mg.Mesh(geometry, L), p)
+    maps = ref.LevelMaps.from_dofmap(d)
+    oracle = ref.Operator(maps)
+    op = mg.Operator(d)
+    assert op.m() == maps.n_dofs
+    src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+    x = seeded(maps.n_dofs)
+    src.from_numpy(x)
+    op.vmult(dst, src)
+    y = dst.to_numpy()
+    assert rel_l2(y, oracle.vmult(x)) < PARITY_RTOL
+    np.testing.assert_array_equal(y[maps.constrained], x[maps.constrained])       # identity rows exactly
+    np.testing.assert_array_equal(src.to_numpy(), x)                               # src restored
+    op.Tvmult(dst, src)
+    assert rel_l2(dst.to_numpy(), oracle.vmult(x)) < PARITY_RTOL
+    op.vmult_interface_down(dst, src)
+    assert rel_l2(dst.to_numpy(), oracle.vmult_interface_down(x)) < PARITY_RTOL
+    op.vmult_interface_up(dst, src)                                                # no edge DoFs on active meshes
+    assert np.all(dst.to_numpy() == 0.0)
+    diag = op.initialize_dof_vector()
+    op.compute_inverse_diagonal(diag)
+    assert rel_l2(diag.to_numpy(), oracle.compute_inverse_diagonal()) < PARITY_RTOL
+    # symmetry of the device operator itself: x.(A z) == z.(A x)
+    z = seeded(maps.n_dofs, 3)
+    vz, Az, Ax = op.initialize_dof_vector(), op.initialize_dof_vector(), op.initialize_dof_vector()
+    vz.from_numpy(z)
+    op.vmult(Az, vz)
+    op.vmult(Ax, src)
+    assert abs(src.dot(Az) - vz.dot(Ax)) < 1e-10 * abs(src.dot(Az))
+
+
+def test_operator_from_raw_arrays_and_full_index_map(gpu):
+    """the boundary takes plain index maps: entity table or the full lexicographic MatrixFree-style map"""
+    mg = gpu
+    d = mg.DoFMap(mg.Mesh("quadrant", 3), 3)
+    maps = ref.LevelMaps.from_dofmap(d)
+    x = seeded(maps.n_dofs)
+    expect = ref.Operator(maps).vmult(x)
+    for kw in (dict(entity_table=d.eval_table()), dict(dof_indices=d.expand("eval"))):
+        op = mg.Operator(degree=3, cell_level=d.cell_level(), n_owned=d.n_owned, mask=d.mask(), constrained=d.constrained(), **kw)
+        src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+        src.from_numpy(x)
+        op.vmult(dst, src)
+        assert rel_l2(dst.to_numpy(), expect) < PARITY_RTOL
+    bad = d.expand("eval").copy()
+    bad[0, 5], bad[0, 6] = bad[0, 6], bad[0, 5]
+    with pytest.raises(mg.MgbError, match="not contiguous"):
+        mg.Operator(degree=3, cell_level=d.cell_level(), n_owned=d.n_owned, dof_indices=bad)
+
+
+def test_vector_blas1(gpu):
+    mg = gpu
+    n = 100003
+    a, b = seeded(n, 1), seeded(n, 2)
+    x, y = mg.Vector(n), mg.Vector(n)
+    x.from_numpy(a)
+    y.from_numpy(b)
+    assert abs(x.dot(y) - a @ b) < 1e-12 * np.sqrt(n)
+    assert abs(x.l2_norm() - np.linalg.norm(a)) < 1e-12 * np.linalg.norm(a)
+    y.add(0.5, x)
+    np.testing.assert_allclose(y.to_numpy(), b + 0.5 * a, rtol=1e-15)
+    y.sadd(2.0, -1.0, x)
+    np.testing.assert_allclose(y.to_numpy(), 2 * (b + 0.5 * a) - a, rtol=1e-14, atol=1e-15)
+    y.equ(3.0, x)
+    np.testing.assert_allclose(y.to_numpy(), 3 * a, rtol=1e-15)
+    g = (3 * a) + 0.25 * a
+    assert abs(y.add_and_dot(0.25, x) - g @ g) < 1e-11 * (g @ g)
+    # deterministic reductions: bitwise identical on repetition
+    assert x.dot(x) == x.dot(x)
+    e = mg.Vector(0)
+    assert e.dot(e) == 0.0                                                         # empty vector
+
+
+@pytest.mark.parametrize("geometry,L,p,degree", [("hypercube", 3, 2, 3), ("quadrant", 4, 4, 3), ("annulus", 5, 1, 5), ("hypercube", 2, 4, 1)])
+def test_chebyshev(gpu, geometry, L, p, degree):
+    mg = gpu
+    d = mg.DoFMap(mg.Mesh(geometry, L), p)
+    maps = ref.LevelMaps.from_dofmap(d)
+    oracle = ref.PreconditionChebyshev(ref.Operator(maps), degree, 20.0, 20)
+    op = mg.Operator(d)
+    cheb = mg.PreconditionChebyshev(op, degree, 20.0, 20)
+    lmin, lmax = cheb.eigenvalues()
+    oracle.estimate_eigenvalues()
+    assert abs(lmax - oracle.lmax) < 1e-10 * oracle.lmax
+    b = seeded(maps.n_dofs)
+    rhs, x = op.initialize_dof_vector(), op.initialize_dof_vector()
+    rhs.from_numpy(b)
+    cheb.vmult(x, rhs)
+    assert rel_l2(x.to_numpy(), oracle.vmult(b)) < 1e-11
+    x0 = seeded(maps.n_dofs, 5)
+    x.from_numpy(x0)
+    cheb.step(x, rhs)
+    assert rel_l2(x.to_numpy(), oracle.step(x0.copy(), b)) < 1e-11
+
+
+TRANSFER_CASES = [("hypercube", 2, 1, "h"), ("hypercube", 3, 4, "h"), ("quadrant", 4, 2, "h"), ("annulus", 5, 3, "h"), ("circle", 4, 4, "h"),
+                  ("quadrant", 3, 4, "p"), ("annulus", 5, 2, "p"), ("hypercube", 2, 3, "p"), ("quadrant", 3, 6, "p")]
+
+
+@pytest.mark.parametrize("geometry,L,p,kind", TRANSFER_CASES)
+def test_two_level_transfer(gpu, geometry, L, p, kind):
+    mg = gpu
+    seq = mesh_sequence(geometry, L)
+    (mf, pf), (mc, pc) = ((seq[-1], p), (seq[-2], p)) if kind == "h" else ((seq[-1], p), (seq[-1], max(p // 2, 1)))
+    df, dc = mg.DoFMap(mf, pf), mg.DoFMap(mc, pc)
+    tm = mg.TransferMap(mf, df, mc, dc)
+    fine, coarse = ref.LevelMaps.from_dofmap(df), ref.LevelMaps.from_dofmap(dc)
+    oracle = ref.MGTwoLevelTransfer(fine, coarse, tm.fine_first(), tm.n_children())
+    opf, opc = mg.Operator(df), mg.Operator(dc)
+    T = mg.MGTwoLevelTransfer(df, dc, tm, opf, opc)
+    uc, uf = seeded(coarse.n_dofs, 1), seeded(fine.n_dofs, 2)
+    vc, vf = opc.initialize_dof_vector(), opf.initialize_dof_vector()
+    # prolongate_and_add adds into a non-zero destination
+    vc.from_numpy(uc)
+    vf.from_numpy(uf)
+    T.prolongate_and_add(vf, vc)
+    expect = uf.copy()
+    oracle.prolongate_and_add(expect, uc)
+    assert rel_l2(vf.to_numpy(), expect) < PARITY_RTOL
+    vc.from_numpy(uc)
+    vf.from_numpy(uf)
+    T.restrict_and_add(vc, vf)
+    expect = uc.copy()
+    oracle.restrict_and_add(expect, uf)
+    assert rel_l2(vc.to_numpy(), expect) < PARITY_RTOL
+
+
+SOLVE_CASES = [("hypercube", 3, 1, "HMG-global", "cg"), ("hypercube", 2, 4, "HMG-global", "cg"), ("hypercube", 3, 2, "HMG-global", "cg_with_chebyshev"),
+               ("quadrant", 3, 2, "HMG-global", "cg"), ("quadrant", 3, 4, "HPMG", "cg"), ("annulus", 5, 2, "PMG", "cg"),
+               ("annulus", 5, 4, "HPMG", "cg_with_chebyshev"), ("circle", 4, 1, "HMG-global", "cg")]
+
+
+@pytest.mark.parametrize("geometry,L,p,mg_type,coarse", SOLVE_CASES)
+def test_vcycle_and_cg_iteration_counts(gpu, geometry, L, p, mg_type, coarse):
+    mg = gpu
+    prob = mg.Problem(params(geometry, L, p, mg_type, coarse))
+    H = OracleHierarchy(geometry, L, p, mg_type, 3, coarse)
+    assert prob.n_levels == len(H.levels)
+    for l in range(prob.n_levels):
+        assert prob.level_n_dofs(l) == H.maps[l].n_dofs and prob.level_degree(l) == H.levels[l][1]
+    n = H.maps[-1].n_dofs
+    # one V-cycle (PreconditionMG::vmult) on a seeded defect
+    r = seeded(n)
+    r[H.maps[-1].constrained] = 0.0
+    src, dst = mg.Vector(n), mg.Vector(n)
+    src.from_numpy(r)
+    prob.vcycle(dst, src)
+    assert rel_l2(dst.to_numpy(), H.mg.vmult(r)) < 1e-11
+    # right-hand side of the problem and the full solve
+    b = prob.rhs().to_numpy()
+    x_ref, its_ref, ctl = H.solve(b.copy())
+    res = prob.solve_once()
+    assert res["n_iterations"] == its_ref
+    assert rel_l2(prob.solution().to_numpy(), x_ref) < 1e-9
+    assert abs(res["final_residual"] - ctl.last_value) < 1e-8 * ctl.initial_value
+    assert res["n_dofs"] == n and res["n_levels"] == len(H.levels)
+
+
+def test_rhs_matches_oracle_integration(gpu):
+    """Operator::rhs for f = 1 (include/operator.h:362-413)"""
+    mg = gpu
+    prob = mg.Problem(params("quadrant", 3, 3))
+    maps = ref.LevelMaps.from_dofmap(prob.level_dofmap(prob.n_levels - 1))
+    m1 = maps.fe.M.sum(axis=1)
+    loc = np.einsum("k,j,i->kji", m1, m1, m1).ravel()
+    rhs = np.zeros(maps.n_dofs)
+    for m in np.unique(maps.mask):
+        c = np.nonzero(maps.mask == m)[0]
+        r = np.tile(loc, (len(c), 1)) * (maps.h[c] ** 3)[:, None]
+        if m >> 3:
+            r = r @ maps.C(m)
+        np.add.at(rhs, maps.eval_idx[c][~maps.eval_flag[c]], r[~maps.eval_flag[c]])
+    assert rel_l2(prob.rhs().to_numpy(), rhs) < 1e-13
+
+
+def test_float_level_number_type(gpu):
+    """MGNumberType=float (the reference default): float V-cycle inside the double CG still converges"""
+    mg = gpu
+    res_d = mg.Problem(params("hypercube", 3, 2, number="double")).solve_once()
+    res_f = mg.Problem(params("hypercube", 3, 2, number="float")).solve_once()
+    assert abs(res_f["n_iterations"] - res_d["n_iterations"]) <= 1
+    assert res_f["final_residual"] <= 1e-4 * res_f["initial_residual"]
+
+
+def test_unsupported_inputs_raise(gpu):
+    mg = gpu
+    with pytest.raises(mg.MgbError, match="out of scope"):
+        mg.Problem(params(coarse="amg"))
+    with pytest.raises(mg.MgbError, match="unknown GeometryType"):
+        mg.Problem(params(geometry="torus"))
+    with pytest.raises(mg.MgbError, match="Type"):
+        mg.Problem(params(mg_type="AMG"))

@@ -1,0 +1,198 @@
+"""CPU tests of the stand-in setup (mesh, DoF numbering, constraints, transfer maps) and of the C ABI surface.
+They verify the product's index maps through geometry with the oracle's independent formulations."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import dealii_multigrid_b200 as mg
+from dealii_multigrid_b200 import _lib
+from oracle import fe as ofe
+from oracle import reference as ref
+from util import mesh_sequence
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_capi_exports_every_declared_symbol():
+    """the shared library loads and exports exactly the entry points include/mgb200.h declares"""
+    header = open(os.path.join(ROOT, "include", "mgb200.h")).read()
+    declared = set(re.findall(r"\b(mgb_[a-z0-9_]+)\s*\(", header))
+    lib = _lib.load()
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in mgb200.h but not exported"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+
+
+def test_no_cpu_fallback_without_gpu():
+    """compute entry points must fail loudly when no CUDA device is present (this container has none)"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(mg.MgbError, match="no CUDA device"):
+        mg.init(0)
+    with pytest.raises(mg.MgbError, match="no CUDA device"):
+        mg.Vector(10)
+
+
+@pytest.mark.parametrize("p", [1, 2, 3, 4, 5, 6])
+def test_fe_1d_matches_oracle(p):
+    a, b = mg.fe_1d(p), ofe.FE1D(p)
+    np.testing.assert_allclose(a["nodes"], b.nodes, atol=1e-14)
+    for k, ref_m in (("M", b.M), ("K", b.K), ("S0", b.S[0]), ("S1", b.S[1]), ("Ph", b.Ph)):
+        np.testing.assert_allclose(a[k], ref_m, atol=2e-13, err_msg=k)
+    assert abs(a["M"].sum() - 1.0) < 1e-14          # integral of 1
+    np.testing.assert_allclose(a["K"].sum(axis=1), 0, atol=1e-12)  # constants in the kernel
+    np.testing.assert_allclose(a["S0"].sum(axis=1), 1, atol=1e-13)
+    if p > 1:
+        np.testing.assert_allclose(mg.fe_p_embedding(p, max(p // 2, 1)), ofe.p_embedding(p, max(p // 2, 1)), atol=1e-13)
+
+
+def _check_balance(cells):
+    """2:1 balance across faces, edges and corners, by brute force"""
+    leaves = {tuple(c) for c in cells.tolist()}
+    for (l, x, y, z) in leaves:
+        n = 1 << l
+        for dx in (-1, 0, 1):
+            for dy in (-1, 0, 1):
+                for dz in (-1, 0, 1):
+                    nx, ny, nz = x + dx, y + dy, z + dz
+                    if (dx, dy, dz) == (0, 0, 0) or not (0 <= nx < n and 0 <= ny < n and 0 <= nz < n):
+                        continue
+                    for s in range(2, l + 1):  # an ancestor >= 2 levels coarser must not be a leaf
+                        assert (l - s, nx >> s, ny >> s, nz >> s) not in leaves
+
+
+@pytest.mark.parametrize("geometry,L,n_expected", [("hypercube", 3, 512), ("quadrant", 4, None), ("annulus", 6, None),
+                                                    ("circle", 5, None), ("quadrant_flexible", 2, 64)])
+def test_mesh_and_coarsening_sequence(geometry, L, n_expected):
+    seq = mesh_sequence(geometry, L)
+    fine = seq[-1]
+    if n_expected:
+        assert fine.n_cells == n_expected
+    assert seq[0].n_cells == 1 and len(seq) == fine.n_global_levels
+    vol = sum(8.0 ** (-int(c[0])) for c in fine.cells())
+    assert abs(vol - 1.0) < 1e-12  # leaves tile the root cube
+    for m in seq:
+        _check_balance(m.cells())
+    # every coarse cell is a fine leaf or the parent of 8 fine leaves
+    for coarse, finer in zip(seq[:-1], seq[1:]):
+        fl = {tuple(c) for c in finer.cells().tolist()}
+        for (l, x, y, z) in coarse.cells().tolist():
+            if (l, x, y, z) in fl:
+                continue
+            assert all((l + 1, 2 * x + (c & 1), 2 * y + ((c >> 1) & 1), 2 * z + ((c >> 2) & 1)) in fl for c in range(8))
+
+
+def test_quadrant_matches_reference_rule():
+    """create_quadrant (include/grid_generator.h:34-65): L=2 -> 8 cells, one of them refined again"""
+    assert mg.Mesh("quadrant", 1).n_cells == 8
+    assert mg.Mesh("quadrant", 2).n_cells == 15
+    m = mg.Mesh("quadrant", 3)
+    assert m.n_global_levels == 4
+
+
+@pytest.mark.parametrize("L,p", [(2, 1), (3, 2), (2, 4), (1, 6)])
+def test_hypercube_dof_count(L, p):
+    d = mg.DoFMap(mg.Mesh("hypercube", L), p)
+    assert d.n_dofs_global == (p * 2 ** L + 1) ** 3
+    assert d.n_cells_hanging == 0
+    # Dirichlet DoFs = boundary nodes
+    assert d.n_constrained == (p * 2 ** L + 1) ** 3 - (p * 2 ** L - 1) ** 3
+
+
+def _poly(xyz, p):
+    x, y, z = xyz[..., 0], xyz[..., 1], xyz[..., 2]
+    return 1.0 + 0.3 * x ** p - 0.7 * y ** p * x + 0.5 * z ** p * y ** max(p - 1, 0) + x * y * z
+
+
+@pytest.mark.parametrize("geometry,L", [("hypercube", 2), ("quadrant", 3), ("quadrant", 4), ("annulus", 5), ("circle", 4)])
+@pytest.mark.parametrize("p", [1, 2, 4])
+def test_dofmap_reproduces_polynomials(geometry, L, p):
+    """geometric pin of the index maps: with master DoFs set by nodal interpolation of a degree-p polynomial,
+    gather through the evaluation table + hanging-node interpolation reproduces the polynomial at every cell's
+    own nodes; own tables give every DoF one consistent support point."""
+    d = mg.DoFMap(mg.Mesh(geometry, L), p)
+    maps = ref.LevelMaps.from_dofmap(d)
+    xyz_cells = maps.node_coordinates()
+    # consistency of the numbering: every (cell, node) referencing a DoF sees the same coordinates
+    xyz = maps.dof_coordinates()
+    assert not np.isnan(xyz).any(), "a DoF is not referenced by any cell"
+    np.testing.assert_allclose(xyz[maps.own_idx], xyz_cells, atol=1e-14)
+    assert len(np.unique(maps.own_idx)) == d.n_dofs_global
+    u = _poly(xyz, p)
+    # slots hold real DoFs (Dirichlet flags ignored here: inhomogeneous values)
+    for m in np.unique(maps.mask):
+        cells = np.nonzero(maps.mask == m)[0]
+        loc = u[maps.eval_idx[cells]]
+        if m >> 3:
+            loc = loc @ maps.C(m).T
+        np.testing.assert_allclose(loc, _poly(xyz_cells[cells], p), atol=1e-11)
+    # constrained list = Dirichlet (on the boundary) + hanging DoFs (own entity replaced by a coarse one)
+    on_bnd = (np.abs(np.abs(xyz) - 1.0) < 1e-14).any(axis=1)
+    hanging = np.zeros(d.n_dofs_global, dtype=bool)
+    for m in np.unique(maps.mask):
+        if m >> 3:
+            cells = np.nonzero(maps.mask == m)[0]
+            differs = maps.eval_idx[cells] != maps.own_idx[cells]
+            hanging[maps.own_idx[cells][differs]] = True
+    np.testing.assert_array_equal(np.nonzero(on_bnd | hanging)[0], maps.constrained)
+    # flags: eval flag <=> slot DoF on the boundary; own flag <=> constrained
+    slot_xyz_on_bnd = on_bnd[maps.eval_idx]
+    np.testing.assert_array_equal(maps.eval_flag, slot_xyz_on_bnd)
+    np.testing.assert_array_equal(maps.own_flag, (on_bnd | hanging)[maps.own_idx])
+    # hanging DoFs are never masters
+    assert not hanging[maps.eval_idx].any()
+
+
+def test_full_index_map_matches_entity_table():
+    d = mg.DoFMap(mg.Mesh("quadrant", 3), 3)
+    idx, flag = ref.expand_table(d.eval_table(), 3)
+    full = d.expand("eval")
+    np.testing.assert_array_equal(full & mg.INDEX_MASK, idx)
+    np.testing.assert_array_equal((full & mg.FLAG_BIT) != 0, flag)
+
+
+@pytest.mark.parametrize("geometry,L,p", [("hypercube", 2, 2), ("quadrant", 4, 1), ("quadrant", 3, 4), ("annulus", 5, 2)])
+def test_transfer_map_weights(geometry, L, p):
+    seq = mesh_sequence(geometry, L)
+    mf, mc = seq[-1], seq[-2]
+    df, dc = mg.DoFMap(mf, p), mg.DoFMap(mc, p)
+    tm = mg.TransferMap(mf, df, mc, dc)
+    assert tm.n_children().astype(int).sum() == mf.n_cells
+    fine, coarse = ref.LevelMaps.from_dofmap(df), ref.LevelMaps.from_dofmap(dc)
+    w = ref.transfer_weights(fine, coarse, tm.fine_first(), tm.n_children())
+    code = tm.weight_code().astype(float)
+    ent, _ = ref.node_entity_tables(p)
+    w_prod = np.where(code > 0, 1.0 / np.maximum(code, 1), 0.0)[:, ent]
+    np.testing.assert_array_equal(w_prod, w[fine.own_idx])
+
+
+@pytest.mark.parametrize("n_ranks", [2, 3, 8])
+@pytest.mark.parametrize("geometry,L,p", [("hypercube", 2, 2), ("quadrant", 4, 3)])
+def test_partitioned_dofmaps_are_consistent(geometry, L, p, n_ranks):
+    """rank-local maps describe the same global numbering as the serial map; ghost/import lists match pairwise"""
+    mesh = mg.Mesh(geometry, L)
+    serial = mg.DoFMap(mesh, p)
+    parts = [mg.DoFMap(mesh, p, n_ranks, r) for r in range(n_ranks)]
+    assert sum(d.n_owned for d in parts) == serial.n_dofs_global
+    assert sum(d.n_cells for d in parts) == serial.n_cells
+    s_eval = serial.eval_table()
+    for d in parts:
+        pt = d.partitioner()
+        l2g = np.concatenate([np.arange(d.owned_begin, d.owned_begin + d.n_owned), pt["ghost_global"]])
+        t = d.eval_table()
+        g = l2g[t & mg.INDEX_MASK] | (t & mg.FLAG_BIT)
+        np.testing.assert_array_equal(g, s_eval[d.cell_begin:d.cell_begin + d.n_cells])
+        np.testing.assert_array_equal(l2g[d.constrained()], serial.constrained()[(serial.constrained() >= d.owned_begin) &
+                                                                               (serial.constrained() < d.owned_begin + d.n_owned)])
+    # what rank a imports from ... equals what rank b expects as ghosts, in the same order
+    for a in parts:
+        pa = a.partitioner()
+        for i, b_rank in enumerate(pa["import_ranks"]):
+            send = pa["import_indices"][pa["import_offsets"][i]:pa["import_offsets"][i + 1]] + a.owned_begin
+            pb = parts[b_rank].partitioner()
+            j = list(pb["ghost_ranks"]).index(a.rank)
+            recv = pb["ghost_global"][pb["ghost_offsets"][j]:pb["ghost_offsets"][j + 1]]
+            np.testing.assert_array_equal(send, recv)
