@@ -82,6 +82,8 @@ SIGNATURES = {
     "mgb_set_stream": (C.c_int, [P]),
     "mgb_synchronize": (C.c_int, []),
     "mgb_launch_count": (C.c_int64, []),
+    "mgb_profile_start": (C.c_int, [C.c_int64]),
+    "mgb_profile_stop": (C.c_int, [c_f64p, c_i64p]),
     "mgb_comm_unique_id": (C.c_int, [P, C.c_char_p]),
     "mgb_comm_init": (C.c_int, [P, C.c_int, C.c_int, C.c_char_p]),
     "mgb_comm_finalize": (C.c_int, []),
@@ -151,6 +153,7 @@ SIGNATURES = {
     "mgb_problem_solution": (P, [P]),
     "mgb_problem_vcycle": (C.c_int, [P, P, P]),
     "mgb_problem_solve_once": (C.c_int, [P, C.c_int, C.POINTER(Result)]),
+    "mgb_problem_solve_host": (C.c_int, [P, C.c_void_p, C.c_void_p, C.POINTER(Result)]),
     "mgb_problem_run": (C.c_int, [P, C.c_int, C.POINTER(Result)]),
 }
 

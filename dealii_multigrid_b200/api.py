@@ -54,6 +54,17 @@ def launch_count():
     return int(_lib.load().mgb_launch_count())
 
 
+def profile_start(n_cells):
+    _check(_lib.load().mgb_profile_start(int(n_cells)))
+
+
+def profile_stop():
+    """-> (total milliseconds, number of launches) of the profiled cell-loop kernel"""
+    ms, n = C.c_double(0), C.c_int64(0)
+    _check(_lib.load().mgb_profile_stop(C.byref(ms), C.byref(n)))
+    return ms.value, n.value
+
+
 def comm_unique_id(libnccl_path=None):
     buf = C.create_string_buffer(128)
     _check(_lib.load().mgb_comm_unique_id(buf, libnccl_path.encode() if libnccl_path else None))
@@ -494,6 +505,12 @@ class Problem:
     def solve_once(self, with_stage_timers=False):
         r = _lib.Result()
         _check(self._lib.mgb_problem_solve_once(self._h, int(with_stage_timers), C.byref(r)))
+        return r.as_dict()
+
+    def solve_host(self, rhs_host_ptr, solution_host_ptr):
+        """solve with HOST buffers (raw addresses of n_owned doubles each, ideally pinned): H2D, solve, D2H"""
+        r = _lib.Result()
+        _check(self._lib.mgb_problem_solve_host(self._h, C.c_void_p(rhs_host_ptr), C.c_void_p(solution_host_ptr), C.byref(r)))
         return r.as_dict()
 
     def run(self, n_repetitions=5):

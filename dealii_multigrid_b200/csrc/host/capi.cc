@@ -155,6 +155,36 @@ int mgb_synchronize(void)
 }
 int64_t mgb_launch_count(void) { return ctx().launches; }
 
+int mgb_profile_start(int64_t n_cells)
+{
+  return guarded([&] {
+    Context &c     = ctx();
+    c.prof_enabled = true;
+    c.prof_cells   = n_cells;
+    c.prof_used    = 0;
+  });
+}
+int mgb_profile_stop(double *total_ms, int64_t *n_launches)
+{
+  return guarded([&] {
+    Context &c = ctx();
+    MGB_CUDA(cudaStreamSynchronize(c.stream));
+    double sum = 0;
+    for (size_t i = 0; i < c.prof_used; ++i)
+      {
+        float ms = 0;
+        MGB_CUDA(cudaEventElapsedTime(&ms, c.prof_events[i].first, c.prof_events[i].second));
+        sum += ms;
+      }
+    if (total_ms)
+      *total_ms = sum;
+    if (n_launches)
+      *n_launches = (int64_t)c.prof_used;
+    c.prof_enabled = false;
+    c.prof_used    = 0;
+  });
+}
+
 int mgb_comm_unique_id(void *out128, const char *libnccl_path)
 {
   return guarded([&] { nccl_get_unique_id(out128, libnccl_path); });
@@ -813,6 +843,17 @@ int mgb_problem_vcycle(mgb_problem *p, mgb_vector *dst, const mgb_vector *src)
 int mgb_problem_solve_once(mgb_problem *p, int with_timers, mgb_result *result)
 {
   return guarded([&] { fill_result(p->p->solve_once(with_timers != 0), result); });
+}
+int mgb_problem_solve_host(mgb_problem *p, const double *rhs_host, double *solution_host, mgb_result *result)
+{
+  return guarded([&] {
+    DVec<double> &b = p->p->rhs();
+    DVec<double> &x = p->p->solution();
+    MGB_CUDA(cudaMemcpyAsync(b.data, rhs_host, size_t(b.n_owned) * sizeof(double), cudaMemcpyHostToDevice, ctx().stream));
+    fill_result(p->p->solve_once(false), result);
+    MGB_CUDA(cudaMemcpyAsync(solution_host, x.data, size_t(x.n_owned) * sizeof(double), cudaMemcpyDeviceToHost, ctx().stream));
+    MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+  });
 }
 int mgb_problem_run(mgb_problem *p, int n_repetitions, mgb_result *result)
 {

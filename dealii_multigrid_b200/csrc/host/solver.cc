@@ -33,6 +33,27 @@ namespace mgb
     MGB_CUDA(cudaMallocHost((void **)&host_result, 8 * sizeof(double)));
   }
 
+  void Context::prof_begin(long long n_cells)
+  {
+    if (!prof_enabled || n_cells != prof_cells)
+      return;
+    if (prof_used == prof_events.size())
+      {
+        cudaEvent_t a, b;
+        MGB_CUDA(cudaEventCreate(&a));
+        MGB_CUDA(cudaEventCreate(&b));
+        prof_events.emplace_back(a, b);
+      }
+    MGB_CUDA(cudaEventRecord(prof_events[prof_used].first, stream));
+  }
+  void Context::prof_end(long long n_cells)
+  {
+    if (!prof_enabled || n_cells != prof_cells)
+      return;
+    MGB_CUDA(cudaEventRecord(prof_events[prof_used].second, stream));
+    ++prof_used;
+  }
+
   DevicePartitioner::DevicePartitioner(const Partitioner &p)
     : host(p)
   {
@@ -228,7 +249,11 @@ namespace mgb
           cell_laplace_apply<T>(cd_, src.data, dst.data, edge_cells_.ptr, (long long)edge_cells_.n, c.stream), ++c.launches;
       }
     else
-      cell_laplace_apply<T>(cd_, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
+      {
+        c.prof_begin(cd_.n_cells);
+        cell_laplace_apply<T>(cd_, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
+        c.prof_end(cd_.n_cells);
+      }
     dst.compress_add();
     src.zero_out_ghost_values();
   }

@@ -30,6 +30,14 @@ namespace mgb
     Comm        *comm        = nullptr;
     long long    launches    = 0; // kernels enqueued by this library (bench.py's gpu_launches)
     void         ensure();
+    // live timing of the dominant kernel (bench.py's roofline): CUDA-event pairs around every cell-loop
+    // launch over exactly prof_cells cells while prof_enabled
+    bool                                             prof_enabled = false;
+    long long                                        prof_cells   = 0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    size_t                                           prof_used = 0;
+    void prof_begin(long long n_cells);
+    void prof_end(long long n_cells);
   };
   Context &ctx();
 

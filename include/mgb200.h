@@ -57,6 +57,10 @@ int mgb_init(int device);                 /* cudaSetDevice + scratch allocation;
 int mgb_set_stream(void *cuda_stream);    /* all subsequent kernels are enqueued on this cudaStream_t */
 int mgb_synchronize(void);
 int64_t mgb_launch_count(void);           /* kernels enqueued by the library so far */
+/* live timing of the dominant kernel: CUDA-event pairs around every cell-loop launch over exactly n_cells cells
+ * between start and stop (bench.py's roofline.achieved); stop synchronises and returns the summed duration */
+int mgb_profile_start(int64_t n_cells);
+int mgb_profile_stop(double *total_ms, int64_t *n_launches);
 /* NCCL communicator for ghost exchange and reductions; unique_id = 128-byte ncclUniqueId */
 int mgb_comm_unique_id(void *out128, const char *libnccl_path);
 int mgb_comm_init(const void *unique_id128, int rank, int size, const char *libnccl_path);
@@ -215,6 +219,9 @@ mgb_vector         *mgb_problem_solution(mgb_problem *p);
 int  mgb_problem_vcycle(mgb_problem *p, mgb_vector *dst, const mgb_vector *src);
 /* SolverCG with the V-cycle preconditioner: one solve from a zero initial guess (no timing protocol) */
 int  mgb_problem_solve_once(mgb_problem *p, int with_stage_timers, mgb_result *result);
+/* the same solve with HOST buffers: rhs_host (n_owned doubles) is copied to the device, solved from a zero
+ * initial guess, and the solution copied back into solution_host (n_owned doubles) */
+int  mgb_problem_solve_host(mgb_problem *p, const double *rhs_host, double *solution_host, mgb_result *result);
 /* the reference's protocol: 1 warm-up + n_repetitions timed solves, best one reported (:1140-1283) */
 int  mgb_problem_run(mgb_problem *p, int n_repetitions, mgb_result *result);
 
