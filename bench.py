@@ -1,0 +1,269 @@
+#!/usr/bin/env python
+"""bench.py -- V-cycle-preconditioned CG throughput (DoFs/s) of the B200 hot path, with the vmult roofline.
+
+Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]` prints ONE JSON line on rank 0.
+  * one "step" = one complete preconditioned-CG solve (SolverCG + PreconditionMG V-cycle, Chebyshev(3) smoothing,
+    matrix-free coarse CG) of the reference's multigrid_throughput on the workload below
+    (multigrid_throughput.cc:1238-1283; throughput = n_dofs * n_iterations / t_solve, :1282);
+  * `value`: all inputs resident in HBM (Problem.solve_once);
+  * `e2e`: the same solve through the host-buffer entry point of the C ABI (mgb_problem_solve_host: H2D of the
+    right-hand side from pinned memory, solve, D2H of the solution), copies inside the timed region;
+  * `roofline`: the dominant kernel (finest-level FP64 Laplace cell loop), timed live with CUDA-event pairs on the
+    launching stream around every launch inside the timed region (mgb_profile_start/stop);
+    algorithmic bytes = 16 B/DoF (read src once, write dst once);
+  * `cpu_baseline` / `--impl reference`: the CPU restatement of the reference algorithm under oracle/ timed on the
+    host cores (deal.II itself cannot be built here: SURVEY.md 8(c)).
+Workload: BASELINE.json configs[1] -- 3-D hypercube Poisson, global coarsening, p=4, FP64 V-cycle, coarse CG.
+N>1: one rank per GPU (torchrun), z-order partition of the same mesh (strong scaling), NCCL ghost exchange.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "V-cycle-preconditioned CG DoFs/s (n_dofs * n_iterations / t_solve)"
+UNIT = "DoFs/s"
+
+
+def workload_params(n_ref, degree=4, number="double", coarse="cg"):
+    return {"Type": "HMG-global", "GeometryType": "hypercube", "NRefGlobal": str(n_ref), "NRefLocal": "0", "Degree": str(degree),
+            "Paraview": False, "Verbosity": False, "PartitionerName": "DefaultPolicy", "MinLevel": "0", "MinNCells": "0",
+            "CoarseGridSolverType": coarse, "SmootherDegree": 3, "CoarseSolverNCycles": 1, "RelativeTolerance": 1e-4,
+            "MGNumberType": number, "SimulationType": "Constant"}
+
+
+def workload_name(n_ref, degree, number):
+    n1 = degree * 2 ** n_ref + 1
+    return (f"hypercube L={n_ref} p={degree} HMG-global ({n1}^3 = {n1 ** 3} DoFs), MGNumberType={number}, Chebyshev(3), "
+            f"coarse CG, reltol 1e-4")
+
+
+class ClockSampler:
+    """nvidia-smi sampling during the timed region (B200_PROFILING.md 'clocks' line)"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])), mx.append(float(r[1])), pw.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "power_w_max": max(pw) if pw else None, "samples": len(sm)}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm (oracle)
+def cpu_solve_sample(n_ref, degree, steps, warmup):
+    """time the CPU restatement (oracle/) of the same solve on a bounded sample of the workload"""
+    import numpy as np
+    import dealii_multigrid_b200 as mg  # host-side map generator only (no GPU call)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from util import OracleHierarchy
+    from oracle import reference as ref
+
+    H = OracleHierarchy("hypercube", n_ref, degree, "HMG-global", 3, "cg")
+    b = ref.assemble_rhs_constant(H.maps[-1])
+    n = H.maps[-1].n_dofs
+    for s in H.smoothers:
+        s.estimate_eigenvalues()
+    best, its = 1e300, 0
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        _, its, _ = H.solve(b.copy())
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            best = min(best, dt)
+    return {"n_dofs": n, "n_iterations": its, "seconds": best, "value": n * its / best,
+            "cores": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1)) if False else 1}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_ref = args.cpu_nref
+    r = cpu_solve_sample(n_ref, args.degree, max(1, args.steps), 0 if args.steps else 0)
+    sample = f"{workload_name(n_ref, args.degree, 'double')}: best of {max(1, args.steps)} solves, numpy oracle (deal.II unavailable)"
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["seconds"] * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args.nref, args.degree, args.number), "sample": sample},
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "n_iterations": r["n_iterations"]}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import dealii_multigrid_b200 as mg
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    mg.init(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        uid = [mg.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        mg.comm_init(uid[0], rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    t_setup = time.perf_counter()
+    prob = mg.Problem(workload_params(args.nref, args.degree, args.number), world, rank)
+    fine = prob.n_levels - 1
+    n_dofs = prob.level_n_dofs(fine)
+    dm = prob.level_dofmap(fine)
+    n_owned, n_cells_local = dm.n_owned, dm.n_cells
+    t_setup = time.perf_counter() - t_setup
+
+    # host buffers of the end-to-end arm (pinned)
+    rhs_host = torch.empty(n_owned, dtype=torch.float64).pin_memory()
+    sol_host = torch.empty(n_owned, dtype=torch.float64).pin_memory()
+    rhs_host.copy_(torch.from_numpy(prob.rhs().to_numpy()))
+
+    for _ in range(max(args.warmup, 1)):  # the first solve also runs the lazy Chebyshev eigenvalue estimation
+        res = prob.solve_once()
+    prob.solve_host(rhs_host.data_ptr(), sol_host.data_ptr())
+
+    # ---- timed region 1: K solves, inputs resident in HBM
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    launches0 = mg.launch_count()
+    mg.profile_start(n_cells_local)
+    ev0.record()
+    its = 0
+    for _ in range(args.steps):
+        res = prob.solve_once()
+        its += res["n_iterations"]
+    ev1.record()
+    barrier()
+    k_ms, k_launches = mg.profile_stop()
+    launches = mg.launch_count() - launches0
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    # ---- timed region 2: the same K solves through host buffers (H2D rhs, D2H solution inside the timed region)
+    barrier()
+    ev0.record()
+    its_e2e = 0
+    for _ in range(args.steps):
+        r2 = prob.solve_host(rhs_host.data_ptr(), sol_host.data_ptr())
+        its_e2e += r2["n_iterations"]
+    ev1.record()
+    barrier()
+    ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
+    clocks = sampler.stop() if sampler else None
+
+    value = n_dofs * its / (ms * 1e-3)
+    e2e = n_dofs * its_e2e / (ms_e2e * 1e-3)
+    peak, peak_src = measured_peaks()
+    k_avg_s = (k_ms / max(k_launches, 1)) * 1e-3
+    k_avg_s = max_over_ranks(k_avg_s)
+    alg_bytes = 16.0 * n_owned
+    achieved = alg_bytes / k_avg_s / 1e9 if k_launches else 0.0
+    n1 = args.degree + 1
+    flops_ref = n_cells_local * (24.0 * n1 ** 4 + 9.0 * n1 ** 3)   # F_alg of the 12-sweep reference kernel
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        c = cpu_solve_sample(args.cpu_nref, args.degree, 1, 0)
+        cpu = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
+               "sample": f"{workload_name(args.cpu_nref, args.degree, 'double')}: 1 solve ({c['seconds']:.1f} s), numpy oracle"}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64" if args.number == "double" else "f64 outer CG / f32 V-cycle", "data": "synthetic",
+        "config": {"workload": workload_name(args.nref, args.degree, args.number), "partition": f"z-order, {world} rank(s)",
+                   "l2": "inputs larger than L2 (each fine-level vector %.0f MB, >10 vectors touched per iteration)" % (n_owned * 8 / 1e6),
+                   "n_iterations_per_solve": its / args.steps, "setup_s": round(t_setup, 2)},
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 8 * n_owned, "d2h_bytes_per_step": 8 * n_owned,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": launches,
+        "roofline": {"kernel": f"k_laplace_apply<{args.degree},double> (finest level)", "bound": "hbm", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg_bytes, "launches_timed": k_launches, "avg_launch_ms": k_avg_s * 1e3,
+                     "share_of_step": k_ms / ms, "gdofs_per_s": n_owned / k_avg_s / 1e9,
+                     "fp64_tflops_reference_flop_count": flops_ref / k_avg_s / 1e12},
+        "cpu_baseline": cpu, "clocks": clocks,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--nref", type=int, default=6, help="NRefGlobal of the GPU workload")
+    ap.add_argument("--degree", type=int, default=4)
+    ap.add_argument("--number", default="double", choices=["double", "float"], help="MGNumberType")
+    ap.add_argument("--cpu-nref", type=int, default=4, help="NRefGlobal of the bounded CPU sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -515,6 +515,20 @@ class CoarseGridCG:
         return x
 
 
+def assemble_rhs_constant(maps):
+    """Operator::rhs for f = 1, u_D = 0 (include/operator.h:362-413): b_i = int phi_i, constrained rows dropped"""
+    m1 = maps.fe.M.sum(axis=1)
+    loc = np.einsum("k,j,i->kji", m1, m1, m1).ravel()
+    rhs = np.zeros(maps.n_dofs)
+    for m in np.unique(maps.mask):
+        c = np.nonzero(maps.mask == m)[0]
+        r = np.tile(loc, (len(c), 1)) * (maps.h[c] ** 3)[:, None]
+        if m >> 3:
+            r = r @ maps.C(m)
+        np.add.at(rhs, maps.eval_idx[c][~maps.eval_flag[c]], r[~maps.eval_flag[c]])
+    return rhs
+
+
 def polynomial_coarsening_sequence_bisect(degree):
     d = [degree]
     while d[-1] > 1:
