@@ -88,6 +88,7 @@ SIGNATURES = {
     "mgb_comm_init": (C.c_int, [P, C.c_int, C.c_int, C.c_char_p]),
     "mgb_comm_finalize": (C.c_int, []),
     "mgb_fe_1d": (C.c_int, [C.c_int, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p]),
+    "mgb_fe_1d_fdm": (C.c_int, [C.c_int, c_f64p, c_f64p]),
     "mgb_fe_p_embedding": (C.c_int, [C.c_int, C.c_int, c_f64p]),
     "mgb_mesh_create": (C.c_int, [C.c_char_p, C.c_uint, C.c_uint, PP]),
     "mgb_mesh_coarsen": (C.c_int, [P, PP]),

@@ -94,6 +94,14 @@ def fe_1d(degree):
     return out
 
 
+def fe_1d_fdm(degree):
+    """fast-diagonalisation data of the cell kernels: (Tm, lambda) with K = Tm^T diag(lambda) Tm, M = Tm^T Tm"""
+    n = degree + 1
+    Tm, lam = np.zeros(n * n), np.zeros(n)
+    _check(_lib.load().mgb_fe_1d_fdm(degree, Tm.ctypes.data_as(_lib.c_f64p), lam.ctypes.data_as(_lib.c_f64p)))
+    return Tm.reshape(n, n), lam
+
+
 def fe_p_embedding(degree_fine, degree_coarse):
     P = np.zeros((degree_fine + 1) * (degree_coarse + 1))
     _check(_lib.load().mgb_fe_p_embedding(degree_fine, degree_coarse, P.ctypes.data_as(_lib.c_f64p)))

@@ -14,9 +14,117 @@ namespace mgb
     double M[MAXN * MAXN];
     double K[MAXN * MAXN];
     double S[2][MAXN * MAXN];
+    // fast diagonalisation (fe1d.h): K = Tm^T diag(lam) Tm, M = Tm^T Tm; lam2[j*MAXN+k] = lam[j]+lam[k]
+    double Tm[MAXN * MAXN];
+    double lam[MAXN];
+    double lam2[MAXN * MAXN];
+  };
+  struct FEConstF // single-precision copy of the sweep data (MGNumberType=float kernels)
+  {
+    float Tm[MAXN * MAXN];
+    float lam[MAXN];
+    float lam2[MAXN * MAXN];
   };
   // defined once: this header is included by exactly one translation unit (cells.cu)
-  __constant__ FEConst c_fe[MAX_DEGREE + 1];
+  __constant__ FEConst  c_fe[MAX_DEGREE + 1];
+  __constant__ FEConstF c_fef[MAX_DEGREE + 1];
+
+  template <int P, typename T> struct FDM;
+  template <int P> struct FDM<P, double>
+  {
+    static __device__ __forceinline__ double Tm(int a, int l) { return c_fe[P].Tm[a * MAXN + l]; }
+    static __device__ __forceinline__ double lam(int a) { return c_fe[P].lam[a]; }
+    static __device__ __forceinline__ double lam2(int j, int k) { return c_fe[P].lam2[j * MAXN + k]; }
+  };
+  template <int P> struct FDM<P, float>
+  {
+    static __device__ __forceinline__ float Tm(int a, int l) { return c_fef[P].Tm[a * MAXN + l]; }
+    static __device__ __forceinline__ float lam(int a) { return c_fef[P].lam[a]; }
+    static __device__ __forceinline__ float lam2(int j, int k) { return c_fef[P].lam2[j * MAXN + k]; }
+  };
+
+  // 1-D sweeps on a register line v[0..n-1] (stride S inside a register array), even-odd form:
+  // forward  v <- Tm v      (nodal values -> modes; symmetric modes first)
+  // backward v <- Tm^T v    (modes -> nodal)
+  template <int P, typename T, int S> __device__ __forceinline__ void fdm_forward(T *v)
+  {
+    constexpr int n = P + 1, ne = (n + 1) / 2, no = n / 2;
+    T             e[ne], o[no > 0 ? no : 1];
+#pragma unroll
+    for (int l = 0; l < no; ++l)
+      {
+        e[l] = v[l * S] + v[(n - 1 - l) * S];
+        o[l] = v[l * S] - v[(n - 1 - l) * S];
+      }
+    if (n % 2 == 1)
+      e[ne - 1] = v[(n / 2) * S];
+#pragma unroll
+    for (int a = 0; a < ne; ++a)
+      {
+        T acc = FDM<P, T>::Tm(a, 0) * e[0];
+#pragma unroll
+        for (int l = 1; l < ne; ++l)
+          acc += FDM<P, T>::Tm(a, l) * e[l];
+        v[a * S] = acc;
+      }
+#pragma unroll
+    for (int a = 0; a < no; ++a)
+      {
+        T acc = FDM<P, T>::Tm(ne + a, 0) * o[0];
+#pragma unroll
+        for (int l = 1; l < no; ++l)
+          acc += FDM<P, T>::Tm(ne + a, l) * o[l];
+        v[(ne + a) * S] = acc;
+      }
+  }
+  template <int P, typename T, int S> __device__ __forceinline__ void fdm_backward(T *v)
+  {
+    constexpr int n = P + 1, ne = (n + 1) / 2, no = n / 2;
+    T             e[ne], o[no > 0 ? no : 1];
+#pragma unroll
+    for (int l = 0; l < ne; ++l)
+      {
+        T acc = FDM<P, T>::Tm(0, l) * v[0];
+#pragma unroll
+        for (int a = 1; a < ne; ++a)
+          acc += FDM<P, T>::Tm(a, l) * v[a * S];
+        e[l] = acc;
+      }
+#pragma unroll
+    for (int l = 0; l < no; ++l)
+      {
+        T acc = FDM<P, T>::Tm(ne, l) * v[ne * S];
+#pragma unroll
+        for (int a = 1; a < no; ++a)
+          acc += FDM<P, T>::Tm(ne + a, l) * v[(ne + a) * S];
+        o[l] = acc;
+      }
+#pragma unroll
+    for (int l = 0; l < no; ++l)
+      {
+        v[l * S]           = e[l] + o[l];
+        v[(n - 1 - l) * S] = e[l] - o[l];
+      }
+    if (n % 2 == 1)
+      v[(n / 2) * S] = e[ne - 1];
+  }
+
+  // shared-memory layout of the slab kernels: one cell = n planes (k) of n*n values with plane stride PS and cell
+  // stride CS, chosen so that lane (cell, plane) -> cell*CS + plane*PS and lane (cell, i) -> cell*CS + i are both
+  // bank-conflict free (64-bit: per half-warp on 16 banks; 32-bit: per warp on 32 banks).
+  template <int N, int BYTES> struct SlabLayout;
+  template <> struct SlabLayout<2, 8> { static constexpr int PS = 5, CS = 10; };
+  template <> struct SlabLayout<3, 8> { static constexpr int PS = 17, CS = 51; };
+  template <> struct SlabLayout<4, 8> { static constexpr int PS = 17, CS = 68; };
+  template <> struct SlabLayout<5, 8> { static constexpr int PS = 33, CS = 165; };
+  template <> struct SlabLayout<6, 8> { static constexpr int PS = 41, CS = 246; };
+  template <> struct SlabLayout<7, 8> { static constexpr int PS = 49, CS = 343; };
+  template <> struct SlabLayout<2, 4> { static constexpr int PS = 5, CS = 10; };
+  template <> struct SlabLayout<3, 4> { static constexpr int PS = 30, CS = 93; };
+  template <> struct SlabLayout<4, 4> { static constexpr int PS = 17, CS = 68; };
+  template <> struct SlabLayout<5, 4> { static constexpr int PS = 30, CS = 155; };
+  template <> struct SlabLayout<6, 4> { static constexpr int PS = 47, CS = 282; };
+  template <> struct SlabLayout<7, 4> { static constexpr int PS = 49, CS = 344; };
 
   // lexicographic node (i,j,k) of FE_Q(P) -> entity (ternary) and offset inside the entity
   template <int P> __device__ __forceinline__ void node_to_entity(int i, int j, int k, int &e, int &off)
@@ -42,6 +150,18 @@ namespace mgb
   }
 
   template <typename T> __device__ __forceinline__ void atomic_add(T *p, T v) { atomicAdd(p, v); }
+
+  // asynchronous global -> shared copy of one vector entry (LDGSTS); !valid zero-fills (Dirichlet entries)
+  template <typename T> __device__ __forceinline__ void cp_async_entry(T *smem_dst, const T *gmem_src, const bool valid)
+  {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    const unsigned b = valid ? (unsigned)sizeof(T) : 0u;
+    if (sizeof(T) == 8)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(s), "l"(gmem_src), "r"(b) : "memory");
+    else
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(s), "l"(gmem_src), "r"(b) : "memory");
+  }
+  __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
   // In-place hanging-node interpolation of one cell's nodal values `u` (n^3, lexicographic, in shared
   // memory) -- SURVEY.md A.3 step 2 (TRANSPOSE=false, before evaluation) and step 6 (TRANSPOSE=true,

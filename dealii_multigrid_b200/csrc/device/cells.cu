@@ -27,7 +27,21 @@ namespace mgb
           h.S[0][i * MAXN + j] = fe.S[0][i * fe.n + j];
           h.S[1][i * MAXN + j] = fe.S[1][i * fe.n + j];
         }
+    FEConstF hf{};
+    for (int i = 0; i < fe.n; ++i)
+      {
+        h.lam[i] = fe.lambda[i];
+        hf.lam[i] = (float)fe.lambda[i];
+        for (int j = 0; j < fe.n; ++j)
+          {
+            h.Tm[i * MAXN + j]    = fe.Tm[i * fe.n + j];
+            h.lam2[i * MAXN + j]  = fe.lambda[i] + fe.lambda[j];
+            hf.Tm[i * MAXN + j]   = (float)fe.Tm[i * fe.n + j];
+            hf.lam2[i * MAXN + j] = (float)(fe.lambda[i] + fe.lambda[j]);
+          }
+      }
     MGB_CUDA(cudaMemcpyToSymbol(c_fe, &h, sizeof(FEConst), sizeof(FEConst) * degree));
+    MGB_CUDA(cudaMemcpyToSymbol(c_fef, &hf, sizeof(FEConstF), sizeof(FEConstF) * degree));
     done[degree] = true;
   }
 

@@ -225,6 +225,16 @@ int mgb_fe_1d(int degree, double *nodes, double *M, double *K, double *S0, doubl
       std::memcpy(Ph, fe.Ph.data(), fe.Ph.size() * sizeof(double));
   });
 }
+int mgb_fe_1d_fdm(int degree, double *Tm, double *lambda)
+{
+  return guarded([&] {
+    FE1D fe(degree);
+    if (Tm)
+      std::memcpy(Tm, fe.Tm.data(), fe.Tm.size() * sizeof(double));
+    if (lambda)
+      std::memcpy(lambda, fe.lambda.data(), fe.lambda.size() * sizeof(double));
+  });
+}
 int mgb_fe_p_embedding(int pf, int pc, double *Pp)
 {
   return guarded([&] {

@@ -160,6 +160,173 @@ namespace mgb
     for (int I = 0; I < nf; ++I)
       for (int j = 0; j < n; ++j)
         Ph[I * n + j] = (I <= degree) ? S[0][I * n + j] : S[1][(I - degree) * n + j];
+    compute_fdm();
+  }
+
+  namespace
+  {
+    // generalised symmetric eigenproblem Kb y = lambda Mb y (m x m, Mb SPD): Cholesky + cyclic Jacobi.
+    // Returns eigenvectors as columns of Y (Y^T Mb Y = I) and eigenvalues in ascending order.
+    void generalized_eig(const std::vector<long double> &Kb, const std::vector<long double> &Mb, int m, std::vector<long double> &Y,
+                         std::vector<long double> &lam)
+    {
+      std::vector<long double> L(m * m, 0.0L);
+      for (int i = 0; i < m; ++i)
+        for (int j = 0; j <= i; ++j)
+          {
+            long double s = Mb[i * m + j];
+            for (int k = 0; k < j; ++k)
+              s -= L[i * m + k] * L[j * m + k];
+            L[i * m + j] = (i == j) ? std::sqrt(s) : s / L[j * m + j];
+          }
+      // C = L^-1 Kb L^-T
+      std::vector<long double> X(m * m), C(m * m);
+      for (int c = 0; c < m; ++c) // X = L^-1 Kb (column by column)
+        for (int i = 0; i < m; ++i)
+          {
+            long double s = Kb[i * m + c];
+            for (int k = 0; k < i; ++k)
+              s -= L[i * m + k] * X[k * m + c];
+            X[i * m + c] = s / L[i * m + i];
+          }
+      for (int r = 0; r < m; ++r) // C^T = L^-1 X^T
+        for (int i = 0; i < m; ++i)
+          {
+            long double s = X[r * m + i];
+            for (int k = 0; k < i; ++k)
+              s -= L[i * m + k] * C[r * m + k];
+            C[r * m + i] = s / L[i * m + i];
+          }
+      std::vector<long double> Q(m * m, 0.0L);
+      for (int i = 0; i < m; ++i)
+        Q[i * m + i] = 1.0L;
+      for (int sweep = 0; sweep < 100; ++sweep)
+        {
+          long double off = 0;
+          for (int i = 0; i < m; ++i)
+            for (int j = 0; j < i; ++j)
+              off += C[i * m + j] * C[i * m + j];
+          if (off < 1e-60L)
+            break;
+          for (int p = 0; p < m; ++p)
+            for (int q = p + 1; q < m; ++q)
+              {
+                if (std::fabs((double)C[p * m + q]) < 1e-300)
+                  continue;
+                const long double theta = (C[q * m + q] - C[p * m + p]) / (2.0L * C[p * m + q]);
+                const long double t     = (theta >= 0 ? 1.0L : -1.0L) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0L));
+                const long double c = 1.0L / std::sqrt(t * t + 1.0L), s = t * c;
+                for (int k = 0; k < m; ++k)
+                  {
+                    const long double a = C[k * m + p], b = C[k * m + q];
+                    C[k * m + p] = c * a - s * b;
+                    C[k * m + q] = s * a + c * b;
+                  }
+                for (int k = 0; k < m; ++k)
+                  {
+                    const long double a = C[p * m + k], b = C[q * m + k];
+                    C[p * m + k] = c * a - s * b;
+                    C[q * m + k] = s * a + c * b;
+                  }
+                for (int k = 0; k < m; ++k)
+                  {
+                    const long double a = Q[k * m + p], b = Q[k * m + q];
+                    Q[k * m + p] = c * a - s * b;
+                    Q[k * m + q] = s * a + c * b;
+                  }
+              }
+        }
+      // Y = L^-T Q, sorted by eigenvalue
+      std::vector<int> order(m);
+      for (int i = 0; i < m; ++i)
+        order[i] = i;
+      std::sort(order.begin(), order.end(), [&](int a, int b) { return C[a * m + a] < C[b * m + b]; });
+      Y.assign(m * m, 0.0L);
+      lam.assign(m, 0.0L);
+      for (int cc = 0; cc < m; ++cc)
+        {
+          const int c = order[cc];
+          lam[cc]     = C[c * m + c];
+          for (int i = m - 1; i >= 0; --i)
+            {
+              long double s = Q[i * m + c];
+              for (int k = i + 1; k < m; ++k)
+                s -= L[k * m + i] * Y[k * m + cc];
+              Y[i * m + cc] = s / L[i * m + i];
+            }
+        }
+    }
+  } // namespace
+
+  void FE1D::compute_fdm()
+  {
+    // work in the symmetric / antisymmetric subspaces so that the modes have exact parity
+    const int ne = (n + 1) / 2, no = n / 2;
+    Tm.assign(n * n, 0.0);
+    lambda.assign(n, 0.0);
+    const long double r2 = std::sqrt(0.5L);
+    for (int parity = 0; parity < 2; ++parity)
+      {
+        const int m = parity == 0 ? ne : no;
+        if (m == 0)
+          continue;
+        // basis vectors b_c (c < m) of the subspace, as full-length vectors
+        std::vector<long double> Bv(m * n, 0.0L);
+        for (int c = 0; c < m; ++c)
+          {
+            if (n % 2 == 1 && c == n / 2)
+              Bv[c * n + c] = 1.0L; // middle node (even subspace only)
+            else
+              {
+                Bv[c * n + c]         = r2;
+                Bv[c * n + n - 1 - c] = parity == 0 ? r2 : -r2;
+              }
+          }
+        std::vector<long double> Kb(m * m), Mb(m * m);
+        for (int a = 0; a < m; ++a)
+          for (int b = 0; b < m; ++b)
+            {
+              long double k = 0, mm = 0;
+              for (int i = 0; i < n; ++i)
+                for (int j = 0; j < n; ++j)
+                  {
+                    k += Bv[a * n + i] * (long double)K[i * n + j] * Bv[b * n + j];
+                    mm += Bv[a * n + i] * (long double)M[i * n + j] * Bv[b * n + j];
+                  }
+              Kb[a * m + b] = k;
+              Mb[a * m + b] = mm;
+            }
+        std::vector<long double> Y, lam;
+        generalized_eig(Kb, Mb, m, Y, lam);
+        for (int c = 0; c < m; ++c)
+          {
+            const int row = parity == 0 ? c : ne + c;
+            lambda[row]   = (double)std::max(lam[c], 0.0L);
+            if (parity == 0 && c == 0)
+              lambda[row] = 0.0; // constant mode: K 1 = 0 exactly
+            // s = sum_b Y[b][c] b_b ;  Tm[row,:] = s^T M
+            std::vector<long double> s(n, 0.0L);
+            for (int b = 0; b < m; ++b)
+              for (int i = 0; i < n; ++i)
+                s[i] += Y[b * m + c] * Bv[b * n + i];
+            for (int l = 0; l < n; ++l)
+              {
+                long double v = 0;
+                for (int i = 0; i < n; ++i)
+                  v += s[i] * (long double)M[i * n + l];
+                Tm[row * n + l] = (double)v;
+              }
+            // exact parity
+            for (int l = 0; l < n / 2; ++l)
+              {
+                const double a = 0.5 * (Tm[row * n + l] + (parity == 0 ? 1.0 : -1.0) * Tm[row * n + n - 1 - l]);
+                Tm[row * n + l]         = a;
+                Tm[row * n + n - 1 - l] = parity == 0 ? a : -a;
+              }
+            if (parity == 1 && n % 2 == 1)
+              Tm[row * n + n / 2] = 0.0;
+          }
+      }
   }
 
   std::vector<double> p_embedding(int degree_fine, int degree_coarse)

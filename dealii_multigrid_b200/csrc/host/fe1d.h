@@ -31,7 +31,17 @@ namespace mgb
     std::vector<double> M, K;        // n*n row-major
     std::vector<double> S[2];        // n*n row-major, S[c][i*n+j] = l_j(c/2 + x_i/2)
     std::vector<double> Ph;          // (2p+1)*n row-major
+    // fast diagonalisation of the pencil (K, M):  K = Tm^T diag(lambda) Tm,  M = Tm^T Tm, so that
+    //   A_e = h (Tm x Tm x Tm)^T diag(lambda_i + lambda_j + lambda_k) (Tm x Tm x Tm)
+    // Rows of Tm are the modes; the first (n+1)/2 rows are symmetric in the node index, the remaining
+    // n/2 antisymmetric (the nodes are symmetric about 1/2), which the device kernels use as an
+    // even-odd decomposition of every 1-D sweep.
+    std::vector<double> Tm;          // n*n row-major, Tm[a*n+l]
+    std::vector<double> lambda;      // n
     explicit FE1D(int degree);
+
+  private:
+    void compute_fdm();
   };
 
   // p-embedding: (pf+1) x (pc+1), coarse basis at the fine nodes

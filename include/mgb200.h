@@ -69,6 +69,9 @@ int mgb_comm_finalize(void);
 /* ---- 1-D finite element data (host; FE_Q(degree) + QGauss(degree+1) on [0,1]) ------------------- */
 /* nodes[n], M[n*n], K[n*n], S0[n*n], S1[n*n], Ph[(2p+1)*n]; any pointer may be NULL */
 int mgb_fe_1d(int degree, double *nodes, double *M, double *K, double *S0, double *S1, double *Ph);
+/* fast diagonalisation of the 1-D pencil used by the cell kernels: K = Tm^T diag(lambda) Tm, M = Tm^T Tm;
+ * Tm[n*n] (rows = modes, symmetric ones first), lambda[n] */
+int mgb_fe_1d_fdm(int degree, double *Tm, double *lambda);
 /* Pp[(pf+1)*(pc+1)] */
 int mgb_fe_p_embedding(int degree_fine, int degree_coarse, double *Pp);
 
