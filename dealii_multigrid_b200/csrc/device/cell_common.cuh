@@ -110,21 +110,21 @@ namespace mgb
   }
 
   // shared-memory layout of the slab kernels: one cell = n planes (k) of n*n values with plane stride PS and cell
-  // stride CS, chosen so that lane (cell, plane) -> cell*CS + plane*PS and lane (cell, i) -> cell*CS + i are both
-  // bank-conflict free (64-bit: per half-warp on 16 banks; 32-bit: per warp on 32 banks).
+  // stride CS, chosen so that the slab pattern, lane (cell, plane) -> cell*CS + plane*PS, and the column pattern,
+  // lane c -> (c / n^2)*CS + c % n^2, are bank-conflict free (64-bit: per half-warp on 16 banks; 32-bit: per warp).
   template <int N, int BYTES> struct SlabLayout;
   template <> struct SlabLayout<2, 8> { static constexpr int PS = 5, CS = 10; };
-  template <> struct SlabLayout<3, 8> { static constexpr int PS = 17, CS = 51; };
+  template <> struct SlabLayout<3, 8> { static constexpr int PS = 19, CS = 57; };
   template <> struct SlabLayout<4, 8> { static constexpr int PS = 17, CS = 68; };
-  template <> struct SlabLayout<5, 8> { static constexpr int PS = 33, CS = 165; };
-  template <> struct SlabLayout<6, 8> { static constexpr int PS = 41, CS = 246; };
-  template <> struct SlabLayout<7, 8> { static constexpr int PS = 49, CS = 343; };
+  template <> struct SlabLayout<5, 8> { static constexpr int PS = 37, CS = 185; };
+  template <> struct SlabLayout<6, 8> { static constexpr int PS = 37, CS = 222; };
+  template <> struct SlabLayout<7, 8> { static constexpr int PS = 55, CS = 385; };
   template <> struct SlabLayout<2, 4> { static constexpr int PS = 5, CS = 10; };
-  template <> struct SlabLayout<3, 4> { static constexpr int PS = 30, CS = 93; };
+  template <> struct SlabLayout<3, 4> { static constexpr int PS = 26, CS = 105; };
   template <> struct SlabLayout<4, 4> { static constexpr int PS = 17, CS = 68; };
-  template <> struct SlabLayout<5, 4> { static constexpr int PS = 30, CS = 155; };
-  template <> struct SlabLayout<6, 4> { static constexpr int PS = 47, CS = 282; };
-  template <> struct SlabLayout<7, 4> { static constexpr int PS = 49, CS = 344; };
+  template <> struct SlabLayout<5, 4> { static constexpr int PS = 27, CS = 153; };
+  template <> struct SlabLayout<6, 4> { static constexpr int PS = 37, CS = 222; };
+  template <> struct SlabLayout<7, 4> { static constexpr int PS = 50, CS = 369; };
 
   // lexicographic node (i,j,k) of FE_Q(P) -> entity (ternary) and offset inside the entity
   template <int P> __device__ __forceinline__ void node_to_entity(int i, int j, int k, int &e, int &off)

@@ -58,6 +58,7 @@ namespace mgb
     int             degree     = 1;
     long long       n_cells    = 0;
     const uint32_t *etab       = nullptr; // n_cells*27 entity table (local indices | FLAG_BIT)
+    const uint32_t *ctab       = nullptr; // n_cells*32 packed cell records: 27 entity entries, word 27 = mask | level << 16
     const uint16_t *mask       = nullptr; // n_cells hanging-node masks (may be null)
     const uint8_t  *level      = nullptr; // n_cells refinement levels; h = root_length / 2^level
     double          root_length = 2.0;

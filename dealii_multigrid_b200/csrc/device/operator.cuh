@@ -15,6 +15,9 @@
 #pragma once
 #include "cell_common.cuh"
 
+#include <algorithm>
+#include <stdexcept>
+
 namespace mgb
 {
   // number of cells per block for degree P
@@ -120,11 +123,12 @@ namespace mgb
     static constexpr int CW  = 32 / n;          // cells per warp
     static constexpr int W   = P <= 4 ? 4 : 2;  // warps per block
     static constexpr int CPB = CW * W;          // cells per block
+    static constexpr int MIN_BLOCKS = P <= 4 ? 3 : 2; // resident blocks per SM the register allocation must allow
   };
 
-  // warp-level version of hanging_node_sweeps for the padded slab layout; `u` = the warp's cells, smask = their masks
+  // warp-level version of hanging_node_sweeps for the padded slab layout; `u` = the warp's cells, tb = their 32-word records (word 27 = mask | level << 16)
   template <int P, typename T, bool TRANSPOSE>
-  __device__ __forceinline__ void hanging_node_sweeps_slab(T *u, const uint16_t *smask, const int ncw, const int lane)
+  __device__ __forceinline__ void hanging_node_sweeps_slab(T *u, const uint32_t *tb, const int ncw, const int lane)
   {
     constexpr int n = P + 1, n2 = n * n;
     constexpr int PS = SlabLayout<n, sizeof(T)>::PS, CS = SlabLayout<n, sizeof(T)>::CS;
@@ -136,7 +140,7 @@ namespace mgb
         for (int w = lane; w < ncw * n2; w += 32)
           {
             const int      cl = w / n2, t = w % n2;
-            const unsigned mask = smask[cl];
+            const unsigned mask = tb[cl * 32 + 27] & 0xffffu;
             if (!(mask >> 3))
               continue;
             const int  a = t % n, b = t / n;
@@ -170,144 +174,228 @@ namespace mgb
       }
   }
 
-  template <int P, typename T>
-  __global__ void __launch_bounds__(SlabCfg<P>::W * 32)
-    k_laplace_apply(const uint32_t *__restrict__ etab, const uint16_t *__restrict__ maskv, const uint8_t *__restrict__ levelv,
-                    const double root_length, const long long n_work, const uint32_t *__restrict__ cell_list,
-                    const T *__restrict__ src, T *__restrict__ dst)
+  // Persistent, software-pipelined kernel.  Every warp walks over its batches of CW cells (stride = all warps of the
+  // grid).  Two thread layouts alternate inside a batch:
+  //   column layout: lane <-> one (i,j) column of one cell (CW*n^2 columns, NR rounds of 32); the n values along z
+  //                  live in registers.  Gather (coalesced along the lexicographic node index, straight into
+  //                  registers), the z sweep, its transpose and the scatter (RED) happen here, without shared memory.
+  //   slab layout:   lane <-> (cell, plane k); the n^2 values of the plane live in registers for the x and y sweeps,
+  //                  the diagonal scaling and the transposed y and x sweeps.
+  // The two transposes between the layouts are the only shared-memory traffic of the data path (4 n^3 words per cell).
+  // Prefetching: the gather of batch b+1 is issued into registers as soon as the z sweep of batch b has consumed the
+  // previous ones, and the cells' packed 32-word records (27 entity entries | mask+level word) of batch b+2 are
+  // streamed into a 3-deep shared ring by 16-byte LDGSTS, so no warp waits for a load it has just issued.
+  constexpr int CTAB_STRIDE = 32; // words per cell record
+
+  template <int P, typename T> struct SlabSmem
   {
-    constexpr int n = P + 1, n2 = n * n, n3 = n2 * n;
+    static constexpr int n  = P + 1;
+    static constexpr int CW = SlabCfg<P>::CW;
+    static constexpr int CS = SlabLayout<n, sizeof(T)>::CS;
+    // per warp: cell storage + 3 table buffers
+    static constexpr size_t u_bytes            = (size_t(CW * CS) * sizeof(T) + 15) / 16 * 16;
+    static constexpr size_t warp_bytes_aligned = u_bytes + 3 * size_t(CW) * CTAB_STRIDE * 4;
+    static size_t           block_bytes(int warps) { return warps * warp_bytes_aligned; }
+  };
+
+  template <int P, typename T>
+  __global__ void __launch_bounds__(SlabCfg<P>::W * 32, SlabCfg<P>::MIN_BLOCKS)
+    k_laplace_apply(const uint32_t *__restrict__ ctab, const int any_hanging, const double root_length, const long long n_work,
+                    const uint32_t *__restrict__ cell_list, const T *__restrict__ src, T *__restrict__ dst)
+  {
+    constexpr int n = P + 1, n2 = n * n;
     constexpr int CW = SlabCfg<P>::CW, W = SlabCfg<P>::W;
     constexpr int PS = SlabLayout<n, sizeof(T)>::PS, CS = SlabLayout<n, sizeof(T)>::CS;
-    __shared__ T        sU[W][CW * CS];
-    __shared__ uint32_t stab[W][CW][27];
-    __shared__ T        sh[W][CW];
-    __shared__ uint16_t smask[W][CW];
-    __shared__ uint32_t slut[n3]; // node q -> entity (bits 24..), offset in entity (bits 16..23), smem address (bits 0..15)
+    constexpr int NR = (CW * n2 + 31) / 32; // rounds of the column layout
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int      warp  = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned char *wbase = smem_raw + warp * SlabSmem<P, T>::warp_bytes_aligned;
+    T             *u     = reinterpret_cast<T *>(wbase);                                  // [CW*CS]
+    uint32_t      *tbuf  = reinterpret_cast<uint32_t *>(wbase + SlabSmem<P, T>::u_bytes);          // [3][CW][32]
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int q = threadIdx.x; q < n3; q += W * 32)
-      {
-        const int i = q % n, j = (q / n) % n, k = q / n2;
-        int       e, off;
-        node_to_entity<P>(i, j, k, e, off);
-        slut[q] = (uint32_t(e) << 24) | (uint32_t(off) << 16) | uint32_t(k * PS + j * n + i);
-      }
-    const long long first = ((long long)blockIdx.x * W + warp) * CW;
-    const int       ncw   = (int)max(0ll, min((long long)CW, n_work - first));
-    for (int idx = lane; idx < ncw * 27; idx += 32)
-      {
-        const int       cl   = idx / 27, e = idx - cl * 27;
-        const long long cell = cell_list ? (long long)cell_list[first + cl] : first + cl;
-        stab[warp][cl][e]    = etab[cell * 27 + e];
-      }
-    unsigned mymask = 0;
-    if (lane < ncw)
-      {
-        const long long cell = cell_list ? (long long)cell_list[first + lane] : first + lane;
-        if (maskv)
-          mymask = maskv[cell];
-        smask[warp][lane] = (uint16_t)mymask;
-        sh[warp][lane]    = T(root_length / double(1u << levelv[cell]));
-      }
-    const bool warp_hn = __any_sync(0xffffffffu, (mymask >> 3) != 0);
-    __syncthreads();
+    const long long n_batches = (n_work + CW - 1) / CW;
+    const long long stride    = (long long)gridDim.x * W;
+    long long       b         = (long long)blockIdx.x * W + warp;
+    if (b >= n_batches)
+      return;
 
-    T *u = sU[warp];
-    // gather (Dirichlet entities read 0): asynchronous copies straight into shared memory, all in flight at once
-    for (int cl = 0; cl < ncw; ++cl)
+    // static per-lane description of the columns of each round, packed into one word:
+    // cell (5 bits) | entity base tx+3ty (4) | offset inside the entity (5) | z stride inside the entity (5) | smem address (13)
+    uint32_t col[NR];
 #pragma unroll
-      for (int q = lane; q < n3; q += 32)
+    for (int r = 0; r < NR; ++r)
+      {
+        const int c  = r * 32 + lane;
+        const int cl = c / n2, ij = c - cl * n2, i = ij % n, j = ij / n;
+        const int tx = i == 0 ? 0 : (i == P ? 2 : 1), ty = j == 0 ? 0 : (j == P ? 2 : 1);
+        const int sx = tx == 1 ? P - 1 : 1;
+        col[r] = uint32_t(c < CW * n2 ? cl : 31) | uint32_t(tx + 3 * ty) << 5 |
+                 uint32_t((tx == 1 ? i - 1 : 0) + (ty == 1 ? (j - 1) * sx : 0)) << 9 | uint32_t(sx * (ty == 1 ? P - 1 : 1)) << 14 |
+                 uint32_t(c < CW * n2 ? cl * CS + ij : 0) << 19;
+      }
+    const auto col_cl = [&](const int r) { return int(col[r] & 31u); };
+    const auto col_sm = [&](const int r) { return int(col[r] >> 19); };
+
+    const auto issue_tables = [&](const long long batch, uint32_t *tb) {
+      if (batch >= n_batches)
+        return;
+      const long long first = batch * CW;
+      const int       ncw   = (int)min((long long)CW, n_work - first);
+      for (int idx = lane; idx < ncw * (CTAB_STRIDE / 4); idx += 32)
         {
-          const uint32_t lut  = slut[q];
-          const uint32_t tb   = stab[warp][cl][lut >> 24];
-          const bool     flag = (tb & D_FLAG_BIT) != 0;
-          cp_async_entry<T>(u + cl * CS + (lut & 0xffffu), src + (flag ? 0u : (tb & D_INDEX_MASK) + ((lut >> 16) & 0xffu)), !flag);
+          const int       cl   = idx / (CTAB_STRIDE / 4), part = idx % (CTAB_STRIDE / 4);
+          const long long cell = cell_list ? (long long)cell_list[first + cl] : first + cl;
+          const unsigned  s    = (unsigned)__cvta_generic_to_shared(tb + cl * CTAB_STRIDE + part * 4);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(ctab + cell * CTAB_STRIDE + part * 4) : "memory");
         }
+    };
+    // global index of node k of a column (bit 31 = Dirichlet)
+    const auto column_index = [&](const uint32_t *tb, const int r, const int k) -> uint32_t {
+      const uint32_t e = tb[(col[r] & 31u) * CTAB_STRIDE + ((col[r] >> 5) & 15u) + (k == 0 ? 0 : (k == P ? 18 : 9))];
+      return e + ((col[r] >> 9) & 31u) + ((k > 0 && k < P) ? (k - 1) * ((col[r] >> 14) & 31u) : 0);
+    };
+    T          pre[NR][n];
+    const auto issue_gather = [&](const long long batch, const uint32_t *tb) {
+      const int ncw = batch < n_batches ? (int)min((long long)CW, n_work - batch * CW) : 0;
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+#pragma unroll
+        for (int k = 0; k < n; ++k)
+          {
+            pre[r][k] = T(0);
+            if (col_cl(r) < ncw)
+              {
+                const uint32_t idx = column_index(tb, r, k);
+                if (!(idx & D_FLAG_BIT))
+                  pre[r][k] = __ldg(src + idx);
+              }
+          }
+    };
+
+    // prologue
+    issue_tables(b, tbuf);
     cp_async_wait_all();
     __syncwarp();
-    if (warp_hn)
-      hanging_node_sweeps_slab<P, T, false>(u, smask[warp], ncw, lane);
+    issue_gather(b, tbuf);
+    issue_tables(b + stride, tbuf + CW * CTAB_STRIDE);
 
-    const int  cl = lane / n, t = lane - cl * n;
-    const bool active = cl < ncw;
-    T          reg[n2];
-    if (active)
+    const int cl = lane / n, t = lane - cl * n;
+    const T   lk = cl < CW ? FDM<P, T>::lam(t) : T(0);
+    int       it = 0;
+    for (; b < n_batches; b += stride, ++it)
       {
-        T *pl = u + cl * CS + t * PS; // plane k = t: reg[j*n+i]
-#pragma unroll
-        for (int r = 0; r < n2; ++r)
-          reg[r] = pl[r];
-#pragma unroll
-        for (int j = 0; j < n; ++j)
-          fdm_forward<P, T, 1>(reg + j * n);
-#pragma unroll
-        for (int i = 0; i < n; ++i)
-          fdm_forward<P, T, n>(reg + i);
-#pragma unroll
-        for (int r = 0; r < n2; ++r)
-          pl[r] = reg[r];
-      }
-    __syncwarp();
-    if (active)
-      {
-        T *col = u + cl * CS + t; // plane i = t: reg[k*n+j] = element (i, j, k)
-#pragma unroll
-        for (int k = 0; k < n; ++k)
-#pragma unroll
-          for (int j = 0; j < n; ++j)
-            reg[k * n + j] = col[k * PS + j * n];
-#pragma unroll
-        for (int j = 0; j < n; ++j)
-          fdm_forward<P, T, n>(reg + j);
-        const T li = FDM<P, T>::lam(t);
-#pragma unroll
-        for (int k = 0; k < n; ++k)
-#pragma unroll
-          for (int j = 0; j < n; ++j)
-            reg[k * n + j] *= (li + FDM<P, T>::lam2(j, k));
-#pragma unroll
-        for (int j = 0; j < n; ++j)
-          fdm_backward<P, T, n>(reg + j);
-#pragma unroll
-        for (int k = 0; k < n; ++k)
-#pragma unroll
-          for (int j = 0; j < n; ++j)
-            col[k * PS + j * n] = reg[k * n + j];
-      }
-    __syncwarp();
-    if (active)
-      {
-        T *pl = u + cl * CS + t * PS;
-#pragma unroll
-        for (int r = 0; r < n2; ++r)
-          reg[r] = pl[r];
-#pragma unroll
-        for (int i = 0; i < n; ++i)
-          fdm_backward<P, T, n>(reg + i);
-#pragma unroll
-        for (int j = 0; j < n; ++j)
-          fdm_backward<P, T, 1>(reg + j * n);
-#pragma unroll
-        for (int r = 0; r < n2; ++r)
-          pl[r] = reg[r];
-      }
-    __syncwarp();
-    if (warp_hn)
-      hanging_node_sweeps_slab<P, T, true>(u, smask[warp], ncw, lane);
-
-    // scatter-add
-    for (int c2 = 0; c2 < ncw; ++c2)
-      {
-        const T h = sh[warp][c2];
-#pragma unroll
-        for (int q = lane; q < n3; q += 32)
+        const uint32_t *tb  = tbuf + (it % 3) * (CW * CTAB_STRIDE);
+        const int       ncw = (int)min((long long)CW, n_work - b * CW);
+        bool            warp_hn = false;
+        if (any_hanging)
           {
-            const uint32_t lut = slut[q];
-            const uint32_t tb  = stab[warp][c2][lut >> 24];
-            if (!(tb & D_FLAG_BIT))
-              atomic_add(dst + (tb & D_INDEX_MASK) + ((lut >> 16) & 0xffu), h * u[c2 * CS + (lut & 0xffffu)]);
+            const unsigned mymask = lane < ncw ? (tb[lane * CTAB_STRIDE + 27] & 0xffffu) : 0u;
+            warp_hn               = __any_sync(0xffffffffu, (mymask >> 3) != 0);
           }
+        if (warp_hn)
+          {
+            // hanging-node interpolation on the nodal values (through shared memory; only warps that have such cells)
+#pragma unroll
+            for (int r = 0; r < NR; ++r)
+              if (col_cl(r) < ncw)
+#pragma unroll
+                for (int k = 0; k < n; ++k)
+                  u[col_sm(r) + k * PS] = pre[r][k];
+            __syncwarp();
+            hanging_node_sweeps_slab<P, T, false>(u, tb, ncw, lane);
+#pragma unroll
+            for (int r = 0; r < NR; ++r)
+              if (col_cl(r) < ncw)
+#pragma unroll
+                for (int k = 0; k < n; ++k)
+                  pre[r][k] = u[col_sm(r) + k * PS];
+            __syncwarp();
+          }
+        // z sweep in the column layout, then to shared memory
+#pragma unroll
+        for (int r = 0; r < NR; ++r)
+          if (col_cl(r) < ncw)
+            {
+              fdm_forward<P, T, 1>(pre[r]);
+#pragma unroll
+              for (int k = 0; k < n; ++k)
+                u[col_sm(r) + k * PS] = pre[r][k];
+            }
+        // tables(b+stride) have landed (issued one iteration ago): start the gather of the next batch
+        cp_async_wait_all();
+        __syncwarp();
+        issue_gather(b + stride, tbuf + ((it + 1) % 3) * (CW * CTAB_STRIDE));
+        issue_tables(b + 2 * stride, tbuf + ((it + 2) % 3) * (CW * CTAB_STRIDE));
+
+        if (cl < ncw)
+          {
+            T  reg[n2];
+            T *pl = u + cl * CS + t * PS; // plane k = t (z mode t): reg[j*n+i]
+#pragma unroll
+            for (int r = 0; r < n2; ++r)
+              reg[r] = pl[r];
+#pragma unroll
+            for (int j = 0; j < n; ++j)
+              fdm_forward<P, T, 1>(reg + j * n);
+#pragma unroll
+            for (int i = 0; i < n; ++i)
+              fdm_forward<P, T, n>(reg + i);
+#pragma unroll
+            for (int j = 0; j < n; ++j)
+#pragma unroll
+              for (int i = 0; i < n; ++i)
+                reg[j * n + i] *= (lk + FDM<P, T>::lam2(i, j));
+#pragma unroll
+            for (int i = 0; i < n; ++i)
+              fdm_backward<P, T, n>(reg + i);
+#pragma unroll
+            for (int j = 0; j < n; ++j)
+              fdm_backward<P, T, 1>(reg + j * n);
+#pragma unroll
+            for (int r = 0; r < n2; ++r)
+              pl[r] = reg[r];
+          }
+        __syncwarp();
+        // transposed z sweep in the column layout and scatter-add
+        if (warp_hn)
+          {
+#pragma unroll
+            for (int r = 0; r < NR; ++r)
+              if (col_cl(r) < ncw)
+                {
+                  T res[n];
+#pragma unroll
+                  for (int k = 0; k < n; ++k)
+                    res[k] = u[col_sm(r) + k * PS];
+                  fdm_backward<P, T, 1>(res);
+#pragma unroll
+                  for (int k = 0; k < n; ++k)
+                    u[col_sm(r) + k * PS] = res[k];
+                }
+            __syncwarp();
+            hanging_node_sweeps_slab<P, T, true>(u, tb, ncw, lane);
+          }
+#pragma unroll
+        for (int r = 0; r < NR; ++r)
+          if (col_cl(r) < ncw)
+            {
+              T res[n];
+#pragma unroll
+              for (int k = 0; k < n; ++k)
+                res[k] = u[col_sm(r) + k * PS];
+              if (!warp_hn)
+                fdm_backward<P, T, 1>(res);
+              const unsigned level = (tb[col_cl(r) * CTAB_STRIDE + 27] >> 16) & 0xffu;
+              const T        h     = T(root_length * __hiloint2double((1023 - (int)level) << 20, 0));
+#pragma unroll
+              for (int k = 0; k < n; ++k)
+                {
+                  const uint32_t idx = column_index(tb, r, k);
+                  if (!(idx & D_FLAG_BIT))
+                    atomic_add(dst + idx, h * res[k]);
+                }
+            }
+        __syncwarp(); // u is rewritten by the next iteration's columns
       }
   }
 
@@ -385,13 +473,25 @@ namespace mgb
   template <int P, typename T>
   void launch_apply(const CellData &cd, const T *src, T *dst, const uint32_t *cell_list, long long n_list, cudaStream_t s)
   {
-    constexpr int   CPB    = SlabCfg<P>::CPB;
+    constexpr int   CW = SlabCfg<P>::CW, W = SlabCfg<P>::W;
     const long long n_work = cell_list ? n_list : cd.n_cells;
     if (n_work <= 0)
       return;
-    const long long blocks = (n_work + CPB - 1) / CPB;
-    k_laplace_apply<P, T><<<(unsigned)blocks, SlabCfg<P>::W * 32, 0, s>>>(cd.etab, cd.any_hanging ? cd.mask : nullptr, cd.level,
-                                                                          cd.root_length, n_work, cell_list, src, dst);
+    const size_t smem = SlabSmem<P, T>::block_bytes(W);
+    static int   blocks_per_sm = 0, n_sm = 0; // per (P, T) instantiation
+    if (blocks_per_sm == 0)
+      {
+        int dev = 0;
+        MGB_CUDA(cudaGetDevice(&dev));
+        MGB_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+        MGB_CUDA(cudaFuncSetAttribute(k_laplace_apply<P, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_laplace_apply<P, T>, W * 32, smem));
+        if (blocks_per_sm < 1)
+          throw std::runtime_error("k_laplace_apply does not fit on an SM");
+      }
+    const long long n_batches = (n_work + CW - 1) / CW;
+    const long long blocks    = std::min<long long>((n_batches + W - 1) / W, (long long)blocks_per_sm * n_sm);
+    k_laplace_apply<P, T><<<(unsigned)blocks, W * 32, smem, s>>>(cd.ctab, cd.any_hanging, cd.root_length, n_work, cell_list, src, dst);
     MGB_CUDA(cudaGetLastError());
   }
 

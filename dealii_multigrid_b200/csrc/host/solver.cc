@@ -219,6 +219,17 @@ namespace mgb
           any_hanging |= (s.mask[c] >> 3) != 0;
         mask_.upload(s.mask, size_t(s.n_cells));
       }
+    {
+      // packed 32-word cell records of the vmult kernel (operator.cuh)
+      std::vector<uint32_t> rec(size_t(s.n_cells) * 32, 0u);
+      for (long long c = 0; c < s.n_cells; ++c)
+        {
+          std::memcpy(&rec[size_t(c) * 32], s.entity_table + size_t(c) * 27, 27 * sizeof(uint32_t));
+          rec[size_t(c) * 32 + 27] = uint32_t(s.mask ? s.mask[c] : 0) | (uint32_t(s.cell_level[c]) << 16);
+        }
+      ctab_.upload(rec.data(), rec.size());
+    }
+    cd_.ctab        = ctab_.ptr;
     cd_.degree      = s.degree;
     cd_.n_cells     = s.n_cells;
     cd_.etab        = etab_.ptr;

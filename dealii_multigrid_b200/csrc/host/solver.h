@@ -350,7 +350,7 @@ namespace mgb
   private:
     void cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_cells_only) const;
     CellData                           cd_;
-    DeviceBuffer<uint32_t>             etab_;
+    DeviceBuffer<uint32_t>             etab_, ctab_;
     DeviceBuffer<uint16_t>             mask_;
     DeviceBuffer<uint8_t>              level_;
     DeviceBuffer<uint32_t>             constrained_, edge_, edge_cells_;
