@@ -1,0 +1,49 @@
+#!/usr/bin/env python
+"""make_golden.py -- (re)generate tests/golden/*.npz from the CPU oracle.
+
+The reference ships no golden vectors for this path, and deal.II cannot run here, so these fixtures
+freeze the ORACLE's answers on seeded inputs: they guard the oracle against silent drift (CPU suite) and give the GPU
+suite a file-based known answer that does not depend on executing oracle code on the GPU box.
+Index maps come from the product's host generator (they are inputs of both sides); run from the repo root:
+    python tests/golden/make_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+sys.path.insert(0, os.path.dirname(HERE))
+
+from util import OracleHierarchy, seeded  # noqa: E402
+
+CASES = [("hypercube", 2, 4, "HMG-global", "cg"), ("quadrant", 3, 2, "HMG-global", "cg"), ("annulus", 4, 2, "HPMG", "cg_with_chebyshev"),
+         ("quadrant", 3, 4, "PMG", "cg")]
+
+
+def case_name(c):
+    return "%s_L%d_p%d_%s_%s" % c
+
+
+def generate(c):
+    from oracle import reference as ref
+    geometry, L, p, mg_type, coarse = c
+    H = OracleHierarchy(geometry, L, p, mg_type, 3, coarse)
+    n = H.maps[-1].n_dofs
+    x = seeded(n)
+    r = x.copy()
+    r[H.maps[-1].constrained] = 0.0
+    b = ref.assemble_rhs_constant(H.maps[-1])
+    sol, its, ctl = H.solve(b.copy())
+    for s in H.smoothers:
+        s.estimate_eigenvalues()
+    return dict(n_dofs=n, level_dofs=np.array([m.n_dofs for m in H.maps]), vmult=H.ops[-1].vmult(x),
+                inverse_diagonal=H.ops[-1].compute_inverse_diagonal(), vcycle=H.mg.vmult(r), rhs=b, solution=sol,
+                n_iterations=its, final_residual=ctl.last_value, lambda_max=np.array([s.lmax for s in H.smoothers]))
+
+
+if __name__ == "__main__":
+    for c in CASES:
+        np.savez_compressed(os.path.join(HERE, case_name(c) + ".npz"), **generate(c))
+        print("wrote", case_name(c))

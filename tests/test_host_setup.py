@@ -196,3 +196,22 @@ def test_partitioned_dofmaps_are_consistent(geometry, L, p, n_ranks):
             j = list(pb["ghost_ranks"]).index(a.rank)
             recv = pb["ghost_global"][pb["ghost_offsets"][j]:pb["ghost_offsets"][j + 1]]
             np.testing.assert_array_equal(send, recv)
+
+
+@pytest.mark.parametrize("p", [1, 2, 3, 4, 5, 6])
+def test_fast_diagonalisation_of_the_1d_pencil(p):
+    """the cell kernels evaluate A_e = h (Tm x Tm x Tm)^T diag(l_i+l_j+l_k) (Tm x Tm x Tm): K = Tm^T L Tm, M = Tm^T Tm,
+    modes exactly symmetric / antisymmetric (even-odd sweeps), constant mode in the null space"""
+    fe, (Tm, lam) = mg.fe_1d(p), mg.fe_1d_fdm(p)
+    n, ne = p + 1, (p + 2) // 2
+    assert np.abs(Tm.T @ np.diag(lam) @ Tm - fe["K"]).max() < 1e-13 * np.abs(fe["K"]).max()
+    assert np.abs(Tm.T @ Tm - fe["M"]).max() < 1e-15
+    assert np.array_equal(Tm[:ne], Tm[:ne, ::-1]) and np.array_equal(Tm[ne:], -Tm[ne:, ::-1])
+    assert lam[0] == 0.0 and np.all(lam[1:] > 0)
+    # 3-D cell matrix from the factorisation equals the Kronecker form
+    if p <= 3:
+        T3 = np.kron(Tm, np.kron(Tm, Tm))
+        D = (lam[:, None, None] + lam[None, :, None] + lam[None, None, :]).ravel()
+        M, K = fe["M"], fe["K"]
+        A = np.kron(K, np.kron(M, M)) + np.kron(M, np.kron(K, M)) + np.kron(M, np.kron(M, K))
+        assert np.abs(T3.T @ (D[:, None] * T3) - A).max() < 1e-13 * np.abs(A).max()
