@@ -76,15 +76,14 @@ namespace mgb
   {
     int             degree_fine = 1, degree_coarse = 1;
     long long       n_coarse_cells = 0;
-    const uint32_t *coarse_etab    = nullptr; // eval table of the coarse cells
-    const uint16_t *coarse_mask    = nullptr;
+    const uint32_t *coarse_ctab    = nullptr; // packed 32-word evaluation records of the coarse cells (CellData::ctab)
     int             coarse_any_hanging = 0;
+    bool            h_mode         = true;    // geometric (same degree, cell -> itself or 8 children) or polynomial (same cell)
     const uint32_t *fine_own       = nullptr; // own table of the fine cells
     const uint32_t *fine_first     = nullptr;
     const uint8_t  *n_children     = nullptr;
     const uint8_t  *weight_code    = nullptr; // per fine cell-entity
-    const double   *P_h            = nullptr; // device: (2pc+1) x (pc+1) h-embedding of the coarse degree
-    const double   *P_p            = nullptr; // device: (pf+1) x (pc+1) p-embedding (identity if pf==pc)
+    double          P[(2 * MAX_DEGREE + 1) * (MAX_DEGREE + 1)] = {}; // host: 1-D embedding, NF x (pc+1) row-major
   };
   template <typename T> void transfer_prolongate_add(const TransferData &td, T *dst_fine, const T *src_coarse, cudaStream_t s);
   template <typename T> void transfer_restrict_add(const TransferData &td, T *dst_coarse, const T *src_fine, cudaStream_t s);

@@ -1,222 +1,346 @@
 // Cell-wise two-level transfer kernels: MGTwoLevelTransfer::prolongate_and_add / restrict_and_add
-// (multigrid_throughput.cc:1600-1621).  One coarse cell per thread block:
-//   prolongation: gather coarse DoFs through the coarse evaluation table (Dirichlet -> 0, hanging-node
-//                 interpolation), 1-D embedding in x,y,z, multiply by the fine weights, scatter-add into
-//                 the fine cells' own DoFs;
-//   restriction : exact transpose.
-// Geometric transfer: the fine patch is the coarse cell itself (identity) or its 8 children
-// ((2p+1)^3 nodes, 1-D matrix P_h); polynomial transfer: same cell, 1-D matrix P_p.
-// HBM-bound gather/scatter kernels; runtime degrees (no template explosion over (p_f, p_c) pairs).
+// (multigrid_throughput.cc:1600-1621).
+//   prolongation: gather the coarse cell's DoFs through its evaluation record (Dirichlet -> 0, hanging-node
+//                 interpolation), 1-D embedding in x, y, z, multiply by the fine weights, add into the fine cells' own DoFs;
+//   restriction : the exact transpose.
+// Geometric (h) transfer: the fine patch of a coarse cell is the cell itself (identity) or its 8 Morton-contiguous
+// children ((2p+1)^3 nodes, 1-D matrix P_h); polynomial (p) transfer: the same cell at a higher degree (P_p).
+//
+// One persistent warp per coarse cell (4 warps per block, no block-level synchronisation after the prologue).  The x and
+// y embeddings run line-wise through shared memory; the z embedding runs in the column layout of the vmult kernel (lane
+// <-> one (I,J) column of the fine patch, values along z in registers) so that the fine-side scatter/gather goes
+// straight from/to registers, coalesced along the lexicographic fine node index.  The 1-D matrix is a kernel parameter
+// (constant bank), degrees are template parameters.  HBM-bound: s (N_c + 2 N_f) bytes per prolongation.
 #pragma once
 #include "cell_common.cuh"
 
+#include <algorithm>
+#include <stdexcept>
+
 namespace mgb
 {
-  constexpr int TRANSFER_THREADS = 128;
+  constexpr int TRANSFER_WARPS = 4;
 
-  __device__ __forceinline__ void node_to_entity_rt(const int P, int i, int j, int k, int &e, int &off)
+  template <typename T> struct TransferMat
   {
-    const int tx = i == 0 ? 0 : (i == P ? 2 : 1);
-    const int ty = j == 0 ? 0 : (j == P ? 2 : 1);
-    const int tz = k == 0 ? 0 : (k == P ? 2 : 1);
-    e            = tx + 3 * ty + 9 * tz;
-    int stride   = 1;
-    off          = 0;
-    if (tx == 1)
-      {
-        off += (i - 1);
-        stride = P - 1;
-      }
-    if (ty == 1)
-      {
-        off += (j - 1) * stride;
-        stride *= (P - 1);
-      }
-    if (tz == 1)
-      off += (k - 1) * stride;
+    T v[(2 * MAX_DEGREE + 1) * MAXN]; // NF x nc row-major with leading dimension nc
+  };
+
+  template <int PC, int PF, bool HMODE, typename T> struct TransferCfg
+  {
+    static constexpr int nc  = PC + 1;
+    static constexpr int NF  = HMODE ? 2 * PF + 1 : PF + 1;
+    static constexpr int PSC = SlabLayout<nc, sizeof(T)>::PS; // plane stride of the coarse cell storage (hanging_node_sweeps_slab)
+    static constexpr int n_C = nc * PSC, n_X = NF * nc * nc, n_XY = NF * NF * nc;
+    static constexpr int NCH = HMODE ? 8 : 1;
+    // per warp: values | fine weights (NCH*27 T) | coarse record (32 words) | fine own entries (NCH*27 words)
+    static constexpr size_t val_bytes  = (size_t(n_C + n_X + n_XY) * sizeof(T) + 15) / 16 * 16;
+    static constexpr size_t warp_bytes = (val_bytes + 32 * 4 + NCH * 27 * 4 + NCH * 27 * sizeof(T) + 15) / 16 * 16;
+    static constexpr size_t lut_bytes  = (size_t(nc * nc * nc) * 4 + 15) / 16 * 16;
+    static size_t           block_bytes() { return lut_bytes + TRANSFER_WARPS * warp_bytes; }
+  };
+
+  // fine patch coordinate along one axis -> (child bit, local node index, ternary entity digit)
+  template <int PF, bool HMODE> __device__ __forceinline__ void fine_axis(const int I, int &c, int &i, int &t)
+  {
+    c = (HMODE && I > PF) ? 1 : 0;
+    i = I - c * PF;
+    t = i == 0 ? 0 : (i == PF ? 2 : 1);
   }
 
-  // runtime-degree version of hanging_node_sweeps for one cell handled by the whole block
-  template <typename T, bool TRANSPOSE> __device__ void hanging_node_sweeps_rt(T *u, const int P, const unsigned mask)
-  {
-    const int n = P + 1, n2 = n * n;
-    for (int dd = 0; dd < 3; ++dd)
-      {
-        const int  d  = TRANSPOSE ? 2 - dd : dd;
-        const int  da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
-        const int  sa = (mask >> da) & 1, sb = (mask >> db) & 1, sd = (mask >> d) & 1;
-        const bool fa = (mask >> (3 + da)) & 1, fb = (mask >> (3 + db)) & 1, ed = (mask >> (6 + d)) & 1;
-        const double *S = c_fe[P].S[sd];
-        for (int t = threadIdx.x; t < n2; t += blockDim.x)
-          {
-            const int  a = t % n, b = t / n;
-            const bool on_a = (a == sa * P), on_b = (b == sb * P);
-            if ((fa && on_a) || (fb && on_b) || (ed && on_a && on_b))
-              {
-                const int base   = d == 0 ? (b * n + a) * n : (d == 1 ? b * n2 + a : b * n + a);
-                const int stride = d == 0 ? 1 : (d == 1 ? n : n2);
-                T         v[MAXN], r[MAXN];
-                for (int i = 0; i < n; ++i)
-                  v[i] = u[base + i * stride];
-                for (int i = 0; i < n; ++i)
-                  {
-                    T acc = 0;
-                    for (int j = 0; j < n; ++j)
-                      acc += T(TRANSPOSE ? S[j * MAXN + i] : S[i * MAXN + j]) * v[j];
-                    r[i] = acc;
-                  }
-                for (int i = 0; i < n; ++i)
-                  u[base + i * stride] = r[i];
-              }
-          }
-        __syncthreads();
-      }
-  }
-
-  // out[(c*NO + I)*..] 1-D product along one direction of a 3-index array.
-  // in: [n2][n1][n0], apply along dimension `dim` a matrix Pm (NO x NI, row-major) or its transpose.
-  template <typename T, bool TRANSPOSE>
-  __device__ void sweep_rt(const T *in, T *out, const double *Pm, const int rows, const int cols, const int dim, const int n0,
-                           const int n1, const int n2)
-  {
-    // input extent along dim is NI = TRANSPOSE ? rows : cols ; output extent NO = TRANSPOSE ? cols : rows
-    const int NI = TRANSPOSE ? rows : cols, NO = TRANSPOSE ? cols : rows;
-    const int o0 = dim == 0 ? NO : n0, o1 = dim == 1 ? NO : n1, o2 = dim == 2 ? NO : n2;
-    const int total = o0 * o1 * o2;
-    for (int q = threadIdx.x; q < total; q += blockDim.x)
-      {
-        const int i0 = q % o0, i1 = (q / o0) % o1, i2 = q / (o0 * o1);
-        const int I  = dim == 0 ? i0 : (dim == 1 ? i1 : i2);
-        T         acc = 0;
-        for (int l = 0; l < NI; ++l)
-          {
-            const int j0 = dim == 0 ? l : i0, j1 = dim == 1 ? l : i1, j2 = dim == 2 ? l : i2;
-            const T   m  = T(TRANSPOSE ? Pm[l * cols + I] : Pm[I * cols + l]);
-            acc += m * in[(j2 * n1 + j1) * n0 + j0];
-          }
-        out[q] = acc;
-      }
-    __syncthreads();
-  }
-
-  template <typename T, bool PROLONGATE>
-  __global__ void __launch_bounds__(TRANSFER_THREADS)
-    k_transfer(const int PC, const int PF, const uint32_t *__restrict__ coarse_etab, const uint16_t *__restrict__ coarse_mask,
+  template <int PC, int PF, bool HMODE, bool PROLONGATE, typename T>
+  __global__ void __launch_bounds__(TRANSFER_WARPS * 32)
+    k_transfer(const long long n_coarse, const uint32_t *__restrict__ coarse_ctab, const int coarse_any_hanging,
                const uint32_t *__restrict__ fine_own, const uint32_t *__restrict__ fine_first, const uint8_t *__restrict__ n_children,
-               const uint8_t *__restrict__ weight_code, const double *__restrict__ P_h, const double *__restrict__ P_p,
-               T *__restrict__ dst, const T *__restrict__ src)
+               const uint8_t *__restrict__ weight_code, const __grid_constant__ TransferMat<T> Pm, T *__restrict__ dst,
+               const T *__restrict__ src)
   {
+    using Cfg = TransferCfg<PC, PF, HMODE, T>;
+    constexpr int nc = Cfg::nc, NF = Cfg::NF, PSC = Cfg::PSC, nc3 = nc * nc * nc;
+    constexpr int NRC = (NF * NF + 31) / 32; // column rounds
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    T *smem = reinterpret_cast<T *>(smem_raw);
-    __shared__ uint32_t stab[27];
+    uint32_t      *slut  = reinterpret_cast<uint32_t *>(smem_raw); // coarse node q -> entity<<24 | offset<<16 | address in C
+    const int      warp  = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned char *wbase = smem_raw + Cfg::lut_bytes + warp * Cfg::warp_bytes;
+    T             *C     = reinterpret_cast<T *>(wbase);
+    T             *X     = C + Cfg::n_C;
+    T             *XY    = X + Cfg::n_X;
+    T             *sw    = reinterpret_cast<T *>(wbase + Cfg::val_bytes);
+    uint32_t      *srec  = reinterpret_cast<uint32_t *>(sw + Cfg::NCH * 27);
+    uint32_t      *sfo   = srec + 32;
 
-    const long long c    = blockIdx.x;
-    const int       nc   = PC + 1;
-    const int       nch  = n_children[c];
-    const bool      hx   = nch == 8;                 // h-embedding into 8 children
-    const bool      ident = (!hx) && PF == PC;       // same cell, same degree
-    const int       NF   = hx ? 2 * PF + 1 : PF + 1; // 1-D size of the fine patch
-    const double   *Pm   = hx ? P_h : P_p;           // NF x nc
-    const unsigned  mask = coarse_mask ? coarse_mask[c] : 0u;
-    const uint32_t  f0   = fine_first[c];
-
-    T *bufC = smem;                    // nc^3
-    T *buf1 = bufC + nc * nc * nc;     // NF*nc*nc
-    T *buf2 = buf1 + NF * nc * nc;     // NF*NF*nc
-    T *bufF = buf2 + NF * NF * nc;     // NF^3
-
-    if (threadIdx.x < 27)
-      stab[threadIdx.x] = coarse_etab[c * 27 + threadIdx.x];
+    for (int q = threadIdx.x; q < nc3; q += TRANSFER_WARPS * 32)
+      {
+        const int i = q % nc, j = (q / nc) % nc, k = q / (nc * nc);
+        int       e, off;
+        node_to_entity<PC>(i, j, k, e, off);
+        slut[q] = (uint32_t(e) << 24) | (uint32_t(off) << 16) | uint32_t(k * PSC + j * nc + i);
+      }
     __syncthreads();
 
-    // fine patch node -> (index, weight)
-    const auto fine_node = [&](int q, uint32_t &idx, T &w) {
-      const int I = q % NF, J = (q / NF) % NF, K = q / (NF * NF);
-      int       cx = 0, cy = 0, cz = 0, i = I, j = J, k = K;
-      if (hx)
-        {
-          cx = I > PF, cy = J > PF, cz = K > PF;
-          i -= cx * PF, j -= cy * PF, k -= cz * PF;
-        }
-      int e, off;
-      node_to_entity_rt(PF, i, j, k, e, off);
-      const size_t   slot = (size_t(f0) + cx + 2 * cy + 4 * cz) * 27 + e;
-      const unsigned code = weight_code[slot];
-      idx                 = (fine_own[slot] & D_INDEX_MASK) + off;
-      w                   = code ? T(1) / T(code) : T(0);
+    // fine node (I,J,K) -> slot in the per-warp fine tables and offset inside the entity
+    const auto fine_slot = [&](const int I, const int J, const int K, int &slot, int &off) {
+      int cx, cy, cz, i, j, k, tx, ty, tz;
+      fine_axis<PF, HMODE>(I, cx, i, tx);
+      fine_axis<PF, HMODE>(J, cy, j, ty);
+      fine_axis<PF, HMODE>(K, cz, k, tz);
+      const int sx = tx == 1 ? PF - 1 : 1, sy = ty == 1 ? PF - 1 : 1;
+      slot = (cx + 2 * cy + 4 * cz) * 27 + tx + 3 * ty + 9 * tz;
+      off  = (tx == 1 ? i - 1 : 0) + (ty == 1 ? (j - 1) * sx : 0) + (tz == 1 ? (k - 1) * sx * sy : 0);
     };
 
-    if (PROLONGATE)
+    for (long long c = (long long)blockIdx.x * TRANSFER_WARPS + warp; c < n_coarse; c += (long long)gridDim.x * TRANSFER_WARPS)
       {
-        for (int q = threadIdx.x; q < nc * nc * nc; q += blockDim.x)
+        // ---- tables
+        const int nch = HMODE ? n_children[c] : 1;
+        srec[lane]    = coarse_ctab[c * 32 + lane];
+        {
+          const size_t f0 = size_t(fine_first[c]) * 27;
+          for (int idx = lane; idx < nch * 27; idx += 32)
+            {
+              sfo[idx]            = fine_own[f0 + idx] & D_INDEX_MASK;
+              const unsigned code = weight_code[f0 + idx];
+              sw[idx]             = code ? T(1) / T(code) : T(0);
+            }
+        }
+        __syncwarp();
+        const unsigned mask  = coarse_any_hanging ? (srec[27] & 0xffffu) : 0u;
+        const bool     ident = HMODE && nch == 1;
+
+        if (PROLONGATE)
           {
-            const int i = q % nc, j = (q / nc) % nc, k = q / (nc * nc);
-            int       e, off;
-            node_to_entity_rt(PC, i, j, k, e, off);
-            const uint32_t tb = stab[e];
-            bufC[q]           = (tb & D_FLAG_BIT) ? T(0) : src[(tb & D_INDEX_MASK) + off];
+#pragma unroll
+            for (int q = lane; q < nc3; q += 32)
+              {
+                const uint32_t lut = slut[q];
+                const uint32_t tb  = srec[lut >> 24];
+                C[lut & 0xffffu]   = (tb & D_FLAG_BIT) ? T(0) : src[(tb & D_INDEX_MASK) + ((lut >> 16) & 0xffu)];
+              }
+            __syncwarp();
+            if (mask >> 3)
+              hanging_node_sweeps_slab<PC, T, false>(C, srec, 1, lane);
+            if (ident)
+              {
+                for (int q = lane; q < nc3; q += 32)
+                  {
+                    const uint32_t lut = slut[q];
+                    const T        w   = sw[lut >> 24];
+                    if (w != T(0))
+                      atomic_add(dst + sfo[lut >> 24] + ((lut >> 16) & 0xffu), w * C[lut & 0xffffu]);
+                  }
+              }
+            else
+              {
+                // x: lines (j,k)
+                for (int ln = lane; ln < nc * nc; ln += 32)
+                  {
+                    const int j = ln % nc, k = ln / nc;
+                    T         v[nc];
+#pragma unroll
+                    for (int l = 0; l < nc; ++l)
+                      v[l] = C[k * PSC + j * nc + l];
+#pragma unroll
+                    for (int I = 0; I < NF; ++I)
+                      {
+                        T acc = Pm.v[I * nc] * v[0];
+#pragma unroll
+                        for (int l = 1; l < nc; ++l)
+                          acc += Pm.v[I * nc + l] * v[l];
+                        X[ln * NF + I] = acc;
+                      }
+                  }
+                __syncwarp();
+                // y: lines (I,k)
+                for (int ln = lane; ln < NF * nc; ln += 32)
+                  {
+                    const int I = ln % NF, k = ln / NF;
+                    T         v[nc];
+#pragma unroll
+                    for (int l = 0; l < nc; ++l)
+                      v[l] = X[(k * nc + l) * NF + I];
+#pragma unroll
+                    for (int J = 0; J < NF; ++J)
+                      {
+                        T acc = Pm.v[J * nc] * v[0];
+#pragma unroll
+                        for (int l = 1; l < nc; ++l)
+                          acc += Pm.v[J * nc + l] * v[l];
+                        XY[(k * NF + J) * NF + I] = acc;
+                      }
+                  }
+                __syncwarp();
+                // z in the column layout + weighted scatter-add
+#pragma unroll
+                for (int r = 0; r < NRC; ++r)
+                  {
+                    const int col = r * 32 + lane;
+                    if (col < NF * NF)
+                      {
+                        const int I = col % NF, J = col / NF;
+                        T         v[nc];
+#pragma unroll
+                        for (int l = 0; l < nc; ++l)
+                          v[l] = XY[l * NF * NF + col];
+#pragma unroll
+                        for (int K = 0; K < NF; ++K)
+                          {
+                            T acc = Pm.v[K * nc] * v[0];
+#pragma unroll
+                            for (int l = 1; l < nc; ++l)
+                              acc += Pm.v[K * nc + l] * v[l];
+                            int slot, off;
+                            fine_slot(I, J, K, slot, off);
+                            const T w = sw[slot];
+                            if (w != T(0))
+                              atomic_add(dst + sfo[slot] + off, w * acc);
+                          }
+                      }
+                  }
+              }
           }
-        __syncthreads();
-        if (mask >> 3)
-          hanging_node_sweeps_rt<T, false>(bufC, PC, mask);
-        const T *fine = bufC;
-        if (!ident)
+        else
           {
-            sweep_rt<T, false>(bufC, buf1, Pm, NF, nc, 0, nc, nc, nc);
-            sweep_rt<T, false>(buf1, buf2, Pm, NF, nc, 1, NF, nc, nc);
-            sweep_rt<T, false>(buf2, bufF, Pm, NF, nc, 2, NF, NF, nc);
-            fine = bufF;
+            if (ident)
+              {
+                for (int q = lane; q < nc3; q += 32)
+                  {
+                    const uint32_t lut = slut[q];
+                    const T        w   = sw[lut >> 24];
+                    C[lut & 0xffffu]   = (w != T(0)) ? w * src[sfo[lut >> 24] + ((lut >> 16) & 0xffu)] : T(0);
+                  }
+              }
+            else
+              {
+#pragma unroll
+                for (int r = 0; r < NRC; ++r)
+                  {
+                    const int col = r * 32 + lane;
+                    if (col < NF * NF)
+                      {
+                        const int I = col % NF, J = col / NF;
+                        T         f[NF];
+#pragma unroll
+                        for (int K = 0; K < NF; ++K)
+                          {
+                            int slot, off;
+                            fine_slot(I, J, K, slot, off);
+                            const T w = sw[slot];
+                            f[K]      = (w != T(0)) ? w * src[sfo[slot] + off] : T(0);
+                          }
+#pragma unroll
+                        for (int l = 0; l < nc; ++l)
+                          {
+                            T acc = Pm.v[l] * f[0];
+#pragma unroll
+                            for (int K = 1; K < NF; ++K)
+                              acc += Pm.v[K * nc + l] * f[K];
+                            XY[l * NF * NF + col] = acc;
+                          }
+                      }
+                  }
+                __syncwarp();
+                for (int ln = lane; ln < NF * nc; ln += 32)
+                  {
+                    const int I = ln % NF, k = ln / NF;
+                    T         f[NF];
+#pragma unroll
+                    for (int J = 0; J < NF; ++J)
+                      f[J] = XY[(k * NF + J) * NF + I];
+#pragma unroll
+                    for (int l = 0; l < nc; ++l)
+                      {
+                        T acc = Pm.v[l] * f[0];
+#pragma unroll
+                        for (int J = 1; J < NF; ++J)
+                          acc += Pm.v[J * nc + l] * f[J];
+                        X[(k * nc + l) * NF + I] = acc;
+                      }
+                  }
+                __syncwarp();
+                for (int ln = lane; ln < nc * nc; ln += 32)
+                  {
+                    const int j = ln % nc, k = ln / nc;
+                    T         f[NF];
+#pragma unroll
+                    for (int I = 0; I < NF; ++I)
+                      f[I] = X[ln * NF + I];
+#pragma unroll
+                    for (int l = 0; l < nc; ++l)
+                      {
+                        T acc = Pm.v[l] * f[0];
+#pragma unroll
+                        for (int I = 1; I < NF; ++I)
+                          acc += Pm.v[I * nc + l] * f[I];
+                        C[k * PSC + j * nc + l] = acc;
+                      }
+                  }
+              }
+            __syncwarp();
+            if (mask >> 3)
+              hanging_node_sweeps_slab<PC, T, true>(C, srec, 1, lane);
+#pragma unroll
+            for (int q = lane; q < nc3; q += 32)
+              {
+                const uint32_t lut = slut[q];
+                const uint32_t tb  = srec[lut >> 24];
+                if (!(tb & D_FLAG_BIT))
+                  atomic_add(dst + (tb & D_INDEX_MASK) + ((lut >> 16) & 0xffu), C[lut & 0xffffu]);
+              }
           }
-        for (int q = threadIdx.x; q < NF * NF * NF; q += blockDim.x)
-          {
-            uint32_t idx;
-            T        w;
-            fine_node(q, idx, w);
-            if (w != T(0))
-              atomic_add(dst + idx, w * fine[q]);
-          }
+        __syncwarp(); // tables and value buffers are rewritten by the next coarse cell
       }
-    else
+  }
+
+  template <int PC, int PF, bool HMODE, bool PROLONGATE, typename T>
+  void launch_transfer_t(const TransferData &td, T *dst, const T *src, cudaStream_t s)
+  {
+    using Cfg = TransferCfg<PC, PF, HMODE, T>;
+    const size_t smem = Cfg::block_bytes();
+    static int   blocks_per_sm = 0, n_sm = 0; // per instantiation
+    if (blocks_per_sm == 0)
       {
-        T *fine = ident ? bufC : bufF;
-        for (int q = threadIdx.x; q < NF * NF * NF; q += blockDim.x)
-          {
-            uint32_t idx;
-            T        w;
-            fine_node(q, idx, w);
-            fine[q] = (w != T(0)) ? w * src[idx] : T(0);
-          }
-        __syncthreads();
-        if (!ident)
-          {
-            sweep_rt<T, true>(bufF, buf2, Pm, NF, nc, 2, NF, NF, NF);
-            sweep_rt<T, true>(buf2, buf1, Pm, NF, nc, 1, NF, NF, nc);
-            sweep_rt<T, true>(buf1, bufC, Pm, NF, nc, 0, NF, nc, nc);
-          }
-        if (mask >> 3)
-          hanging_node_sweeps_rt<T, true>(bufC, PC, mask);
-        for (int q = threadIdx.x; q < nc * nc * nc; q += blockDim.x)
-          {
-            const int i = q % nc, j = (q / nc) % nc, k = q / (nc * nc);
-            int       e, off;
-            node_to_entity_rt(PC, i, j, k, e, off);
-            const uint32_t tb = stab[e];
-            if (!(tb & D_FLAG_BIT))
-              atomic_add(dst + (tb & D_INDEX_MASK) + off, bufC[q]);
-          }
+        int dev = 0;
+        MGB_CUDA(cudaGetDevice(&dev));
+        MGB_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+        MGB_CUDA(cudaFuncSetAttribute(k_transfer<PC, PF, HMODE, PROLONGATE, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_transfer<PC, PF, HMODE, PROLONGATE, T>,
+                                                               TRANSFER_WARPS * 32, smem));
+        if (blocks_per_sm < 1)
+          throw std::runtime_error("k_transfer does not fit on an SM");
       }
+    TransferMat<T> Pm{};
+    for (int I = 0; I < Cfg::NF; ++I)
+      for (int l = 0; l < Cfg::nc; ++l)
+        Pm.v[I * Cfg::nc + l] = T(td.P[I * Cfg::nc + l]);
+    const long long blocks =
+      std::min<long long>((td.n_coarse_cells + TRANSFER_WARPS - 1) / TRANSFER_WARPS, (long long)blocks_per_sm * n_sm);
+    k_transfer<PC, PF, HMODE, PROLONGATE, T><<<(unsigned)blocks, TRANSFER_WARPS * 32, smem, s>>>(
+      td.n_coarse_cells, td.coarse_ctab, td.coarse_any_hanging, td.fine_own, td.fine_first, td.n_children, td.weight_code, Pm, dst, src);
+    MGB_CUDA(cudaGetLastError());
   }
 
   template <typename T, bool PROLONGATE> void launch_transfer(const TransferData &td, T *dst, const T *src, cudaStream_t s)
   {
     if (td.n_coarse_cells <= 0)
       return;
-    const int    nc = td.degree_coarse + 1;
-    const int    NF = std::max(2 * td.degree_fine + 1, td.degree_fine + 1);
-    const size_t sh = sizeof(T) * size_t(nc * nc * nc + NF * nc * nc + NF * NF * nc + NF * NF * NF);
-    k_transfer<T, PROLONGATE><<<(unsigned)td.n_coarse_cells, TRANSFER_THREADS, sh, s>>>(
-      td.degree_coarse, td.degree_fine, td.coarse_etab, td.coarse_any_hanging ? td.coarse_mask : nullptr, td.fine_own, td.fine_first,
-      td.n_children, td.weight_code, td.P_h, td.P_p, dst, src);
-    MGB_CUDA(cudaGetLastError());
+    const int pf = td.degree_fine, pc = td.degree_coarse;
+#define MGB_TRANSFER_CASE(PC_, PF_, H_)                                   \
+  if (pc == PC_ && pf == PF_ && td.h_mode == H_)                          \
+    return launch_transfer_t<PC_, PF_, H_, PROLONGATE, T>(td, dst, src, s);
+    MGB_TRANSFER_CASE(1, 1, true)
+    MGB_TRANSFER_CASE(2, 2, true)
+    MGB_TRANSFER_CASE(3, 3, true)
+    MGB_TRANSFER_CASE(4, 4, true)
+    MGB_TRANSFER_CASE(5, 5, true)
+    MGB_TRANSFER_CASE(6, 6, true)
+    // polynomial transfers of create_polynomial_coarsening_sequence(p, bisect) (multigrid_throughput.cc:1506-1510)
+    MGB_TRANSFER_CASE(1, 2, false)
+    MGB_TRANSFER_CASE(1, 3, false)
+    MGB_TRANSFER_CASE(2, 4, false)
+    MGB_TRANSFER_CASE(2, 5, false)
+    MGB_TRANSFER_CASE(3, 6, false)
+#undef MGB_TRANSFER_CASE
+    throw std::runtime_error("two-level transfer: unsupported degree pair (fine " + std::to_string(pf) + ", coarse " + std::to_string(pc) +
+                             (td.h_mode ? ", geometric)" : ", polynomial)"));
   }
 } // namespace mgb

@@ -447,22 +447,20 @@ namespace mgb
     fine_first_.upload(tm.fine_first.data(), tm.fine_first.size());
     n_children_.upload(tm.n_children.data(), tm.n_children.size());
     weight_code_.upload(tm.weight_code.data(), tm.weight_code.size());
-    FE1D fec(coarse.degree);
-    Ph_.upload(fec.Ph.data(), fec.Ph.size());
-    const auto pp = p_embedding(fine.degree, coarse.degree);
-    Pp_.upload(pp.data(), pp.size());
     td_.degree_fine        = fine.degree;
     td_.degree_coarse      = coarse.degree;
+    td_.h_mode             = fine.degree == coarse.degree;
     td_.n_coarse_cells     = tm.n_coarse_cells;
-    td_.coarse_etab        = op_coarse.cell_data().etab;
-    td_.coarse_mask        = op_coarse.cell_data().mask;
+    td_.coarse_ctab        = op_coarse.cell_data().ctab;
     td_.coarse_any_hanging = op_coarse.cell_data().any_hanging;
     td_.fine_own           = fine_own_.ptr;
     td_.fine_first         = fine_first_.ptr;
     td_.n_children         = n_children_.ptr;
     td_.weight_code        = weight_code_.ptr;
-    td_.P_h                = Ph_.ptr;
-    td_.P_p                = Pp_.ptr;
+    {
+      const std::vector<double> P = td_.h_mode ? FE1D(coarse.degree).Ph : p_embedding(fine.degree, coarse.degree);
+      std::copy(P.begin(), P.end(), td_.P);
+    }
     if (fine.degree != coarse.degree)
       for (uint8_t nchild : tm.n_children)
         if (nchild != 1)

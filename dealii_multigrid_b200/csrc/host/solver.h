@@ -400,7 +400,6 @@ namespace mgb
     TransferData           td_;
     DeviceBuffer<uint32_t> fine_own_, fine_first_;
     DeviceBuffer<uint8_t>  n_children_, weight_code_;
-    DeviceBuffer<double>   Ph_, Pp_;
     const OperatorT<T>    &op_fine_, &op_coarse_;
   };
 
