@@ -30,10 +30,15 @@ namespace mgb
   // g += a h; result = g.g   (SolverCG's add_and_dot with w == g)
   template <typename T> void vec_add_and_dot(T *g, T a, const T *h, size_t n, double *result_dev, double *scratch,
                                              unsigned *ticket, cudaStream_t s);
+  // x += a d; g += a h; result = g.g   (the two vector updates of one CG iteration in one pass)
+  template <typename T>
+  void vec_cg_update(T *x, T *g, T a, const T *d, const T *h, size_t n, double *result_dev, double *scratch, unsigned *ticket,
+                     cudaStream_t s);
   int reduction_scratch_size(); // number of doubles `scratch` must hold
 
   // gather / scatter by index lists (identity rows, edge DoFs, ghost pack/unpack, copy_indices)
   template <typename T> void idx_copy(T *dst, const T *src, const uint32_t *idx, uint32_t n, cudaStream_t s); // dst[idx]=src[idx]
+  template <typename T> void idx_residual(T *dst, const T *a, const T *b, const uint32_t *idx, uint32_t n, cudaStream_t s); // dst[idx]=a[idx]-b[idx]
   template <typename T> void idx_gather(T *buf, const T *src, const uint32_t *idx, uint32_t n, cudaStream_t s); // buf[i]=src[idx[i]]
   template <typename T> void idx_scatter(T *dst, const T *buf, const uint32_t *idx, uint32_t n, cudaStream_t s); // dst[idx[i]]=buf[i]
   template <typename T> void idx_scatter_add(T *dst, const T *buf, const uint32_t *idx, uint32_t n, cudaStream_t s);
@@ -42,12 +47,12 @@ namespace mgb
   void idx_pair_copy(T *dst, const uint32_t *dst_idx, const U *src, const uint32_t *src_idx, uint32_t n, cudaStream_t s);
 
   // Chebyshev vector update (PreconditionChebyshev's vector_updates):
-  //   it==0: x = f2 dinv rhs
-  //   it==1: x_new = (1+f1) x + f2 dinv (rhs - t)
-  //   it>=2: x_new = (1+f1) x - f1 x_old + f2 dinv (rhs - t)
-  // x_new is written into x_old's storage (caller swaps pointers)
+  //   it==0: out = f2 dinv rhs
+  //   it==1: out = (1+f1) x + f2 dinv (rhs - t)
+  //   it>=2: out = (1+f1) x - f1 x_old + f2 dinv (rhs - t)
+  // `out` may alias x or x_old (pointwise update)
   template <typename T>
-  void cheb_update(int it, T f1, T f2, const T *rhs, const T *dinv, const T *t, const T *x, T *x_old, size_t n,
+  void cheb_update(int it, T f1, T f2, const T *rhs, const T *dinv, const T *t, const T *x, const T *x_old, T *out, size_t n,
                    cudaStream_t s);
   // d = (|d| > 1e-10) ? 1/d : 1   (include/operator.h:240-241)
   template <typename T> void invert_diagonal(T *d, size_t n, cudaStream_t s);

@@ -151,6 +151,29 @@ namespace mgb
       block_reduce_and_finish(v, result, scratch, ticket);
     }
 
+    // SolverCG's two vector updates of one iteration in one pass: x += a d;  g += a h;  result = g.g
+    template <typename T>
+    __global__ void __launch_bounds__(BLOCK) k_cg_update(T *__restrict__ x, T *__restrict__ g, T a, const T *__restrict__ d,
+                                                         const T *__restrict__ h, size_t n, double *result, double *scratch, unsigned *ticket)
+    {
+      double v = 0;
+      for (size_t i = blockIdx.x * size_t(BLOCK) + threadIdx.x; i < n; i += size_t(gridDim.x) * BLOCK)
+        {
+          x[i] += a * d[i];
+          const T gi = g[i] + a * h[i];
+          g[i]       = gi;
+          v += double(gi) * double(gi);
+        }
+      block_reduce_and_finish(v, result, scratch, ticket);
+    }
+    template <typename T>
+    __global__ void k_idx_residual(T *__restrict__ dst, const T *__restrict__ a, const T *__restrict__ b, const uint32_t *__restrict__ idx, uint32_t n)
+    {
+      const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+      if (i < n)
+        dst[idx[i]] = a[idx[i]] - b[idx[i]];
+    }
+
     template <typename T> __global__ void k_idx_copy(T *__restrict__ dst, const T *__restrict__ src, const uint32_t *__restrict__ idx, uint32_t n)
     {
       const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -189,18 +212,19 @@ namespace mgb
         dst[di[i]] = T(src[si[i]]);
     }
 
+    // out may alias x or x_old (the update is pointwise), hence no __restrict__ on those
     template <typename T, int IT>
-    __global__ void k_cheb(T f1, T f2, const T *__restrict__ rhs, const T *__restrict__ dinv, const T *__restrict__ t,
-                           const T *__restrict__ x, T *__restrict__ x_old, size_t n)
+    __global__ void k_cheb(T f1, T f2, const T *__restrict__ rhs, const T *__restrict__ dinv, const T *__restrict__ t, const T *x,
+                           const T *x_old, T *out, size_t n)
     {
       for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
         {
           if (IT == 0)
-            x_old[i] = f2 * (dinv[i] * rhs[i]);
+            out[i] = f2 * (dinv[i] * rhs[i]);
           else if (IT == 1)
-            x_old[i] = (T(1) + f1) * x[i] + f2 * (dinv[i] * (rhs[i] - t[i]));
+            out[i] = (T(1) + f1) * x[i] + f2 * (dinv[i] * (rhs[i] - t[i]));
           else
-            x_old[i] = (T(1) + f1) * x[i] - f1 * x_old[i] + f2 * (dinv[i] * (rhs[i] - t[i]));
+            out[i] = (T(1) + f1) * x[i] - f1 * x_old[i] + f2 * (dinv[i] * (rhs[i] - t[i]));
         }
     }
     template <typename T> __global__ void k_invert_diag(T *__restrict__ d, size_t n)
@@ -264,6 +288,13 @@ namespace mgb
     MGB_CUDA(cudaGetLastError());
   }
 
+  template <typename T>
+  void vec_cg_update(T *x, T *g, T a, const T *d, const T *h, size_t n, double *result_dev, double *scratch, unsigned *ticket, cudaStream_t s)
+  {
+    k_cg_update<T><<<RED_BLOCKS, BLOCK, 0, s>>>(x, g, a, d, h, n, result_dev, scratch, ticket);
+    MGB_CUDA(cudaGetLastError());
+  }
+
 #define LAUNCH_IDX(kernel, n, ...)                                         \
   do                                                                       \
     {                                                                      \
@@ -276,6 +307,7 @@ namespace mgb
   while (0)
 
   template <typename T> void idx_copy(T *dst, const T *src, const uint32_t *idx, uint32_t n, cudaStream_t s) { LAUNCH_IDX(k_idx_copy<T>, n, dst, src, idx, n); }
+  template <typename T> void idx_residual(T *dst, const T *a, const T *b, const uint32_t *idx, uint32_t n, cudaStream_t s) { LAUNCH_IDX(k_idx_residual<T>, n, dst, a, b, idx, n); }
   template <typename T> void idx_gather(T *buf, const T *src, const uint32_t *idx, uint32_t n, cudaStream_t s) { LAUNCH_IDX(k_idx_gather<T>, n, buf, src, idx, n); }
   template <typename T> void idx_scatter(T *dst, const T *buf, const uint32_t *idx, uint32_t n, cudaStream_t s) { LAUNCH_IDX(k_idx_scatter<T>, n, dst, buf, idx, n); }
   template <typename T> void idx_scatter_add(T *dst, const T *buf, const uint32_t *idx, uint32_t n, cudaStream_t s) { LAUNCH_IDX(k_idx_scatter_add<T>, n, dst, buf, idx, n); }
@@ -287,14 +319,15 @@ namespace mgb
   }
 
   template <typename T>
-  void cheb_update(int it, T f1, T f2, const T *rhs, const T *dinv, const T *t, const T *x, T *x_old, size_t n, cudaStream_t s)
+  void cheb_update(int it, T f1, T f2, const T *rhs, const T *dinv, const T *t, const T *x, const T *x_old, T *out, size_t n,
+                   cudaStream_t s)
   {
     if (it == 0)
-      LAUNCH_STREAM((k_cheb<T, 0>), n, f1, f2, rhs, dinv, t, x, x_old, n);
+      LAUNCH_STREAM((k_cheb<T, 0>), n, f1, f2, rhs, dinv, t, x, x_old, out, n);
     else if (it == 1)
-      LAUNCH_STREAM((k_cheb<T, 1>), n, f1, f2, rhs, dinv, t, x, x_old, n);
+      LAUNCH_STREAM((k_cheb<T, 1>), n, f1, f2, rhs, dinv, t, x, x_old, out, n);
     else
-      LAUNCH_STREAM((k_cheb<T, 2>), n, f1, f2, rhs, dinv, t, x, x_old, n);
+      LAUNCH_STREAM((k_cheb<T, 2>), n, f1, f2, rhs, dinv, t, x, x_old, out, n);
   }
   template <typename T> void invert_diagonal(T *d, size_t n, cudaStream_t s) { LAUNCH_STREAM(k_invert_diag<T>, n, d, n); }
 
@@ -310,11 +343,13 @@ namespace mgb
   template void vec_sum<T>(const T *, size_t, double *, double *, unsigned *, cudaStream_t);                          \
   template void vec_add_and_dot<T>(T *, T, const T *, size_t, double *, double *, unsigned *, cudaStream_t);          \
   template void idx_copy<T>(T *, const T *, const uint32_t *, uint32_t, cudaStream_t);                                \
+  template void idx_residual<T>(T *, const T *, const T *, const uint32_t *, uint32_t, cudaStream_t);                 \
+  template void vec_cg_update<T>(T *, T *, T, const T *, const T *, size_t, double *, double *, unsigned *, cudaStream_t); \
   template void idx_gather<T>(T *, const T *, const uint32_t *, uint32_t, cudaStream_t);                              \
   template void idx_scatter<T>(T *, const T *, const uint32_t *, uint32_t, cudaStream_t);                             \
   template void idx_scatter_add<T>(T *, const T *, const uint32_t *, uint32_t, cudaStream_t);                         \
   template void idx_set<T>(T *, T, const uint32_t *, uint32_t, cudaStream_t);                                         \
-  template void cheb_update<T>(int, T, T, const T *, const T *, const T *, const T *, T *, size_t, cudaStream_t);     \
+  template void cheb_update<T>(int, T, T, const T *, const T *, const T *, const T *, const T *, T *, size_t, cudaStream_t); \
   template void invert_diagonal<T>(T *, size_t, cudaStream_t);
   INST(double)
   INST(float)

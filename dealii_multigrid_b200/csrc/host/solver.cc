@@ -99,6 +99,13 @@ namespace mgb
     ++c.launches;
     return finish_reduction();
   }
+  template <typename T> double DVec<T>::cg_update(DVec &x, T a, const DVec &d, const DVec &h)
+  {
+    Context &c = ctx();
+    vec_cg_update<T>(x.data, data, a, d.data, h.data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    ++c.launches;
+    return finish_reduction();
+  }
   template <typename T> double DVec<T>::mean_value(long long n_global) const
   {
     Context &c = ctx();
@@ -248,21 +255,23 @@ namespace mgb
     part_ = std::make_shared<DevicePartitioner>(*s.partitioner);
   }
 
-  template <typename T> void OperatorT<T>::cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_only) const
+  template <typename T> void OperatorT<T>::cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_only, double alpha) const
   {
-    Context &c = ctx();
+    Context &c  = ctx();
+    CellData cd = cd_;
+    cd.root_length *= alpha; // the cell matrices are linear in h = root_length / 2^level
     src.update_ghost_values();
     if (zero_dst)
       dst.zero();
     if (edge_only)
       {
         if (edge_cells_.n)
-          cell_laplace_apply<T>(cd_, src.data, dst.data, edge_cells_.ptr, (long long)edge_cells_.n, c.stream), ++c.launches;
+          cell_laplace_apply<T>(cd, src.data, dst.data, edge_cells_.ptr, (long long)edge_cells_.n, c.stream), ++c.launches;
       }
     else
       {
         c.prof_begin(cd_.n_cells);
-        cell_laplace_apply<T>(cd_, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
+        cell_laplace_apply<T>(cd, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
         c.prof_end(cd_.n_cells);
       }
     dst.compress_add();
@@ -297,6 +306,15 @@ namespace mgb
     cell_loop(dst, src, true, false);
     if (constrained_.n)
       idx_copy<T>(dst.data, src.data, constrained_.ptr, (uint32_t)constrained_.n, c.stream), ++c.launches;
+  }
+
+  template <typename T> void OperatorT<T>::residual_interface_down(DVec<T> &dst, const DVec<T> &b, const DVec<T> &src) const
+  {
+    Context &c = ctx();
+    dst.copy_from(b);
+    cell_loop(dst, src, false, false, -1.0);
+    if (constrained_.n)
+      idx_residual<T>(dst.data, b.data, src.data, constrained_.ptr, (uint32_t)constrained_.n, c.stream), ++c.launches;
   }
 
   template <typename T> void OperatorT<T>::vmult_interface_up(DVec<T> &dst, const DVec<T> &src) const
@@ -366,7 +384,7 @@ namespace mgb
     std::vector<double> diag, off;
     const auto          A = [this](DVec<T> &d, const DVec<T> &s) { op_.vmult(d, s); };
     const auto          P = [this, &c](DVec<T> &d, const DVec<T> &s) {
-      cheb_update<T>(0, T(0), T(1), s.data, dinv_.data, nullptr, nullptr, d.data, d.n_owned, c.stream);
+      cheb_update<T>(0, T(0), T(1), s.data, dinv_.data, nullptr, nullptr, nullptr, d.data, d.n_owned, c.stream);
       ++c.launches;
     };
     cg_solve<T>(A, P, false, solution_old_, temp1_, ctl, cgw_, /*x_is_zero=*/true, &diag, &off);
@@ -387,52 +405,59 @@ namespace mgb
     eig_done_ = true;
   }
 
-  template <typename T> void ChebyshevT<T>::vmult(DVec<T> &dst, const DVec<T> &rhs)
+  // PreconditionChebyshev::vmult (zero initial guess) and ::step, SURVEY.md A.4.  deal.II swaps the iterate with
+  // solution_old after every update; here the updates alternate between dst and solution_old_ and the LAST one always
+  // writes into dst (pointwise update: it may overwrite either input), so the caller's vector is never re-pointed and
+  // can alias memory owned by someone else (PreconditionMG works directly on the CG vectors).
+  template <typename T> void ChebyshevT<T>::iterate(DVec<T> &dst, const DVec<T> &rhs, const bool zero_guess)
   {
     estimate_eigenvalues();
     Context     &c = ctx();
     const size_t n = dst.n_owned;
-    // iteration_index 0: dst = (1/theta) D^-1 rhs
-    cheb_update<T>(0, T(0), T(1.0 / theta_), rhs.data, dinv_.data, nullptr, nullptr, dst.data, n, c.stream);
-    ++c.launches;
-    if (degree_ < 2 || std::fabs(delta_) < 1e-40)
-      return;
-    double rhok = delta_ / theta_, sigma = theta_ / delta_;
-    for (int k = 0; k < degree_ - 1; ++k)
+    if (solution_old_.n_owned != dst.n_owned || solution_old_.n_ghost != dst.n_ghost)
+      solution_old_.reinit_like(dst);
+    solution_old_.part = dst.part;
+    if (zero_guess)
       {
-        op_.vmult(temp1_, dst);
-        const double rhokp = 1.0 / (2.0 * sigma - rhok);
-        const double f1 = rhokp * rhok, f2 = 2.0 * rhokp / delta_;
-        rhok = rhokp;
-        cheb_update<T>(k + 1, T(f1), T(f2), rhs.data, dinv_.data, temp1_.data, dst.data, solution_old_.data, n, c.stream);
+        // iteration_index 0: dst = (1/theta) D^-1 rhs
+        cheb_update<T>(0, T(0), T(1.0 / theta_), rhs.data, dinv_.data, nullptr, nullptr, nullptr, dst.data, n, c.stream);
         ++c.launches;
-        dst.swap_data(solution_old_);
+      }
+    const bool degenerate = degree_ < 2 || std::fabs(delta_) < 1e-40;
+    const int  n_updates  = zero_guess ? (degenerate ? 0 : degree_ - 1) : (degenerate ? 1 : degree_);
+    DVec<T>   *x = &dst, *xo = &solution_old_;
+    bool       have_old = false;
+    double     rhok = delta_ / theta_, sigma = theta_ / delta_;
+    for (int u = 0; u < n_updates; ++u)
+      {
+        op_.vmult(temp1_, *x);
+        double f1, f2;
+        if (!zero_guess && u == 0)
+          {
+            f1 = 0.0;
+            f2 = 1.0 / theta_;
+          }
+        else
+          {
+            const double rhokp = 1.0 / (2.0 * sigma - rhok);
+            f1   = rhokp * rhok;
+            f2   = 2.0 * rhokp / delta_;
+            rhok = rhokp;
+          }
+        const bool last = u == n_updates - 1;
+        DVec<T>   *out  = last ? &dst : xo;
+        cheb_update<T>(have_old ? 2 : 1, T(f1), T(f2), rhs.data, dinv_.data, temp1_.data, x->data, xo->data, out->data, n, c.stream);
+        ++c.launches;
+        if (!last)
+          {
+            std::swap(x, xo);
+            have_old = true;
+          }
       }
   }
 
-  template <typename T> void ChebyshevT<T>::step(DVec<T> &dst, const DVec<T> &rhs)
-  {
-    estimate_eigenvalues();
-    Context     &c = ctx();
-    const size_t n = dst.n_owned;
-    op_.vmult(temp1_, dst);
-    cheb_update<T>(1, T(0), T(1.0 / theta_), rhs.data, dinv_.data, temp1_.data, dst.data, solution_old_.data, n, c.stream);
-    ++c.launches;
-    dst.swap_data(solution_old_);
-    if (degree_ < 2 || std::fabs(delta_) < 1e-40)
-      return;
-    double rhok = delta_ / theta_, sigma = theta_ / delta_;
-    for (int k = 0; k < degree_ - 1; ++k)
-      {
-        op_.vmult(temp1_, dst);
-        const double rhokp = 1.0 / (2.0 * sigma - rhok);
-        const double f1 = rhokp * rhok, f2 = 2.0 * rhokp / delta_;
-        rhok = rhokp;
-        cheb_update<T>(k + 2, T(f1), T(f2), rhs.data, dinv_.data, temp1_.data, dst.data, solution_old_.data, n, c.stream);
-        ++c.launches;
-        dst.swap_data(solution_old_);
-      }
-  }
+  template <typename T> void ChebyshevT<T>::vmult(DVec<T> &dst, const DVec<T> &rhs) { iterate(dst, rhs, true); }
+  template <typename T> void ChebyshevT<T>::step(DVec<T> &dst, const DVec<T> &rhs) { iterate(dst, rhs, false); }
 
   // ------------------------------------------------------------------------------------------ transfers
   template <typename T>
@@ -488,11 +513,14 @@ namespace mgb
   }
 
   template <typename T>
-  void GCTransferT<T>::copy_to_mg(std::vector<DVec<T>> &defect, unsigned minl, unsigned maxl, const DVec<double> &src) const
+  void GCTransferT<T>::copy_to_mg(std::vector<DVec<T>> &defect, unsigned minl, unsigned maxl, const DVec<double> &src, bool skip_top) const
   {
     Context &c = ctx();
     for (unsigned l = minl; l <= maxl; ++l)
-      operators[l - min_level]->initialize_dof_vector(defect[l - minl]);
+      if (!(skip_top && l == maxl))
+        operators[l - min_level]->initialize_dof_vector(defect[l - minl]);
+    if (skip_top)
+      return;
     DVec<T> &top = defect[maxl - minl];
     vec_convert<T, double>(top.data, src.data, top.n_owned, c.stream);
     ++c.launches;
@@ -553,11 +581,16 @@ namespace mgb
   // ------------------------------------------------------------------------------------------ multigrid
   template <typename T> void MultigridT<T>::cycle()
   {
-    // The defect vector has been initialized by copy_to_mg. Now adjust the other vectors.
+    // The defect vectors have been initialised by copy_to_mg.  deal.II re-initialises solution and t on all levels to
+    // zero here; only the coarse level's solution (zero initial guess of the coarse CG) needs it: on the other levels
+    // the pre-smoother overwrites solution and the residual overwrites t, ghost entries are zero by invariant.
     for (unsigned l = min_level; l <= max_level; ++l)
       {
-        solution[l - min_level].reinit_like(defect[l - min_level]);
-        t[l - min_level].reinit_like(defect[l - min_level]);
+        if (l == min_level)
+          solution[l - min_level].reinit_keep(defect[l - min_level]);
+        else
+          solution[l - min_level].ensure_like(defect[l - min_level]);
+        t[l - min_level].ensure_like(defect[l - min_level]);
       }
     level_v_step(max_level);
   }
@@ -584,8 +617,7 @@ namespace mgb
     smoothers[i]->vmult(solution[i], defect[i]); // pre_smooth->apply (zero initial guess)
     te();
     tb(STAGE_RESIDUAL);
-    matrices[i]->vmult_interface_down(t[i], solution[i]);
-    t[i].sadd(T(-1), T(1), defect[i]);
+    matrices[i]->residual_interface_down(t[i], defect[i], solution[i]); // t = defect - A solution
     te();
     tb(STAGE_RESTRICTION);
     transfer->restrict_and_add(level, defect[i - 1], t[i]);
@@ -609,15 +641,37 @@ namespace mgb
   template <typename T> void PreconditionMGT<T>::vmult(DVec<double> &dst, const DVec<double> &src)
   {
     mg->resize_levels();
+    const unsigned top = mg->max_level - mg->min_level;
+    // FP64 levels without edge matrices never write into defect[max]: let the V-cycle work directly on the caller's
+    // vectors (defect[max] = src, solution[max] = dst) instead of copying in and out (copy_to_mg / copy_from_mg)
+    bool alias = false;
+    if constexpr (std::is_same<T, double>::value)
+      {
+        uint32_t                           no, ng;
+        std::shared_ptr<DevicePartitioner> part;
+        transfer->level_layout(mg->max_level, no, ng, part);
+        alias = !mg->edge_in && src.n_owned == no && src.n_ghost == ng && dst.n_owned == no && dst.n_ghost == ng && src.data != dst.data;
+        if (alias)
+          {
+            mg->defect[top].wrap(const_cast<double *>(src.data), no, ng, part);
+            mg->solution[top].wrap(dst.data, no, ng, part);
+          }
+        else if (!mg->defect[top].owns)
+          {
+            mg->defect[top].wrap(nullptr, 0, 0);
+            mg->solution[top].wrap(nullptr, 0, 0);
+          }
+      }
     if (timers)
       timers->begin(int(mg->min_level), N_STAGES);
-    transfer->copy_to_mg(mg->defect, mg->min_level, mg->max_level, src);
+    transfer->copy_to_mg(mg->defect, mg->min_level, mg->max_level, src, alias);
     if (timers)
       timers->end();
     mg->cycle();
     if (timers)
       timers->begin(int(mg->min_level), N_STAGES + 1);
-    transfer->copy_from_mg(dst, mg->solution, mg->min_level, mg->max_level);
+    if (!alias)
+      transfer->copy_from_mg(dst, mg->solution, mg->min_level, mg->max_level);
     if (timers)
       timers->end();
   }

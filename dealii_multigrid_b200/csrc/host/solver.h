@@ -175,6 +175,26 @@ namespace mgb
     double norm_sqr() const { return dot(*this); }
     double l2_norm() const { return std::sqrt(norm_sqr()); }
     double add_and_dot(T a, const DVec &h); // this += a h ; returns this.this
+    // x += a d; this += a h; returns this.this  (this = CG residual g)
+    double cg_update(DVec &x, T a, const DVec &d, const DVec &h);
+    // same layout as o, zero-filled, without reallocating when the storage already fits (also for wrapped memory)
+    void reinit_keep(const DVec &o)
+    {
+      if (data && n_owned == o.n_owned && n_ghost == o.n_ghost)
+        {
+          part = o.part;
+          zero();
+        }
+      else
+        reinit_like(o);
+    }
+    void ensure_like(const DVec &o) // as reinit_keep, but existing contents are kept (ghost entries are zero by invariant)
+    {
+      if (data && n_owned == o.n_owned && n_ghost == o.n_ghost)
+        part = o.part;
+      else
+        reinit_like(o);
+    }
     double mean_value(long long n_global) const;
     // ghost exchange
     void update_ghost_values() const;
@@ -297,8 +317,7 @@ namespace mgb
         double alpha = d.dot(h);
         alpha        = gh / alpha;
         prev_alpha   = alpha;
-        x.add(T(alpha), d);
-        res = std::sqrt(std::fabs(g.add_and_dot(T(alpha), h)));
+        res = std::sqrt(std::fabs(g.cg_update(x, T(alpha), d, h)));
         if (ctl.check(it, res) != SolverControl::iterate)
           break;
       }
@@ -339,6 +358,9 @@ namespace mgb
     void      vmult(DVec<T> &dst, const DVec<T> &src) const;                // include/operator.h:152-183
     void      Tvmult(DVec<T> &dst, const DVec<T> &src) const { vmult(dst, src); }
     void      vmult_interface_down(DVec<T> &dst, const DVec<T> &src) const; // :191-201
+    // dst = b - A src with A = vmult_interface_down: Multigrid::level_v_step's residual (matrix->vmult followed by
+    // t.sadd(-1, 1, defect)) in one cell loop
+    void      residual_interface_down(DVec<T> &dst, const DVec<T> &b, const DVec<T> &src) const;
     void      vmult_interface_up(DVec<T> &dst, const DVec<T> &src) const;   // :203-226
     void      compute_inverse_diagonal(DVec<T> &diag) const;                // :228-242
     const std::shared_ptr<DevicePartitioner> &partitioner() const { return part_; }
@@ -348,7 +370,7 @@ namespace mgb
     const uint32_t *constrained_dev() const { return constrained_.ptr; }
 
   private:
-    void cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_cells_only) const;
+    void cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_cells_only, double alpha = 1.0) const;
     CellData                           cd_;
     DeviceBuffer<uint32_t>             etab_, ctab_;
     DeviceBuffer<uint16_t>             mask_;
@@ -369,6 +391,7 @@ namespace mgb
     ChebyshevT(const OperatorT<T> &op, int degree, double smoothing_range, unsigned eig_cg_n_iterations);
     void vmult(DVec<T> &dst, const DVec<T> &rhs);
     void step(DVec<T> &dst, const DVec<T> &rhs);
+    void iterate(DVec<T> &dst, const DVec<T> &rhs, bool zero_guess);
     void estimate_eigenvalues();
     double lambda_max() const { return lambda_max_; }
     double lambda_min_estimate() const { return lambda_min_est_; }
@@ -410,7 +433,11 @@ namespace mgb
     virtual void prolongate_and_add(unsigned to_level, DVec<T> &dst, const DVec<T> &src) const = 0;
     virtual void restrict_and_add(unsigned from_level, DVec<T> &dst, const DVec<T> &src) const = 0;
     // double-precision outer vector <-> level vectors
-    virtual void copy_to_mg(std::vector<DVec<T>> &defect, unsigned min_level, unsigned max_level, const DVec<double> &src) const = 0;
+    // skip_top: the top-level defect already aliases src (PreconditionMGT), only the lower levels are (re)initialised
+    virtual void copy_to_mg(std::vector<DVec<T>> &defect, unsigned min_level, unsigned max_level, const DVec<double> &src,
+                            bool skip_top = false) const = 0;
+    // layout of the level vectors on `level` (initialize_dof_vector of that level's operator)
+    virtual void level_layout(unsigned level, uint32_t &n_owned, uint32_t &n_ghost, std::shared_ptr<DevicePartitioner> &part) const = 0;
     virtual void copy_from_mg(DVec<double> &dst, const std::vector<DVec<T>> &solution, unsigned min_level, unsigned max_level) const = 0;
   };
 
@@ -429,7 +456,13 @@ namespace mgb
     {
       transfers[from_level - min_level]->restrict_and_add(dst, src);
     }
-    void copy_to_mg(std::vector<DVec<T>> &defect, unsigned minl, unsigned maxl, const DVec<double> &src) const override;
+    void copy_to_mg(std::vector<DVec<T>> &defect, unsigned minl, unsigned maxl, const DVec<double> &src, bool skip_top = false) const override;
+    void level_layout(unsigned level, uint32_t &n_owned, uint32_t &n_ghost, std::shared_ptr<DevicePartitioner> &part) const override
+    {
+      part    = operators[level - min_level]->partitioner();
+      n_owned = part->host.n_owned;
+      n_ghost = part->host.n_ghost;
+    }
     void copy_from_mg(DVec<double> &dst, const std::vector<DVec<T>> &solution, unsigned minl, unsigned maxl) const override;
   };
 
