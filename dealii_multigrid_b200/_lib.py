@@ -32,6 +32,12 @@ class TransferMapView(C.Structure):
         ("degree_fine", C.c_int32), ("degree_coarse", C.c_int32),
         ("n_coarse_cells", C.c_int64), ("n_fine_cells", C.c_int64),
         ("fine_first", c_u32p), ("n_children", c_u8p), ("weight_code", c_u8p),
+        ("fine_own", c_u32p), ("n_fine_slots", C.c_int64), ("distributed", C.c_int32),
+        ("owned_begin", C.c_int64),
+        ("n_owned", C.c_uint32), ("n_ghost", C.c_uint32), ("n_ghost_ranks", C.c_uint32), ("n_import_ranks", C.c_uint32),
+        ("n_import_indices", C.c_uint32),
+        ("ghost_global", c_i64p), ("ghost_ranks", c_i32p), ("ghost_offsets", c_u32p),
+        ("import_ranks", c_i32p), ("import_offsets", c_u32p), ("import_indices", c_u32p),
     ]
 
 

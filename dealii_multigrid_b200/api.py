@@ -223,6 +223,23 @@ class TransferMap:
         self.view = v
         self.degree_fine, self.degree_coarse = int(v.degree_fine), int(v.degree_coarse)
         self.n_coarse_cells, self.n_fine_cells = int(v.n_coarse_cells), int(v.n_fine_cells)
+        self.n_fine_slots, self.distributed = int(v.n_fine_slots), bool(v.distributed)
+
+    def fine_own(self):
+        """fine-side own table indexed by fine_first (+child); several ranks: numbering of partitioner()"""
+        return _arr(self.view.fine_own, self.n_fine_slots * 27, np.uint32).reshape(self.n_fine_slots, 27)
+
+    def partitioner(self):
+        """layout of the transfer's internal ghosted fine vector (several ranks only)"""
+        v = self.view
+        return dict(
+            owned_begin=int(v.owned_begin), n_owned=int(v.n_owned), n_ghost=int(v.n_ghost),
+            ghost_global=_arr(v.ghost_global, v.n_ghost, np.int64),
+            ghost_ranks=_arr(v.ghost_ranks, v.n_ghost_ranks, np.int32),
+            ghost_offsets=_arr(v.ghost_offsets, v.n_ghost_ranks + 1, np.uint32) if v.distributed else np.zeros(1, np.uint32),
+            import_ranks=_arr(v.import_ranks, v.n_import_ranks, np.int32),
+            import_offsets=_arr(v.import_offsets, v.n_import_ranks + 1, np.uint32) if v.distributed else np.zeros(1, np.uint32),
+            import_indices=_arr(v.import_indices, v.n_import_indices, np.uint32))
 
     def fine_first(self):
         return _arr(self.view.fine_first, self.n_coarse_cells, np.uint32)
@@ -231,7 +248,7 @@ class TransferMap:
         return _arr(self.view.n_children, self.n_coarse_cells, np.uint8)
 
     def weight_code(self):
-        return _arr(self.view.weight_code, self.n_fine_cells * 27, np.uint8).reshape(self.n_fine_cells, 27)
+        return _arr(self.view.weight_code, self.n_fine_slots * 27, np.uint8).reshape(self.n_fine_slots, 27)
 
     def __del__(self):
         if getattr(self, "_h", None):

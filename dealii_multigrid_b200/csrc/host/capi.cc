@@ -353,6 +353,22 @@ int mgb_transfer_map_view_get(const mgb_transfer_map *t, mgb_transfer_map_view *
     v->fine_first     = t->t.fine_first.data();
     v->n_children     = t->t.n_children.data();
     v->weight_code    = t->t.weight_code.data();
+    v->fine_own       = t->t.fine_own.data();
+    v->n_fine_slots   = t->t.n_fine_slots;
+    v->distributed    = t->t.distributed ? 1 : 0;
+    const Partitioner &p = t->t.part;
+    v->n_owned          = p.n_owned;
+    v->n_ghost          = p.n_ghost;
+    v->owned_begin      = p.owned_begin;
+    v->ghost_global     = p.ghost_global.data();
+    v->n_ghost_ranks    = (uint32_t)p.ghost_ranks.size();
+    v->ghost_ranks      = p.ghost_ranks.data();
+    v->ghost_offsets    = p.ghost_offsets.data();
+    v->n_import_ranks   = (uint32_t)p.import_ranks.size();
+    v->import_ranks     = p.import_ranks.data();
+    v->import_offsets   = p.import_offsets.data();
+    v->n_import_indices = (uint32_t)p.import_indices.size();
+    v->import_indices   = p.import_indices.data();
   });
 }
 void mgb_transfer_map_destroy(mgb_transfer_map *t) { delete t; }

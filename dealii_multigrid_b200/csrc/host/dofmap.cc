@@ -192,6 +192,8 @@ namespace mgb
     if (next >= int64_t(INDEX_MASK))
       throw std::runtime_error("DoFMap: more than 2^31 DoFs need 64-bit local indices");
     const int64_t my_begin = dof_begin[rank], my_end = dof_begin[rank + 1];
+    dm.rank_dof_begin   = dof_begin;
+    dm.rank_cell_begin  = cell_begin;
     dm.part.n_global    = next;
     dm.part.owned_begin = my_begin;
     dm.part.n_owned     = uint32_t(my_end - my_begin);
@@ -339,6 +341,8 @@ namespace mgb
     for (const Ent &en : constrained_ents)
       for (int k = 0; k < en.size; ++k)
         dm.constrained.push_back(uint32_t(en.base - my_begin + k));
+    if (n_ranks > 1)
+      dm.global_entities = std::make_shared<FlatMap>(std::move(ent));
     return dm;
   }
 
@@ -361,8 +365,10 @@ namespace mgb
 
   TransferMap TransferMap::build(const Mesh &mesh_fine, const DoFMap &df, const Mesh &mesh_coarse, const DoFMap &dc)
   {
-    if (df.n_ranks != 1 || dc.n_ranks != 1)
-      throw std::runtime_error("TransferMap: multi-rank transfer maps are built by the distributed path");
+    if (df.n_ranks != dc.n_ranks || df.rank != dc.rank)
+      throw std::runtime_error("TransferMap: fine and coarse DoF maps belong to different partitions");
+    if (df.n_ranks > 1)
+      return build_distributed(mesh_fine, df, mesh_coarse, dc);
     TransferMap tm;
     tm.degree_fine    = df.degree;
     tm.degree_coarse  = dc.degree;
@@ -427,6 +433,210 @@ namespace mgb
           tm.weight_code[k] = 0;
         else
           tm.weight_code[k] = valence[t & INDEX_MASK];
+      }
+    tm.fine_own     = df.own_table;
+    tm.n_fine_slots = df.n_cells;
+    tm.distributed  = false;
+    return tm;
+  }
+
+  // Several ranks: the coarse level is partitioned independently of the fine level (equal Morton chunks of each mesh, the
+  // reference's DefaultPolicy), so the children of a locally owned coarse cell may belong to other ranks.  As in
+  // MGTwoLevelTransfer, the transfer gets its own fine-side numbering: the fine level's owned range plus the ghost DoFs
+  // of those children; every rank derives the ghost/import lists of all ranks from the replicated global numbering.
+  TransferMap TransferMap::build_distributed(const Mesh &mesh_fine, const DoFMap &df, const Mesh &mesh_coarse, const DoFMap &dc)
+  {
+    if (!df.global_entities)
+      throw std::runtime_error("TransferMap: the fine DoF map does not carry the global numbering");
+    const int     R = df.n_ranks, me = df.rank, p = df.degree;
+    const int64_t ncc = (int64_t)mesh_coarse.cells.size(), nfc = (int64_t)mesh_fine.cells.size();
+    const EntityKeys K{df.mesh_max_level};
+    int              esize[27];
+    for (int e = 0; e < 27; ++e)
+      esize[e] = ipow(p - 1, entity_dim(e));
+    const int64_t my_begin = df.rank_dof_begin[me], my_end = df.rank_dof_begin[me + 1];
+
+    TransferMap tm;
+    tm.degree_fine   = df.degree;
+    tm.degree_coarse = dc.degree;
+    tm.distributed   = true;
+    // pass 0: coarse cell -> first fine cell / number of children, globally
+    std::vector<int64_t> first(ncc);
+    std::vector<uint8_t> nch(ncc);
+    {
+      int64_t f = 0;
+      for (int64_t c = 0; c < ncc; ++c)
+        {
+          const Cell &cc = mesh_coarse.cells[c];
+          if (f >= nfc)
+            throw std::runtime_error("TransferMap: fine mesh exhausted");
+          const Cell &fc = mesh_fine.cells[f];
+          first[c]       = f;
+          if (fc.level == cc.level && fc.x == cc.x && fc.y == cc.y && fc.z == cc.z)
+            nch[c] = 1;
+          else if (fc.level == cc.level + 1 && (fc.x >> 1) == cc.x && (fc.y >> 1) == cc.y && (fc.z >> 1) == cc.z && f + 8 <= nfc)
+            nch[c] = 8;
+          else
+            throw std::runtime_error("TransferMap: fine mesh is not a one-level refinement of the coarse mesh");
+          f += nch[c];
+        }
+      if (f != nfc)
+        throw std::runtime_error("TransferMap: fine cells left over");
+    }
+    struct Ent
+    {
+      int64_t base;
+      int     size;
+      bool    operator<(const Ent &o) const { return base < o.base; }
+      bool    operator==(const Ent &o) const { return base == o.base; }
+    };
+    // global own entries (base, constrained flag) of one fine cell
+    const auto fine_entries = [&](const int64_t f, int64_t base[27], bool flag[27]) {
+      const Cell &c = mesh_fine.cells[f];
+      uint64_t    own[27], eval[27];
+      uint16_t    mask;
+      analyse_cell(mesh_fine, K, c, own, eval, mask);
+      for (int e = 0; e < 27; ++e)
+        {
+          if (esize[e] == 0)
+            {
+              base[e] = -1;
+              flag[e] = false;
+              continue;
+            }
+          base[e] = df.global_entities->find(own[e]);
+          if (base[e] < 0)
+            throw std::runtime_error("TransferMap: entity lookup failed");
+          flag[e] = K.on_boundary(own[e]) || eval[e] != own[e];
+        }
+    };
+    // pass 1: slots of the locally owned coarse cells
+    const int64_t cb = dc.rank_cell_begin[me], ce = dc.rank_cell_begin[me + 1];
+    tm.n_coarse_cells = ce - cb;
+    tm.fine_first.resize(ce - cb);
+    tm.n_children.resize(ce - cb);
+    std::vector<int64_t> g_own;
+    std::vector<uint8_t> f_own;
+    std::vector<Ent>     ghosts;
+    FlatMap              needed; // global base -> index into valence
+    std::vector<uint8_t> valence;
+    for (int64_t c = cb; c < ce; ++c)
+      {
+        tm.fine_first[c - cb] = uint32_t(g_own.size() / 27);
+        tm.n_children[c - cb] = nch[c];
+        for (int ch = 0; ch < nch[c]; ++ch)
+          {
+            int64_t base[27];
+            bool    flag[27];
+            fine_entries(first[c] + ch, base, flag);
+            for (int e = 0; e < 27; ++e)
+              {
+                g_own.push_back(base[e]);
+                f_own.push_back(flag[e]);
+                if (base[e] < 0)
+                  continue;
+                if (base[e] < my_begin || base[e] >= my_end)
+                  ghosts.push_back(Ent{base[e], esize[e]});
+                if (needed.find(uint64_t(base[e])) < 0)
+                  {
+                    needed.insert(uint64_t(base[e]), int64_t(valence.size()));
+                    valence.push_back(0);
+                  }
+              }
+          }
+      }
+    tm.n_fine_slots = int64_t(g_own.size() / 27);
+    // pass 2: all coarse cells: valences of the needed entities and what the other ranks import from us
+    std::vector<std::vector<Ent>> imports(R);
+    {
+      int              q = 0;
+      std::vector<Ent> patch;
+      for (int64_t c = 0; c < ncc; ++c)
+        {
+          while (dc.rank_cell_begin[q + 1] <= c)
+            ++q;
+          patch.clear();
+          for (int ch = 0; ch < nch[c]; ++ch)
+            {
+              int64_t base[27];
+              bool    flag[27];
+              fine_entries(first[c] + ch, base, flag);
+              for (int e = 0; e < 27; ++e)
+                if (base[e] >= 0)
+                  patch.push_back(Ent{base[e], esize[e]});
+            }
+          std::sort(patch.begin(), patch.end());
+          patch.erase(std::unique(patch.begin(), patch.end()), patch.end());
+          for (const Ent &en : patch)
+            {
+              const int64_t v = needed.find(uint64_t(en.base));
+              if (v >= 0)
+                ++valence[v];
+              if (q != me && en.base >= my_begin && en.base < my_end)
+                imports[q].push_back(en);
+            }
+        }
+    }
+    const auto uniq = [](std::vector<Ent> &v) {
+      std::sort(v.begin(), v.end());
+      v.erase(std::unique(v.begin(), v.end()), v.end());
+    };
+    uniq(ghosts);
+    Partitioner &P = tm.part;
+    P.n_global     = df.part.n_global;
+    P.owned_begin  = my_begin;
+    P.n_owned      = uint32_t(my_end - my_begin);
+    std::vector<uint32_t> ghost_off(ghosts.size() + 1, 0);
+    for (size_t g = 0; g < ghosts.size(); ++g)
+      ghost_off[g + 1] = ghost_off[g] + uint32_t(ghosts[g].size);
+    P.n_ghost = ghost_off.back();
+    P.ghost_global.resize(P.n_ghost);
+    {
+      int owner = -1;
+      for (size_t g = 0; g < ghosts.size(); ++g)
+        {
+          for (int k = 0; k < ghosts[g].size; ++k)
+            P.ghost_global[ghost_off[g] + k] = ghosts[g].base + k;
+          const int o = int(std::upper_bound(df.rank_dof_begin.begin(), df.rank_dof_begin.end(), ghosts[g].base) - df.rank_dof_begin.begin()) - 1;
+          if (o != owner)
+            {
+              P.ghost_ranks.push_back(o);
+              P.ghost_offsets.push_back(ghost_off[g]);
+              owner = o;
+            }
+        }
+      P.ghost_offsets.push_back(P.n_ghost);
+    }
+    P.import_offsets.push_back(0);
+    for (int r = 0; r < R; ++r)
+      {
+        if (imports[r].empty())
+          continue;
+        uniq(imports[r]);
+        P.import_ranks.push_back(r);
+        for (const Ent &en : imports[r])
+          for (int k = 0; k < en.size; ++k)
+            P.import_indices.push_back(uint32_t(en.base - my_begin + k));
+        P.import_offsets.push_back(uint32_t(P.import_indices.size()));
+      }
+    const auto to_local = [&](int64_t base) -> uint32_t {
+      if (base >= my_begin && base < my_end)
+        return uint32_t(base - my_begin);
+      const auto it = std::lower_bound(ghosts.begin(), ghosts.end(), Ent{base, 0});
+      return P.n_owned + ghost_off[it - ghosts.begin()];
+    };
+    tm.fine_own.resize(g_own.size());
+    tm.weight_code.assign(g_own.size(), 0);
+    for (size_t k = 0; k < g_own.size(); ++k)
+      {
+        if (g_own[k] < 0)
+          {
+            tm.fine_own[k] = 0;
+            continue;
+          }
+        tm.fine_own[k] = to_local(g_own[k]) | (f_own[k] ? FLAG_BIT : 0u);
+        if (!f_own[k])
+          tm.weight_code[k] = valence[needed.find(uint64_t(g_own[k]))];
       }
     return tm;
   }

@@ -25,6 +25,7 @@
 #include "octree.h"
 
 #include <cstdint>
+#include <memory>
 #include <vector>
 
 namespace mgb
@@ -76,6 +77,10 @@ namespace mgb
     std::vector<uint32_t> constrained; // owned local indices, ascending (Dirichlet + hanging)
     int64_t               n_cells_hanging = 0; // local cells with a face/edge constraint
     Partitioner           part;
+    // n_ranks > 1 only: the replicated global numbering (entity key -> first global DoF) and the rank boundaries, kept
+    // for the two-level transfers, whose coarse cells may have children owned by other ranks
+    std::shared_ptr<FlatMap> global_entities;
+    std::vector<int64_t>     rank_dof_begin, rank_cell_begin; // n_ranks+1 each
 
     // build the active-mesh DoFs of `mesh` for FE_Q(degree), partitioned over n_ranks (equal cell counts)
     static DoFMap build(const Mesh &mesh, int degree, int n_ranks = 1, int rank = 0);
@@ -99,8 +104,20 @@ namespace mgb
     int64_t               n_coarse_cells = 0;
     std::vector<uint32_t> fine_first;  // per coarse cell: first fine cell (Morton-contiguous children)
     std::vector<uint8_t>  n_children;  // per coarse cell: 1 (same cell) or 8
-    std::vector<uint8_t>  weight_code; // n_fine_cells*27: 0 -> weight 0 (constrained fine entity), v -> 1/v
+    std::vector<uint8_t>  weight_code; // n_fine_slots*27: 0 -> weight 0 (constrained fine entity), v -> 1/v
+    // fine-side DoF table the kernels index with fine_first (+child): n_fine_slots*27 own-table entries.  Single rank: a
+    // copy of the fine DoFMap's own_table (slot = fine cell).  Several ranks: the children of the locally owned COARSE
+    // cells (which other ranks may own), in the numbering of `part`: same owned range as the fine level, plus the ghost
+    // DoFs of those children -- the internal ghosted fine vector of MGTwoLevelTransfer.
+    std::vector<uint32_t> fine_own;
+    int64_t               n_fine_slots = 0;
+    bool                  distributed  = false;
+    Partitioner           part;
     static TransferMap build(const Mesh &mesh_fine, const DoFMap &dofs_fine, const Mesh &mesh_coarse,
                              const DoFMap &dofs_coarse);
+
+  private:
+    static TransferMap build_distributed(const Mesh &mesh_fine, const DoFMap &dofs_fine, const Mesh &mesh_coarse,
+                                         const DoFMap &dofs_coarse);
   };
 } // namespace mgb

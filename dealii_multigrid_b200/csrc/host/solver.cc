@@ -468,7 +468,9 @@ namespace mgb
   {
     ctx().ensure();
     upload_fe_constants(coarse.degree);
-    fine_own_.upload(fine.own_table.data(), fine.own_table.size());
+    fine_own_.upload(tm.fine_own.data(), tm.fine_own.size());
+    if (tm.distributed)
+      fine_part_ = std::make_shared<DevicePartitioner>(tm.part);
     fine_first_.upload(tm.fine_first.data(), tm.fine_first.size());
     n_children_.upload(tm.n_children.data(), tm.n_children.size());
     weight_code_.upload(tm.weight_code.data(), tm.weight_code.size());
@@ -496,20 +498,44 @@ namespace mgb
   {
     Context &c = ctx();
     src_coarse.update_ghost_values();
-    transfer_prolongate_add<T>(td_, dst_fine.data, src_coarse.data, c.stream);
-    ++c.launches;
-    dst_fine.compress_add();
+    if (fine_part_)
+      {
+        // children of local coarse cells may live on other ranks: add into the transfer's own ghosted fine vector,
+        // send the ghost contributions to their owners, then add the owned part to dst
+        vec_fine_.reinit_keep_layout(fine_part_);
+        transfer_prolongate_add<T>(td_, vec_fine_.data, src_coarse.data, c.stream);
+        ++c.launches;
+        vec_fine_.compress_add();
+        dst_fine.add(T(1), vec_fine_);
+      }
+    else
+      {
+        transfer_prolongate_add<T>(td_, dst_fine.data, src_coarse.data, c.stream);
+        ++c.launches;
+        dst_fine.compress_add();
+      }
     src_coarse.zero_out_ghost_values();
   }
 
   template <typename T> void TwoLevelTransferT<T>::restrict_and_add(DVec<T> &dst_coarse, const DVec<T> &src_fine) const
   {
     Context &c = ctx();
-    src_fine.update_ghost_values();
-    transfer_restrict_add<T>(td_, dst_coarse.data, src_fine.data, c.stream);
-    ++c.launches;
+    if (fine_part_)
+      {
+        vec_fine_.reinit_keep_layout(fine_part_);
+        vec_fine_.copy_from(src_fine);
+        vec_fine_.update_ghost_values();
+        transfer_restrict_add<T>(td_, dst_coarse.data, vec_fine_.data, c.stream);
+        ++c.launches;
+      }
+    else
+      {
+        src_fine.update_ghost_values();
+        transfer_restrict_add<T>(td_, dst_coarse.data, src_fine.data, c.stream);
+        ++c.launches;
+        src_fine.zero_out_ghost_values();
+      }
     dst_coarse.compress_add();
-    src_fine.zero_out_ghost_values();
   }
 
   template <typename T>

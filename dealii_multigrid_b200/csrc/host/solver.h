@@ -188,6 +188,16 @@ namespace mgb
       else
         reinit_like(o);
     }
+    void reinit_keep_layout(const std::shared_ptr<DevicePartitioner> &p) // zero-filled vector of the partitioner's layout
+    {
+      if (data && owns && n_owned == p->host.n_owned && n_ghost == p->host.n_ghost)
+        {
+          part = p;
+          zero();
+        }
+      else
+        reinit(p->host.n_owned, p->host.n_ghost, p);
+    }
     void ensure_like(const DVec &o) // as reinit_keep, but existing contents are kept (ghost entries are zero by invariant)
     {
       if (data && n_owned == o.n_owned && n_ghost == o.n_ghost)
@@ -422,6 +432,8 @@ namespace mgb
   private:
     TransferData           td_;
     DeviceBuffer<uint32_t> fine_own_, fine_first_;
+    std::shared_ptr<DevicePartitioner> fine_part_; // several ranks: layout of the internal ghosted fine vector
+    mutable DVec<T>                    vec_fine_;
     DeviceBuffer<uint8_t>  n_children_, weight_code_;
     const OperatorT<T>    &op_fine_, &op_coarse_;
   };

@@ -116,7 +116,19 @@ typedef struct
   int64_t         n_coarse_cells, n_fine_cells;
   const uint32_t *fine_first;  /* n_coarse_cells */
   const uint8_t  *n_children;  /* n_coarse_cells: 1 or 8 */
-  const uint8_t  *weight_code; /* n_fine_cells*27: 0 -> weight 0, v -> 1/v */
+  const uint8_t  *weight_code; /* n_fine_slots*27: 0 -> weight 0, v -> 1/v */
+  /* fine-side table indexed by fine_first (+child): single rank = the fine dofmap's own table; several ranks = the
+   * children of the locally owned coarse cells in the numbering of the transfer's internal ghosted fine vector */
+  const uint32_t *fine_own;    /* n_fine_slots*27 */
+  int64_t         n_fine_slots;
+  int32_t         distributed;
+  /* partitioner of that internal vector (distributed only): same owned range as the fine level */
+  int64_t         owned_begin;
+  uint32_t        n_owned, n_ghost, n_ghost_ranks, n_import_ranks, n_import_indices;
+  const int64_t  *ghost_global;
+  const int32_t  *ghost_ranks;  const uint32_t *ghost_offsets;
+  const int32_t  *import_ranks; const uint32_t *import_offsets;
+  const uint32_t *import_indices;
 } mgb_transfer_map_view;
 int  mgb_transfer_map_create(const mgb_mesh *mesh_fine, const mgb_dofmap *fine, const mgb_mesh *mesh_coarse, const mgb_dofmap *coarse,
                              mgb_transfer_map **out);

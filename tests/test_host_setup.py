@@ -215,3 +215,45 @@ def test_fast_diagonalisation_of_the_1d_pencil(p):
         M, K = fe["M"], fe["K"]
         A = np.kron(K, np.kron(M, M)) + np.kron(M, np.kron(K, M)) + np.kron(M, np.kron(M, K))
         assert np.abs(T3.T @ (D[:, None] * T3) - A).max() < 1e-13 * np.abs(A).max()
+
+
+@pytest.mark.parametrize("n_ranks", [2, 3, 8])
+@pytest.mark.parametrize("geometry,L,p,kind", [("hypercube", 2, 2, "h"), ("quadrant", 4, 3, "h"), ("quadrant", 3, 4, "p"), ("annulus", 5, 1, "h")])
+def test_partitioned_transfer_maps_are_consistent(geometry, L, p, kind, n_ranks):
+    """several ranks: the coarse cells of a rank may have children on other ranks; the transfer's own fine-side table,
+    weights and ghost/import lists must describe the serial transfer in the global numbering"""
+    seq = mesh_sequence(geometry, L)
+    (mf, pf), (mc, pc) = ((seq[-1], p), (seq[-2], p)) if kind == "h" else ((seq[-1], p), (seq[-1], max(p // 2, 1)))
+    sf, sc = mg.DoFMap(mf, pf), mg.DoFMap(mc, pc)
+    st = mg.TransferMap(mf, sf, mc, sc)
+    s_own, s_first, s_nch, s_w = sf.own_table(), st.fine_first(), st.n_children(), st.weight_code()
+    tms = []
+    for r in range(n_ranks):
+        df, dc = mg.DoFMap(mf, pf, n_ranks, r), mg.DoFMap(mc, pc, n_ranks, r)
+        tm = mg.TransferMap(mf, df, mc, dc)
+        tms.append((tm, df))
+        assert tm.distributed and tm.n_coarse_cells == dc.n_cells
+        pt = tm.partitioner()
+        assert pt["owned_begin"] == df.owned_begin and pt["n_owned"] == df.n_owned
+        l2g = np.concatenate([np.arange(df.owned_begin, df.owned_begin + df.n_owned), pt["ghost_global"]])
+        own, first, nch, w = tm.fine_own(), tm.fine_first(), tm.n_children(), tm.weight_code()
+        np.testing.assert_array_equal(nch, s_nch[dc.cell_begin:dc.cell_begin + dc.n_cells])
+        esize = np.array([(pf - 1) ** ((e % 3 == 1) + ((e // 3) % 3 == 1) + (e // 9 == 1)) for e in range(27)])
+        for c in range(dc.n_cells):
+            for ch in range(nch[c]):
+                slot, sfine = first[c] + ch, s_first[dc.cell_begin + c] + ch
+                has = esize > 0
+                np.testing.assert_array_equal(l2g[own[slot] & mg.INDEX_MASK][has], (s_own[sfine] & mg.INDEX_MASK)[has])
+                np.testing.assert_array_equal((own[slot] & mg.FLAG_BIT)[has], (s_own[sfine] & mg.FLAG_BIT)[has])
+                np.testing.assert_array_equal(w[slot], s_w[sfine])
+    for tm, df in tms:
+        pa = tm.partitioner()
+        for i, b_rank in enumerate(pa["import_ranks"]):
+            send = pa["import_indices"][pa["import_offsets"][i]:pa["import_offsets"][i + 1]] + df.owned_begin
+            pb = tms[b_rank][0].partitioner()
+            j = list(pb["ghost_ranks"]).index(df.rank)
+            recv = pb["ghost_global"][pb["ghost_offsets"][j]:pb["ghost_offsets"][j + 1]]
+            np.testing.assert_array_equal(send, recv)
+        # every ghost group has a sender
+        for j, o in enumerate(pa["ghost_ranks"]):
+            assert df.rank in list(tms[o][0].partitioner()["import_ranks"])

@@ -1,0 +1,70 @@
+#!/usr/bin/env python
+"""check_multigpu.py -- parity of the N-rank path against the serial CPU oracle; run under torchrun, one rank per GPU:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tools/check_multigpu.py
+
+Every rank builds its part of the problem, applies the distributed vmult / V-cycle / CG solve (ghost exchange and dot
+products over NCCL) and compares its owned slice with the oracle evaluated on the serial maps (small meshes only)."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    import dealii_multigrid_b200 as mg
+    from util import OracleHierarchy, params, rel_l2, seeded
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    mg.init(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    uid = [mg.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    mg.comm_init(uid[0], rank, world)
+    ok = True
+    for geometry, L, p, mg_type, coarse in [("hypercube", 3, 2, "HMG-global", "cg"), ("quadrant", 4, 4, "HMG-global", "cg"),
+                                            ("annulus", 5, 4, "HPMG", "cg_with_chebyshev"), ("quadrant", 3, 4, "PMG", "cg")]:
+        prob = mg.Problem(params(geometry, L, p, mg_type, coarse), world, rank)
+        H = OracleHierarchy(geometry, L, p, mg_type, 3, coarse)
+        d = prob.level_dofmap(prob.n_levels - 1)
+        lo, hi = d.owned_begin, d.owned_begin + d.n_owned
+        n = H.maps[-1].n_dofs
+        x = seeded(n)
+        op = prob.fine_operator()
+        src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+        src.from_numpy(x[lo:hi])
+        op.vmult(dst, src)
+        e_vmult = rel_l2(dst.to_numpy(d.n_owned), H.ops[-1].vmult(x)[lo:hi])
+        r = x.copy()
+        r[H.maps[-1].constrained] = 0.0
+        src.from_numpy(r[lo:hi])
+        prob.vcycle(dst, src)
+        e_vc = rel_l2(dst.to_numpy(d.n_owned), H.mg.vmult(r)[lo:hi])
+        b = np.zeros(n)
+        from oracle import reference as ref
+        b = ref.assemble_rhs_constant(H.maps[-1])
+        e_rhs = rel_l2(prob.rhs().to_numpy(d.n_owned), b[lo:hi])
+        _, its, _ = H.solve(b.copy())
+        res = prob.solve_once()
+        good = e_vmult < 1e-12 and e_vc < 1e-11 and e_rhs < 1e-13 and res["n_iterations"] == its
+        ok &= good
+        print(f"[rank {rank}/{world}] {geometry} L={L} p={p} {mg_type}: owned={d.n_owned} ghost={d.n_ghost} vmult={e_vmult:.1e} "
+              f"vcycle={e_vc:.1e} rhs={e_rhs:.1e} its={res['n_iterations']} (oracle {its}) {'OK' if good else 'FAIL'}", flush=True)
+    t = torch.tensor([1.0 if ok else 0.0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    mg.comm_finalize()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("MULTIGPU PARITY", "OK" if t.item() == 1.0 else "FAILED")
+    sys.exit(0 if t.item() == 1.0 else 1)
+
+
+if __name__ == "__main__":
+    main()
