@@ -253,7 +253,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--nref", type=int, default=6, help="NRefGlobal of the GPU workload")
+    ap.add_argument("--nref", type=int, default=7, help="NRefGlobal of the GPU workload (7: 513^3 = 135 005 697 DoFs)")
     ap.add_argument("--degree", type=int, default=4)
     ap.add_argument("--number", default="double", choices=["double", "float"], help="MGNumberType")
     ap.add_argument("--cpu-nref", type=int, default=4, help="NRefGlobal of the bounded CPU sample")

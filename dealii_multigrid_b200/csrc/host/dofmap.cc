@@ -139,7 +139,7 @@ namespace mgb
     }
   } // namespace
 
-  DoFMap DoFMap::build(const Mesh &mesh, int degree, int n_ranks, int rank)
+  DoFMap DoFMap::build(const Mesh &mesh, int degree, int n_ranks, int rank, int64_t min_cells_per_rank)
   {
     if (degree < 1)
       throw std::runtime_error("DoFMap: degree must be >= 1");
@@ -156,8 +156,9 @@ namespace mgb
       esize[e] = ipow(degree - 1, entity_dim(e));
 
     std::vector<int64_t> cell_begin(n_ranks + 1);
+    const int64_t n_active = std::max<int64_t>(1, std::min<int64_t>(n_ranks, nc / std::max<int64_t>(1, min_cells_per_rank)));
     for (int r = 0; r <= n_ranks; ++r)
-      cell_begin[r] = (nc * r) / n_ranks;
+      cell_begin[r] = (nc * std::min<int64_t>(r, n_active)) / n_active;
     dm.cell_begin = cell_begin[rank];
     dm.n_cells    = cell_begin[rank + 1] - cell_begin[rank];
 

@@ -83,7 +83,10 @@ namespace mgb
     std::vector<int64_t>     rank_dof_begin, rank_cell_begin; // n_ranks+1 each
 
     // build the active-mesh DoFs of `mesh` for FE_Q(degree), partitioned over n_ranks (equal cell counts)
-    static DoFMap build(const Mesh &mesh, int degree, int n_ranks = 1, int rank = 0);
+    // min_cells_per_rank: meshes with fewer cells per rank are split over the first n_cells/min_cells_per_rank ranks
+    // only (the coarse levels of a global-coarsening hierarchy then live on few GPUs or on rank 0 alone and need no
+    // halo exchange; the two-level transfers move the data between the different partitions)
+    static DoFMap build(const Mesh &mesh, int degree, int n_ranks = 1, int rank = 0, int64_t min_cells_per_rank = 1);
 
     // expand to the lexicographic (p+1)^3 index map (what MatrixFree stores); flags kept in bit 31
     void expand(const std::vector<uint32_t> &table, std::vector<uint32_t> &out) const;

@@ -462,7 +462,7 @@ namespace mgb
                 L.degree     = level_degrees[std::max<int>(0, int(l) - int(n_trias) + 1)];
                 L.mesh_index = std::min(l, n_trias - 1);
               }
-            L.dofs = std::make_unique<DoFMap>(DoFMap::build(meshes[L.mesh_index], L.degree, n_ranks, rank));
+            L.dofs = std::make_unique<DoFMap>(DoFMap::build(meshes[L.mesh_index], L.degree, n_ranks, rank, /*min_cells_per_rank=*/512));
             L.op   = std::make_unique<OperatorT<LT>>(setup_from_dofmap(*L.dofs));
           }
         // two-level transfers (ref :1600-1604)
