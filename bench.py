@@ -146,6 +146,11 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback)")
     torch.cuda.set_device(local)
     mg.init(local)
+    # the library enqueues on this (non-default) stream, so torch's events below bracket its work and the V-cycle can be
+    # replayed from a CUDA graph
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    mg.set_stream(stream.cuda_stream)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         uid = [mg.comm_unique_id() if rank == 0 else None]
@@ -186,7 +191,6 @@ def run_ours(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     launches0 = mg.launch_count()
-    mg.profile_start(n_cells_local)
     ev0.record()
     its = 0
     for _ in range(args.steps):
@@ -194,9 +198,19 @@ def run_ours(args):
         its += res["n_iterations"]
     ev1.record()
     barrier()
-    k_ms, k_launches = mg.profile_stop()
     launches = mg.launch_count() - launches0
     ms = max_over_ranks(ev0.elapsed_time(ev1))
+    # ---- timed region 1b: the same K solves with a CUDA-event pair around every finest-level cell-loop launch (the
+    # events force the eager launch path instead of the CUDA-graph replay, so this region is timed separately)
+    barrier()
+    mg.profile_start(n_cells_local)
+    ev0.record()
+    for _ in range(args.steps):
+        prob.solve_once()
+    ev1.record()
+    barrier()
+    k_ms, k_launches = mg.profile_stop()
+    ms_prof = max_over_ranks(ev0.elapsed_time(ev1))
     # ---- timed region 2: the same K solves through host buffers (H2D rhs, D2H solution inside the timed region)
     barrier()
     ev0.record()
@@ -238,7 +252,8 @@ def run_ours(args):
         "roofline": {"kernel": f"k_laplace_apply<{args.degree},double> (finest level)", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "launches_timed": k_launches, "avg_launch_ms": k_avg_s * 1e3,
-                     "share_of_step": k_ms / ms, "gdofs_per_s": n_owned / k_avg_s / 1e9,
+                     "share_of_step": k_ms / ms_prof, "timed_in": "second pass of the same K solves with per-launch CUDA events "
+                     "(eager launches, %.3f ms/step)" % (ms_prof / args.steps), "gdofs_per_s": n_owned / k_avg_s / 1e9,
                      "fp64_tflops_reference_flop_count": flops_ref / k_avg_s / 1e12},
         "cpu_baseline": cpu, "clocks": clocks,
     }

@@ -76,6 +76,13 @@ namespace mgb
   // diag += diag(C^T A_e C) cell-wise (MatrixFreeTools::compute_diagonal)
   template <typename T> void cell_laplace_diagonal(const CellData &cd, T *diag, cudaStream_t s);
 
+  // ---------------------------------------------------------------- coarse-grid solver (coarse.cu)
+  // whole preconditioned CG (identity or Chebyshev(cheb_degree) preconditioner; cheb_degree = 0: none) on the dense,
+  // symmetric n x n level matrix A in ONE thread block; adds the iteration count to *n_iterations_dev
+  template <typename T>
+  void coarse_cg_solve(const T *A, int n, const T *dinv, int cheb_degree, double theta, double delta, unsigned maxiter, double abstol,
+                       double reltol, const T *b, T *x, int *n_iterations_dev, cudaStream_t s);
+
   // ---------------------------------------------------------------- transfers (transfer.cu)
   struct TransferData
   {

@@ -561,7 +561,9 @@ namespace mgb
         r.n_iterations      = (int)ctl.last_step;
         r.initial_residual  = ctl.initial_value;
         r.final_residual    = ctl.last_value;
-        r.coarse_iterations = coarse->total_iterations;
+        r.coarse_iterations = coarse->collect_device_iterations();
+        // every lazy initialisation has happened now: later V-cycles may be replayed from a CUDA graph
+        precond.allow_graph = coarse->single_kernel();
         std::vector<std::array<double, N_STAGES + 2>> st(levels.size());
         for (auto &a : st)
           a.fill(0.0);

@@ -561,6 +561,74 @@ namespace mgb
     ++c.launches;
   }
 
+  // ------------------------------------------------------------------------------------------ coarse solver
+  template <typename T> void CoarseCGT<T>::setup_dense()
+  {
+    dense_checked_ = true;
+    Context           &c = ctx();
+    const Partitioner &p = op_.partitioner()->host;
+    // the level lives entirely on this rank (or this rank owns nothing of it) and is small
+    const bool local = p.n_ghost == 0 && p.import_indices.empty() && (p.n_owned == 0 || (long long)p.n_owned == op_.m());
+    if (!local || op_.m() > max_dense_size)
+      return;
+    dense_ = true;
+    dense_its_.alloc(1);
+    MGB_CUDA(cudaMemset(dense_its_.ptr, 0, sizeof(int)));
+    const int n = (int)p.n_owned;
+    if (n == 0)
+      return;
+    // column j of the level matrix = A e_j (the operator with its identity rows is symmetric)
+    dense_A_.alloc(size_t(n) * n);
+    DVec<T> e, col;
+    op_.initialize_dof_vector(e);
+    op_.initialize_dof_vector(col);
+    for (int j = 0; j < n; ++j)
+      {
+        e.zero();
+        const T one = T(1);
+        MGB_CUDA(cudaMemcpyAsync(e.data + j, &one, sizeof(T), cudaMemcpyHostToDevice, c.stream));
+        op_.vmult(col, e);
+        MGB_CUDA(cudaMemcpyAsync(dense_A_.ptr + size_t(j) * n, col.data, size_t(n) * sizeof(T), cudaMemcpyDeviceToDevice, c.stream));
+        MGB_CUDA(cudaStreamSynchronize(c.stream));
+      }
+  }
+
+  template <typename T> void CoarseCGT<T>::operator()(unsigned, DVec<T> &dst, const DVec<T> &src)
+  {
+    if (precond_)
+      precond_->estimate_eigenvalues(); // also on ranks that own nothing of the level: collective
+    if (!dense_checked_)
+      setup_dense();
+    if (dense_)
+      {
+        Context &c = ctx();
+        if (dst.n_owned)
+          {
+            coarse_cg_solve<T>(dense_A_.ptr, (int)dst.n_owned, precond_ ? precond_->inverse_diagonal().data : nullptr,
+                               precond_ ? precond_->degree() : 0, precond_ ? precond_->theta() : 1.0, precond_ ? precond_->delta() : 1.0,
+                               ctl_.maxiter, ctl_.abstol, ctl_.reltol, src.data, dst.data, dense_its_.ptr, c.stream);
+            ++c.launches;
+          }
+        return;
+      }
+    const auto A = [this](DVec<T> &d, const DVec<T> &s) { op_.vmult(d, s); };
+    const auto P = [this](DVec<T> &d, const DVec<T> &s) { precond_->vmult(d, s); };
+    last_iterations = cg_solve<T>(A, P, precond_ == nullptr, dst, src, ctl_, work_, /*x_is_zero=*/true);
+    total_iterations += last_iterations;
+  }
+
+  template <typename T> long long CoarseCGT<T>::collect_device_iterations()
+  {
+    if (dense_ && dense_its_.n)
+      {
+        int its = 0;
+        MGB_CUDA(cudaMemcpy(&its, dense_its_.ptr, sizeof(int), cudaMemcpyDeviceToHost));
+        MGB_CUDA(cudaMemset(dense_its_.ptr, 0, sizeof(int)));
+        total_iterations += its;
+      }
+    return total_iterations;
+  }
+
   // ------------------------------------------------------------------------------------------ timers
   cudaEvent_t StageTimers::get()
   {
@@ -664,7 +732,65 @@ namespace mgb
     te();
   }
 
+  template <typename T> PreconditionMGT<T>::~PreconditionMGT()
+  {
+    for (GraphEntry &g : graphs_)
+      cudaGraphExecDestroy(g.exec);
+  }
+
   template <typename T> void PreconditionMGT<T>::vmult(DVec<double> &dst, const DVec<double> &src)
+  {
+    Context   &c = ctx();
+    bool graph_ok = allow_graph && c.stream != nullptr && !(timers && timers->enabled) && !c.prof_enabled &&
+                    !(c.comm && c.comm->size() > 1) && std::is_same<T, double>::value && !mg->edge_in && src.data != dst.data;
+    if (graph_ok)
+      {
+        // only the aliasing path (no allocation, no copies) is captured
+        uint32_t                           no, ng;
+        std::shared_ptr<DevicePartitioner> part;
+        transfer->level_layout(mg->max_level, no, ng, part);
+        graph_ok = src.n_owned == no && src.n_ghost == ng && dst.n_owned == no && dst.n_ghost == ng;
+      }
+    if (!graph_ok)
+      {
+        vmult_eager(dst, src);
+        return;
+      }
+    for (const GraphEntry &g : graphs_)
+      if (g.src == src.data && g.dst == dst.data)
+        {
+          MGB_CUDA(cudaGraphLaunch(g.exec, c.stream));
+          c.launches += g.launches;
+          return;
+        }
+    if (graphs_.size() >= 8)
+      {
+        vmult_eager(dst, src);
+        return;
+      }
+    const long long l0 = c.launches;
+    cudaGraph_t     graph = nullptr;
+    MGB_CUDA(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
+    try
+      {
+        vmult_eager(dst, src);
+      }
+    catch (...)
+      {
+        cudaStreamEndCapture(c.stream, &graph);
+        if (graph)
+          cudaGraphDestroy(graph);
+        throw;
+      }
+    MGB_CUDA(cudaStreamEndCapture(c.stream, &graph));
+    GraphEntry g{src.data, dst.data, nullptr, c.launches - l0};
+    MGB_CUDA(cudaGraphInstantiate(&g.exec, graph, 0));
+    MGB_CUDA(cudaGraphDestroy(graph));
+    graphs_.push_back(g);
+    MGB_CUDA(cudaGraphLaunch(g.exec, c.stream));
+  }
+
+  template <typename T> void PreconditionMGT<T>::vmult_eager(DVec<double> &dst, const DVec<double> &src)
   {
     mg->resize_levels();
     const unsigned top = mg->max_level - mg->min_level;
@@ -732,6 +858,8 @@ namespace mgb
   template class MultigridT<float>;
   template class PreconditionMGT<double>;
   template class PreconditionMGT<float>;
+  template class CoarseCGT<double>;
+  template class CoarseCGT<float>;
   template class CoarseApplyMGT<double>;
   template class CoarseApplyMGT<float>;
 } // namespace mgb

@@ -404,6 +404,9 @@ namespace mgb
     void iterate(DVec<T> &dst, const DVec<T> &rhs, bool zero_guess);
     void estimate_eigenvalues();
     double lambda_max() const { return lambda_max_; }
+    double theta() const { return theta_; }
+    double delta() const { return delta_; }
+    int    degree() const { return degree_; }
     double lambda_min_estimate() const { return lambda_min_est_; }
     bool   eigenvalues_done() const { return eig_done_; }
     const DVec<T> &inverse_diagonal() const { return dinv_; }
@@ -499,21 +502,28 @@ namespace mgb
       ctl_.abstol  = abstol;
       ctl_.reltol  = reltol;
     }
-    void operator()(unsigned, DVec<T> &dst, const DVec<T> &src) override
-    {
-      const auto A = [this](DVec<T> &d, const DVec<T> &s) { op_.vmult(d, s); };
-      const auto P = [this](DVec<T> &d, const DVec<T> &s) { precond_->vmult(d, s); };
-      last_iterations = cg_solve<T>(A, P, precond_ == nullptr, dst, src, ctl_, work_, /*x_is_zero=*/true);
-      total_iterations += last_iterations;
-    }
+    void operator()(unsigned, DVec<T> &dst, const DVec<T> &src) override;
+    // iterations of the current solve accumulated on the device by the single-kernel path (read once per outer solve)
+    long long collect_device_iterations();
     unsigned  last_iterations  = 0;
     long long total_iterations = 0;
+    static constexpr int max_dense_size = 512; // coarse problems up to this many DoFs are solved by one thread block
 
   private:
     const OperatorT<T> &op_;
     ChebyshevT<T>      *precond_;
     SolverControl       ctl_;
     CGWork<T>           work_;
+    // dense path
+    bool                dense_checked_ = false, dense_ = false;
+
+  public:
+    bool                single_kernel() const { return dense_checked_ && dense_; }
+
+  private:
+    DeviceBuffer<T>     dense_A_;
+    DeviceBuffer<int>   dense_its_;
+    void                setup_dense();
   };
 
   enum MGStage
@@ -581,6 +591,22 @@ namespace mgb
     const MGTransferBase<T> *transfer = nullptr;
     StageTimers             *timers   = nullptr;
     void                     vmult(DVec<double> &dst, const DVec<double> &src);
+    // CUDA-graph replay of the V-cycle: the level structure is static, so once every lazy initialisation has happened
+    // (eigenvalue estimates, dense coarse matrix, vector allocations: the owner sets allow_graph after a first solve)
+    // the whole launch sequence between two fixed vectors is captured once and replayed.  Not used while stage timers
+    // or the per-kernel profiling events are active, on the legacy default stream, or with several ranks.
+    bool allow_graph = false;
+    ~PreconditionMGT();
+
+  private:
+    void vmult_eager(DVec<double> &dst, const DVec<double> &src);
+    struct GraphEntry
+    {
+      const void     *src, *dst;
+      cudaGraphExec_t exec;
+      long long       launches;
+    };
+    std::vector<GraphEntry> graphs_;
   };
 
   // MGCoarseGridApplyPreconditioner (multigrid_throughput.cc:422-564): nested V-cycle as coarse solver

@@ -208,3 +208,37 @@ def test_unsupported_inputs_raise(gpu):
         mg.Problem(params(geometry="torus"))
     with pytest.raises(mg.MgbError, match="Type"):
         mg.Problem(params(mg_type="AMG"))
+
+
+def test_cuda_graph_replay_matches_eager(gpu):
+    """on a non-default stream the V-cycle is captured into a CUDA graph after the first solve; replays must reproduce the
+    eager launches (same kernels, same order) and the single-kernel coarse CG must keep the oracle's iteration count"""
+    import torch
+    mg = gpu
+    stream = torch.cuda.Stream()
+    try:
+        with torch.cuda.stream(stream):
+            mg.set_stream(stream.cuda_stream)
+            prob = mg.Problem(params("quadrant", 4, 3, "HMG-global", "cg"))
+            H = OracleHierarchy("quadrant", 4, 3, "HMG-global", 3, "cg")
+            _, its_ref, _ = H.solve(prob.rhs().to_numpy())
+            r1 = prob.solve_once()                      # eager (lazy initialisation)
+            x1 = prob.solution().to_numpy()
+            n0 = mg.launch_count()
+            r2 = prob.solve_once()                      # captures, then replays
+            r3 = prob.solve_once()
+            x3 = prob.solution().to_numpy()
+            assert r1["n_iterations"] == r2["n_iterations"] == r3["n_iterations"] == its_ref
+            assert rel_l2(x3, x1) < 1e-12
+            assert mg.launch_count() - n0 > 100         # replayed launches are counted
+            n = x1.size
+            v = seeded(n)
+            v[H.maps[-1].constrained] = 0.0
+            src, dst = prob.fine_operator().initialize_dof_vector(), prob.fine_operator().initialize_dof_vector()
+            src.from_numpy(v)
+            prob.vcycle(dst, src)
+            prob.vcycle(dst, src)
+            assert rel_l2(dst.to_numpy(), H.mg.vmult(v)) < 1e-11
+            mg.synchronize()
+    finally:
+        mg.set_stream(0)

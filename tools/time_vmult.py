@@ -23,8 +23,11 @@ def main():
     import torch
     import dealii_multigrid_b200 as mg
 
-    mg.init(0)
     torch.cuda.set_device(0)
+    mg.init(0)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    mg.set_stream(stream.cuda_stream)
     nt = mg.DOUBLE if args.number == "double" else mg.FLOAT
     d = mg.DoFMap(mg.Mesh(args.geometry, args.nref), args.degree)
     op = mg.Operator(d, number_type=nt)
