@@ -1,0 +1,23 @@
+#!/bin/bash
+# gpu_round.sh <tag> -- the per-change GPU pass: parity tests, smoke, bench lines, ncu launch list, one full ncu capture.
+# Run under gpurun from the repo root; everything it writes goes to gpurun_out/<tag>_*.
+TAG=${1:-run}
+O=gpurun_out
+mkdir -p $O
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/${TAG}_smi.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest.log
+timeout 300 python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/${TAG}_smoke.log
+for spec in "hypercube 6 4 double" "hypercube 7 4 double" "hypercube 6 4 float" "hypercube 7 1 double" "hypercube 7 2 double" "quadrant 6 4 double"; do
+  set -- $spec
+  timeout 300 python tools/time_vmult.py --geometry $1 --nref $2 --degree $3 --number $4 >> $O/${TAG}_time_vmult.txt 2>&1
+done
+timeout 600 python bench.py --nref 6 > $O/${TAG}_bench_L6.json 2> $O/${TAG}_bench_L6.err; echo "bench L6 rc=$?"
+timeout 900 python bench.py > $O/${TAG}_bench_L7.json 2> $O/${TAG}_bench_L7.err; echo "bench L7 rc=$?"
+timeout 600 python bench.py --impl reference --steps 1 --warmup 0 > $O/${TAG}_bench_ref.json 2> $O/${TAG}_bench_ref.err; echo "bench ref rc=$?"
+tail -c 600 $O/${TAG}_bench_L7.json
+# ncu passes: never a bench value
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/${TAG}_launches_L6.csv \
+  python bench.py --nref 6 --steps 1 --warmup 3 --no-cpu > $O/${TAG}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_laplace_apply --launch-skip 3 -c 1 -f -o $O/${TAG}_vmult_L6 \
+  python tools/time_vmult.py --nref 6 --degree 4 --reps 2 > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
+ls -la $O | tail -20
