@@ -41,6 +41,15 @@ class TransferMapView(C.Structure):
     ]
 
 
+class LevelEdgesView(C.Structure):
+    _fields_ = [("n_edge_dofs", C.c_uint32), ("n_edge_cells", C.c_uint32), ("any_global", C.c_int32),
+                ("edge_dofs", c_u32p), ("edge_cells", c_u32p)]
+
+
+class CopyIndicesView(C.Structure):
+    _fields_ = [("n", C.c_uint32), ("active_idx", c_u32p), ("level_idx", c_u32p)]
+
+
 class OperatorDesc(C.Structure):
     _fields_ = [
         ("degree", C.c_int32), ("number_type", C.c_int32),
@@ -98,6 +107,7 @@ SIGNATURES = {
     "mgb_fe_p_embedding": (C.c_int, [C.c_int, C.c_int, c_f64p]),
     "mgb_mesh_create": (C.c_int, [C.c_char_p, C.c_uint, C.c_uint, PP]),
     "mgb_mesh_coarsen": (C.c_int, [P, PP]),
+    "mgb_mesh_level": (C.c_int, [P, C.c_int, PP]),
     "mgb_mesh_n_cells": (C.c_int64, [P]),
     "mgb_mesh_n_levels": (C.c_int, [P]),
     "mgb_mesh_get_cells": (C.c_int, [P, c_u32p]),
@@ -107,6 +117,13 @@ SIGNATURES = {
     "mgb_dofmap_expand": (C.c_int, [P, C.c_int, c_u32p]),
     "mgb_dofmap_destroy": (None, [P]),
     "mgb_transfer_map_create": (C.c_int, [P, P, P, P, PP]),
+    "mgb_transfer_map_create_ls": (C.c_int, [P, P, P, P, PP]),
+    "mgb_level_edges_create": (C.c_int, [P, P, PP]),
+    "mgb_level_edges_view_get": (C.c_int, [P, C.POINTER(LevelEdgesView)]),
+    "mgb_level_edges_destroy": (None, [P]),
+    "mgb_copy_indices_create": (C.c_int, [P, P, P, PP]),
+    "mgb_copy_indices_view_get": (C.c_int, [P, C.POINTER(CopyIndicesView)]),
+    "mgb_copy_indices_destroy": (None, [P]),
     "mgb_transfer_map_view_get": (C.c_int, [P, C.POINTER(TransferMapView)]),
     "mgb_transfer_map_destroy": (None, [P]),
     "mgb_vector_create": (C.c_int, [C.c_uint32, C.c_uint32, C.c_int, PP]),
@@ -128,6 +145,7 @@ SIGNATURES = {
     "mgb_vector_zero_out_ghost_values": (C.c_int, [P]),
     "mgb_operator_create": (C.c_int, [C.POINTER(OperatorDesc), PP]),
     "mgb_operator_create_from_dofmap": (C.c_int, [P, C.c_int, PP]),
+    "mgb_operator_create_level": (C.c_int, [P, P, C.c_int, PP]),
     "mgb_operator_destroy": (None, [P]),
     "mgb_operator_m": (C.c_int64, [P]),
     "mgb_operator_initialize_dof_vector": (C.c_int, [P, PP]),
@@ -156,6 +174,7 @@ SIGNATURES = {
     "mgb_problem_level_smoother": (P, [P, C.c_int]),
     "mgb_problem_level_transfer": (P, [P, C.c_int]),
     "mgb_problem_fine_operator": (P, [P]),
+    "mgb_problem_fine_dofmap": (P, [P]),
     "mgb_problem_rhs": (P, [P]),
     "mgb_problem_solution": (P, [P]),
     "mgb_problem_vcycle": (C.c_int, [P, P, P]),

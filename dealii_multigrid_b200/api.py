@@ -125,6 +125,12 @@ class Mesh:
         _check(self._lib.mgb_mesh_coarsen(self._h, C.byref(h)))
         return Mesh(_handle=h)
 
+    def level_mesh(self, level):
+        """local-smoothing level: all cells of that refinement level, active or not (multigrid_throughput.cc:2044-2046)"""
+        h = C.c_void_p()
+        _check(self._lib.mgb_mesh_level(self._h, level, C.byref(h)))
+        return Mesh(_handle=h)
+
     @property
     def n_cells(self):
         return int(self._lib.mgb_mesh_n_cells(self._h))
@@ -212,11 +218,46 @@ class DoFMap:
         self._h = None
 
 
-class TransferMap:
-    def __init__(self, mesh_fine, dofs_fine, mesh_coarse, dofs_coarse):
+class LevelEdges:
+    """refinement-edge DoFs and cells of one local-smoothing level (include/operator.h:49-99)"""
+
+    def __init__(self, level_mesh, level_dofs):
         self._lib = _lib.load()
         h = C.c_void_p()
-        _check(self._lib.mgb_transfer_map_create(mesh_fine._h, dofs_fine._h, mesh_coarse._h, dofs_coarse._h, C.byref(h)))
+        _check(self._lib.mgb_level_edges_create(level_mesh._h, level_dofs._h, C.byref(h)))
+        self._h = h
+        v = _lib.LevelEdgesView()
+        _check(self._lib.mgb_level_edges_view_get(self._h, C.byref(v)))
+        self.edge_dofs = _arr(v.edge_dofs, v.n_edge_dofs, np.uint32)
+        self.edge_cells = _arr(v.edge_cells, v.n_edge_cells, np.uint32)
+        self.any_global = bool(v.any_global)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.mgb_level_edges_destroy(self._h)
+            self._h = None
+
+
+class CopyIndices:
+    """copy_indices[level] of MGTransferMatrixFree: (active-vector index, level-vector index) pairs"""
+
+    def __init__(self, active_dofs, level_mesh, level_dofs):
+        lib = _lib.load()
+        h = C.c_void_p()
+        _check(lib.mgb_copy_indices_create(active_dofs._h, level_mesh._h, level_dofs._h, C.byref(h)))
+        v = _lib.CopyIndicesView()
+        _check(lib.mgb_copy_indices_view_get(h, C.byref(v)))
+        self.active_idx = _arr(v.active_idx, v.n, np.uint32)
+        self.level_idx = _arr(v.level_idx, v.n, np.uint32)
+        lib.mgb_copy_indices_destroy(h)
+
+
+class TransferMap:
+    def __init__(self, mesh_fine, dofs_fine, mesh_coarse, dofs_coarse, local_smoothing=False):
+        self._lib = _lib.load()
+        h = C.c_void_p()
+        create = self._lib.mgb_transfer_map_create_ls if local_smoothing else self._lib.mgb_transfer_map_create
+        _check(create(mesh_fine._h, dofs_fine._h, mesh_coarse._h, dofs_coarse._h, C.byref(h)))
         self._h = h
         v = _lib.TransferMapView()
         _check(self._lib.mgb_transfer_map_view_get(self._h, C.byref(v)))
@@ -343,7 +384,7 @@ def _ptr(a, ctype):
 class Operator:
     """Operator<3,1,Number> of include/operator.h (matrix-free Laplace with identity rows on constrained DoFs)."""
 
-    def __init__(self, dofs=None, number_type=DOUBLE, _handle=None, _owner=None, **arrays):
+    def __init__(self, dofs=None, number_type=DOUBLE, _handle=None, _owner=None, edges=None, **arrays):
         self._lib = _lib.load()
         self.number_type = number_type
         self._owner = _owner
@@ -352,7 +393,10 @@ class Operator:
             self._h = _handle
             return
         h = C.c_void_p()
-        if dofs is not None and not arrays:
+        if dofs is not None and edges is not None:
+            # level operator of the local-smoothing hierarchy (Operator::reinit with mg_level)
+            _check(self._lib.mgb_operator_create_level(dofs._h, edges._h, number_type, C.byref(h)))
+        elif dofs is not None and not arrays:
             _check(self._lib.mgb_operator_create_from_dofmap(dofs._h, number_type, C.byref(h)))
         else:
             _check(self._lib.mgb_operator_create(C.byref(self._make_desc(number_type, **arrays)), C.byref(h)))
@@ -517,6 +561,10 @@ class Problem:
 
     def fine_operator(self):
         return Operator(number_type=DOUBLE, _handle=C.c_void_p(self._lib.mgb_problem_fine_operator(self._h)), _owner=self)
+
+    def fine_dofmap(self):
+        """active-mesh DoFs of the outer operator (for local smoothing this is not a multigrid level)"""
+        return DoFMap(_handle=C.c_void_p(self._lib.mgb_problem_fine_dofmap(self._h)), _owner=self)
 
     def rhs(self):
         return Vector(_handle=C.c_void_p(self._lib.mgb_problem_rhs(self._h)), _borrowed=True, _owner=self)

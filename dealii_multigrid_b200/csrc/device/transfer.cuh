@@ -93,6 +93,8 @@ namespace mgb
       {
         // ---- tables
         const int nch = HMODE ? n_children[c] : 1;
+        if (HMODE && nch == 0)
+          continue; // local smoothing: parent without children on the fine level (warp-uniform)
         srec[lane]    = coarse_ctab[c * 32 + lane];
         {
           const size_t f0 = size_t(fine_first[c]) * 27;

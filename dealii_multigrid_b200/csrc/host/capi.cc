@@ -47,6 +47,14 @@ struct mgb_transfer_map
   TransferMap t;
   long long   n_fine_cells = 0;
 };
+struct mgb_level_edges
+{
+  LevelEdges e;
+};
+struct mgb_copy_indices
+{
+  CopyIndices c;
+};
 struct mgb_vector
 {
   int                           type = MGB_DOUBLE;
@@ -87,6 +95,7 @@ struct mgb_problem
   std::map<int, std::unique_ptr<mgb_chebyshev>>        smoothers;
   std::map<int, std::unique_ptr<mgb_transfer>>         transfers;
   std::unique_ptr<mgb_operator>                        fine_op;
+  std::unique_ptr<mgb_dofmap>                          fine_dofmap;
   std::unique_ptr<mgb_vector>                          rhs, solution;
 };
 
@@ -262,6 +271,16 @@ int mgb_mesh_coarsen(const mgb_mesh *fine, mgb_mesh **out)
     *out = h.release();
   });
 }
+int mgb_mesh_level(const mgb_mesh *active, int level, mgb_mesh **out)
+{
+  return guarded([&] {
+    if (level < 0 || level >= active->m.n_global_levels())
+      throw std::runtime_error("mgb_mesh_level: no such level");
+    auto h = std::make_unique<mgb_mesh>();
+    h->m   = active->m.level_mesh(level);
+    *out   = h.release();
+  });
+}
 int64_t mgb_mesh_n_cells(const mgb_mesh *m) { return (int64_t)m->m.cells.size(); }
 int     mgb_mesh_n_levels(const mgb_mesh *m) { return m->m.n_global_levels(); }
 int     mgb_mesh_get_cells(const mgb_mesh *m, uint32_t *o)
@@ -343,7 +362,52 @@ int mgb_transfer_map_create(const mgb_mesh *mf, const mgb_dofmap *f, const mgb_m
     *out            = h.release();
   });
 }
-int mgb_transfer_map_view_get(const mgb_transfer_map *t, mgb_transfer_map_view *v)
+int mgb_transfer_map_create_ls(const mgb_mesh *mf, const mgb_dofmap *f, const mgb_mesh *mc, const mgb_dofmap *c, mgb_transfer_map **out)
+{
+  return guarded([&] {
+    auto h          = std::make_unique<mgb_transfer_map>();
+    h->t            = TransferMap::build(mf->m, *f->d, mc->m, *c->d, /*local_smoothing=*/true);
+    h->n_fine_cells = f->d->n_cells;
+    *out            = h.release();
+  });
+}
+int mgb_level_edges_create(const mgb_mesh *level_mesh, const mgb_dofmap *level_dofs, mgb_level_edges **out)
+{
+  return guarded([&] {
+    auto h = std::make_unique<mgb_level_edges>();
+    h->e   = LevelEdges::build(level_mesh->m, *level_dofs->d);
+    *out   = h.release();
+  });
+}
+int mgb_level_edges_view_get(const mgb_level_edges *e, mgb_level_edges_view *v)
+{
+  return guarded([&] {
+    v->n_edge_dofs  = (uint32_t)e->e.edge_dofs.size();
+    v->n_edge_cells = (uint32_t)e->e.edge_cells.size();
+    v->any_global   = e->e.any_global ? 1 : 0;
+    v->edge_dofs    = e->e.edge_dofs.data();
+    v->edge_cells   = e->e.edge_cells.data();
+  });
+}
+void mgb_level_edges_destroy(mgb_level_edges *e) { delete e; }
+int  mgb_copy_indices_create(const mgb_dofmap *active_dofs, const mgb_mesh *level_mesh, const mgb_dofmap *level_dofs, mgb_copy_indices **out)
+{
+  return guarded([&] {
+    auto h = std::make_unique<mgb_copy_indices>();
+    h->c   = CopyIndices::build(*active_dofs->d, level_mesh->m, *level_dofs->d);
+    *out   = h.release();
+  });
+}
+int mgb_copy_indices_view_get(const mgb_copy_indices *c, mgb_copy_indices_view *v)
+{
+  return guarded([&] {
+    v->n          = (uint32_t)c->c.active_idx.size();
+    v->active_idx = c->c.active_idx.data();
+    v->level_idx  = c->c.level_idx.data();
+  });
+}
+void mgb_copy_indices_destroy(mgb_copy_indices *c) { delete c; }
+int  mgb_transfer_map_view_get(const mgb_transfer_map *t, mgb_transfer_map_view *v)
 {
   return guarded([&] {
     v->degree_fine    = t->t.degree_fine;
@@ -637,6 +701,29 @@ int mgb_operator_create_from_dofmap(const mgb_dofmap *dm, int type, mgb_operator
     *out            = make_operator(s, type).release();
   });
 }
+int mgb_operator_create_level(const mgb_dofmap *dm, const mgb_level_edges *edges, int type, mgb_operator **out)
+{
+  return guarded([&] {
+    const DoFMap &d = *dm->d;
+    OperatorSetup s;
+    s.degree        = d.degree;
+    s.n_cells       = d.n_cells;
+    s.entity_table  = d.eval_table.data();
+    s.mask          = d.mask.data();
+    s.cell_level    = d.cell_level.data();
+    s.constrained   = d.constrained.data();
+    s.n_constrained = (uint32_t)d.constrained.size();
+    s.n_dofs_global = d.part.n_global;
+    s.partitioner   = &d.part;
+    const LevelEdges &e            = edges->e;
+    s.edge_constrained             = e.edge_dofs.data();
+    s.n_edge_constrained           = (uint32_t)e.edge_dofs.size();
+    s.has_edge_constrained_global  = e.any_global;
+    s.edge_cells                   = e.edge_cells.data();
+    s.n_edge_cells                 = (uint32_t)e.edge_cells.size();
+    *out                           = make_operator(s, type).release();
+  });
+}
 void    mgb_operator_destroy(mgb_operator *op) { delete op; }
 int64_t mgb_operator_m(const mgb_operator *op) { return op->type == MGB_DOUBLE ? op->pd->m() : op->pf->m(); }
 
@@ -818,7 +905,7 @@ int mgb_problem_create(const char *json_text, int n_ranks, int rank, mgb_problem
         else
           sm->pf = static_cast<ChebyshevT<float> *>(h->p->level_smoother(l));
         h->smoothers[l] = std::move(sm);
-        if (l > 0)
+        if (l > 0 && h->p->level_transfer(l) != nullptr)
           {
             auto tr  = std::make_unique<mgb_transfer>();
             tr->type = type;
@@ -829,6 +916,8 @@ int mgb_problem_create(const char *json_text, int n_ranks, int rank, mgb_problem
             h->transfers[l] = std::move(tr);
           }
       }
+    h->fine_dofmap    = std::make_unique<mgb_dofmap>();
+    h->fine_dofmap->d = &h->p->fine_dofmap();
     h->fine_op       = std::make_unique<mgb_operator>();
     h->fine_op->type = MGB_DOUBLE;
     h->fine_op->pd   = &h->p->fine_operator();
@@ -855,6 +944,7 @@ const mgb_transfer *mgb_problem_level_transfer(const mgb_problem *p, int l)
   return it == p->transfers.end() ? nullptr : it->second.get();
 }
 const mgb_operator *mgb_problem_fine_operator(const mgb_problem *p) { return p->fine_op.get(); }
+const mgb_dofmap   *mgb_problem_fine_dofmap(const mgb_problem *p) { return p->fine_dofmap.get(); }
 mgb_vector         *mgb_problem_rhs(mgb_problem *p) { return p->rhs.get(); }
 mgb_vector         *mgb_problem_solution(mgb_problem *p) { return p->solution.get(); }
 

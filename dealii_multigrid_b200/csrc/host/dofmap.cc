@@ -364,12 +364,13 @@ namespace mgb
         }
   }
 
-  TransferMap TransferMap::build(const Mesh &mesh_fine, const DoFMap &df, const Mesh &mesh_coarse, const DoFMap &dc)
+  TransferMap TransferMap::build(const Mesh &mesh_fine, const DoFMap &df, const Mesh &mesh_coarse, const DoFMap &dc,
+                                 const bool local_smoothing)
   {
     if (df.n_ranks != dc.n_ranks || df.rank != dc.rank)
       throw std::runtime_error("TransferMap: fine and coarse DoF maps belong to different partitions");
     if (df.n_ranks > 1)
-      return build_distributed(mesh_fine, df, mesh_coarse, dc);
+      return build_distributed(mesh_fine, df, mesh_coarse, dc, local_smoothing);
     TransferMap tm;
     tm.degree_fine    = df.degree;
     tm.degree_coarse  = dc.degree;
@@ -379,17 +380,17 @@ namespace mgb
     int64_t f = 0;
     for (int64_t c = 0; c < dc.n_cells; ++c)
       {
-        const Cell &cc = mesh_coarse.cells[c];
-        if (f >= df.n_cells)
-          throw std::runtime_error("TransferMap: fine mesh exhausted");
-        const Cell &fc = mesh_fine.cells[f];
-        if (fc.level == cc.level && fc.x == cc.x && fc.y == cc.y && fc.z == cc.z)
+        const Cell &cc        = mesh_coarse.cells[c];
+        const Cell *fc        = f < df.n_cells ? &mesh_fine.cells[f] : nullptr;
+        const bool  same      = fc && fc->level == cc.level && fc->x == cc.x && fc->y == cc.y && fc->z == cc.z;
+        const bool  first_kid = fc && fc->level == cc.level + 1 && fc->x == 2 * cc.x && fc->y == 2 * cc.y && fc->z == 2 * cc.z;
+        tm.fine_first[c]      = uint32_t(std::min<int64_t>(f, std::max<int64_t>(df.n_cells - 1, 0)));
+        if (same && !local_smoothing)
           {
-            tm.fine_first[c] = uint32_t(f);
             tm.n_children[c] = 1;
             f += 1;
           }
-        else
+        else if (first_kid)
           {
             for (unsigned ch = 0; ch < 8; ++ch)
               {
@@ -400,10 +401,14 @@ namespace mgb
                       s.z == 2 * cc.z + ((ch >> 2) & 1)))
                   throw std::runtime_error("TransferMap: fine mesh is not a one-level refinement of the coarse mesh");
               }
-            tm.fine_first[c] = uint32_t(f);
             tm.n_children[c] = 8;
             f += 8;
           }
+        else if (local_smoothing)
+          tm.n_children[c] = 0; // not refined: no cells on the fine level
+        else
+          throw std::runtime_error(fc ? "TransferMap: fine mesh is not a one-level refinement of the coarse mesh" :
+                                        "TransferMap: fine mesh exhausted");
       }
     if (f != df.n_cells)
       throw std::runtime_error("TransferMap: fine cells left over");
@@ -445,7 +450,8 @@ namespace mgb
   // reference's DefaultPolicy), so the children of a locally owned coarse cell may belong to other ranks.  As in
   // MGTwoLevelTransfer, the transfer gets its own fine-side numbering: the fine level's owned range plus the ghost DoFs
   // of those children; every rank derives the ghost/import lists of all ranks from the replicated global numbering.
-  TransferMap TransferMap::build_distributed(const Mesh &mesh_fine, const DoFMap &df, const Mesh &mesh_coarse, const DoFMap &dc)
+  TransferMap TransferMap::build_distributed(const Mesh &mesh_fine, const DoFMap &df, const Mesh &mesh_coarse, const DoFMap &dc,
+                                             const bool local_smoothing)
   {
     if (!df.global_entities)
       throw std::runtime_error("TransferMap: the fine DoF map does not carry the global numbering");
@@ -469,14 +475,14 @@ namespace mgb
       for (int64_t c = 0; c < ncc; ++c)
         {
           const Cell &cc = mesh_coarse.cells[c];
-          if (f >= nfc)
-            throw std::runtime_error("TransferMap: fine mesh exhausted");
-          const Cell &fc = mesh_fine.cells[f];
-          first[c]       = f;
-          if (fc.level == cc.level && fc.x == cc.x && fc.y == cc.y && fc.z == cc.z)
+          const Cell *fc = f < nfc ? &mesh_fine.cells[f] : nullptr;
+          first[c]       = std::min<int64_t>(f, std::max<int64_t>(nfc - 1, 0));
+          if (!local_smoothing && fc && fc->level == cc.level && fc->x == cc.x && fc->y == cc.y && fc->z == cc.z)
             nch[c] = 1;
-          else if (fc.level == cc.level + 1 && (fc.x >> 1) == cc.x && (fc.y >> 1) == cc.y && (fc.z >> 1) == cc.z && f + 8 <= nfc)
+          else if (fc && fc->level == cc.level + 1 && (fc->x >> 1) == cc.x && (fc->y >> 1) == cc.y && (fc->z >> 1) == cc.z && f + 8 <= nfc)
             nch[c] = 8;
+          else if (local_smoothing)
+            nch[c] = 0;
           else
             throw std::runtime_error("TransferMap: fine mesh is not a one-level refinement of the coarse mesh");
           f += nch[c];
@@ -640,5 +646,124 @@ namespace mgb
           tm.weight_code[k] = valence[needed.find(uint64_t(g_own[k]))];
       }
     return tm;
+  }
+
+  // ------------------------------------------------------------------------------------------ local smoothing
+  namespace
+  {
+    // keys of the level entities lying on a face between a level cell and the region without level cells (covered by
+    // a coarser active cell): MGTools::extract_inner_interface_dofs marks all DoFs of such faces
+    void refinement_edge_entities(const Mesh &lm, const EntityKeys &K, FlatMap &edge)
+    {
+      for (const Cell &c : lm.cells)
+        {
+          const int64_t  N     = int64_t(1) << c.level;
+          const uint32_t co[3] = {c.x, c.y, c.z};
+          for (int d = 0; d < 3; ++d)
+            for (int s = 0; s < 2; ++s)
+              {
+                int64_t n[3] = {co[0], co[1], co[2]};
+                n[d] += s ? 1 : -1;
+                if (n[d] < 0 || n[d] >= N)
+                  continue; // domain boundary: Dirichlet, not a refinement edge
+                if (lm.leaf(c.level, uint32_t(n[0]), uint32_t(n[1]), uint32_t(n[2])) >= 0)
+                  continue;
+                for (int e = 0; e < 27; ++e)
+                  {
+                    const int t[3] = {e % 3, (e / 3) % 3, e / 9};
+                    if (t[d] != 2 * s)
+                      continue;
+                    const uint64_t key = K(c.level, c.x, c.y, c.z, e);
+                    if (edge.find(key) < 0)
+                      edge.insert(key, 1);
+                  }
+              }
+        }
+    }
+  } // namespace
+
+  LevelEdges LevelEdges::build(const Mesh &lm, const DoFMap &dm)
+  {
+    LevelEdges       le;
+    const EntityKeys K{dm.mesh_max_level};
+    int              esize[27];
+    for (int e = 0; e < 27; ++e)
+      esize[e] = ipow(dm.degree - 1, entity_dim(e));
+    FlatMap edge;
+    refinement_edge_entities(lm, K, edge);
+    le.any_global = edge.size() > 0;
+    if (!le.any_global)
+      return le;
+    for (int64_t c = 0; c < dm.n_cells; ++c)
+      {
+        bool touches = false;
+        for (int e = 0; e < 27; ++e)
+          {
+            if (esize[e] == 0)
+              continue;
+            const uint64_t key = K(dm.cell_level[c], dm.cell_xyz[3 * c], dm.cell_xyz[3 * c + 1], dm.cell_xyz[3 * c + 2], e);
+            if (edge.find(key) < 0)
+              continue;
+            touches            = true;
+            const uint32_t base = dm.own_table[c * 27 + e] & INDEX_MASK;
+            if (base < dm.part.n_owned)
+              for (int k = 0; k < esize[e]; ++k)
+                le.edge_dofs.push_back(base + uint32_t(k));
+          }
+        if (touches)
+          le.edge_cells.push_back(uint32_t(c));
+      }
+    std::sort(le.edge_dofs.begin(), le.edge_dofs.end());
+    le.edge_dofs.erase(std::unique(le.edge_dofs.begin(), le.edge_dofs.end()), le.edge_dofs.end());
+    return le;
+  }
+
+  CopyIndices CopyIndices::build(const DoFMap &ad, const Mesh &lm, const DoFMap &ld)
+  {
+    if (ad.n_ranks > 1 || ld.n_ranks > 1)
+      throw std::runtime_error("CopyIndices: local smoothing on several ranks is not available yet (copy_indices_global_mine)");
+    if (ad.degree != ld.degree)
+      throw std::runtime_error("CopyIndices: degrees differ");
+    CopyIndices      ci;
+    const int        level = ld.mesh_max_level;
+    const EntityKeys K{level};
+    int              esize[27];
+    for (int e = 0; e < 27; ++e)
+      esize[e] = ipow(ad.degree - 1, entity_dim(e));
+    FlatMap edge;
+    refinement_edge_entities(lm, K, edge);
+    struct Seg
+    {
+      uint32_t a, b;
+      int      size;
+      bool     operator<(const Seg &o) const { return a < o.a; }
+      bool     operator==(const Seg &o) const { return a == o.a; }
+    };
+    std::vector<Seg> segs;
+    for (int64_t c = 0; c < ad.n_cells; ++c)
+      {
+        if (ad.cell_level[c] != level)
+          continue;
+        const uint32_t x = ad.cell_xyz[3 * c], y = ad.cell_xyz[3 * c + 1], z = ad.cell_xyz[3 * c + 2];
+        const int64_t  j = lm.leaf(level, x, y, z);
+        if (j < ld.cell_begin || j >= ld.cell_begin + ld.n_cells)
+          throw std::runtime_error("CopyIndices: active cell not found on its level");
+        const int64_t lc = j - ld.cell_begin;
+        for (int e = 0; e < 27; ++e)
+          {
+            if (esize[e] == 0 || edge.find(K(level, x, y, z, e)) >= 0)
+              continue;
+            segs.push_back(Seg{ad.own_table[c * 27 + e] & INDEX_MASK, ld.own_table[lc * 27 + e] & INDEX_MASK, esize[e]});
+          }
+      }
+    std::sort(segs.begin(), segs.end());
+    segs.erase(std::unique(segs.begin(), segs.end()), segs.end());
+    for (const Seg &sg : segs)
+      for (int k = 0; k < sg.size; ++k)
+        {
+          ci.active_idx.push_back(sg.a + uint32_t(k));
+          ci.level_idx.push_back(sg.b + uint32_t(k));
+        }
+    return ci;
   }
 } // namespace mgb

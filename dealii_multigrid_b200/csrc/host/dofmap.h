@@ -116,11 +116,34 @@ namespace mgb
     int64_t               n_fine_slots = 0;
     bool                  distributed  = false;
     Partitioner           part;
+    // local_smoothing: the two meshes are consecutive levels of the refinement tree (Mesh::level_mesh); a coarse cell
+    // then has 8 children on the fine level or none at all (n_children 0: contributes nothing, MGTransferMatrixFree,
+    // SURVEY.md A.8)
     static TransferMap build(const Mesh &mesh_fine, const DoFMap &dofs_fine, const Mesh &mesh_coarse,
-                             const DoFMap &dofs_coarse);
+                             const DoFMap &dofs_coarse, bool local_smoothing = false);
 
   private:
     static TransferMap build_distributed(const Mesh &mesh_fine, const DoFMap &dofs_fine, const Mesh &mesh_coarse,
-                                         const DoFMap &dofs_coarse);
+                                         const DoFMap &dofs_coarse, bool local_smoothing);
+  };
+
+  // Refinement-edge data of one local-smoothing level: MGConstrainedDoFs::refinement_edge_indices /
+  // MGTools::extract_inner_interface_dofs (include/operator.h:49-66, 539-556) and the cells that touch such a DoF
+  // (edge_constrained_cell, include/operator.h:71-99).
+  struct LevelEdges
+  {
+    std::vector<uint32_t> edge_dofs;  // owned local indices, ascending
+    std::vector<uint32_t> edge_cells; // local cells touching an edge DoF (owned or ghost), ascending
+    bool                  any_global = false; // include/operator.h:67-69
+    static LevelEdges build(const Mesh &level_mesh, const DoFMap &level_dofs);
+  };
+
+  // copy_indices of MGLevelGlobalTransfer: pairs (active-vector index, level-vector index) of the DoFs of
+  // the ACTIVE cells living on this level, refinement-edge DoFs of the level skipped (fill_copy_indices with
+  // skip_interface_dofs = true).
+  struct CopyIndices
+  {
+    std::vector<uint32_t> active_idx, level_idx;
+    static CopyIndices build(const DoFMap &active_dofs, const Mesh &level_mesh, const DoFMap &level_dofs);
   };
 } // namespace mgb

@@ -254,6 +254,23 @@ namespace mgb
     return out;
   }
 
+  Mesh Mesh::level_mesh(int level) const
+  {
+    // leaves are Morton-ordered, so the level-`level` ancestors of the leaves at least that fine appear in Morton order too
+    Mesh out;
+    for (const Cell &c : cells)
+      {
+        if (c.level < level)
+          continue;
+        const int  s = c.level - level;
+        const Cell a{c.x >> s, c.y >> s, c.z >> s, uint8_t(level)};
+        if (out.cells.empty() || out.cells.back().x != a.x || out.cells.back().y != a.y || out.cells.back().z != a.z)
+          out.cells.push_back(a);
+      }
+    out.rebuild_index();
+    return out;
+  }
+
   Mesh Mesh::create(const std::string &geometry, unsigned n_ref_global, unsigned n_ref_local)
   {
     Mesh m;

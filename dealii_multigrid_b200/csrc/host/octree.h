@@ -56,6 +56,9 @@ namespace mgb
     // one global coarsening step: every complete family of 8 leaves -> parent, then balance
     // (MGTransferGlobalCoarseningTools::create_geometric_coarsening_sequence, ref :2219-2224)
     Mesh coarsen_global() const;
+    // local-smoothing level l of the refinement tree: ALL cells of refinement level l, active or not (SURVEY.md A.1,
+    // construct_multigrid_hierarchy, ref :2044-2046).  The result does not cover the domain where coarser leaves live.
+    Mesh level_mesh(int level) const;
 
     void rebuild_index();
     // leaf index of the cell (level,x,y,z); -1 if that cell is not a leaf

@@ -370,6 +370,15 @@ namespace mgb
       std::vector<Level>                 levels;
       std::vector<TransferMap>           tmaps;
       GCTransferT<LT>                    transfer;
+      // local smoothing (solve_with_local_smoothing, ref :1673-1873)
+      LSTransferT<LT>                    ls_transfer;
+      std::vector<LevelEdges>            level_edges;
+      std::unique_ptr<DoFMap>            fine_dofs_own; // HMG-local: active-mesh DoFs (not a multigrid level)
+      const DoFMap                      *fine_dofs = nullptr;
+      MultigridT<LT>                     mg_inter;      // HPMG-local: LS V-cycle nested as coarse solver (ref :1093-1114)
+      PreconditionMGT<LT>                precond_inter;
+      CoarseApplyMGT<LT>                 coarse_apply;
+      bool                               local_smoothing = false;
       std::unique_ptr<OperatorT<double>> fine_op_own;
       OperatorT<double>                 *fine_op = nullptr;
       DVec<double>                       rhs_, solution_;
@@ -395,14 +404,17 @@ namespace mgb
         const std::string &type = prm.type;
         if (type == "AMG" || type == "AMGPETSc")
           throw std::runtime_error("Type '" + type + "' (Trilinos ML / hypre BoomerAMG) is out of scope of the B200 hot path");
-        if (type == "HMG-local" || type == "HPMG-local")
-          throw std::runtime_error("Type '" + type + "': local smoothing is not available in this build yet");
-        if (type != "PMG" && type != "HMG-global" && type != "HPMG")
+        if (type != "PMG" && type != "HMG-global" && type != "HPMG" && type != "HMG-local" && type != "HPMG-local")
           throw std::runtime_error("unknown Type '" + type + "'");
         const std::string &cs = prm.mg_data.coarse_solver.type;
         if (cs != "cg" && cs != "cg_with_chebyshev")
           throw std::runtime_error("CoarseGridSolverType '" + cs +
                                    "' needs Trilinos/PETSc AMG (out of scope); use \"cg\" or \"cg_with_chebyshev\"");
+        if (type == "HMG-local" || type == "HPMG-local")
+          {
+            build_local_smoothing();
+            return;
+          }
 
         // geometric coarsening sequence (ref :2219-2224), then MinLevel / MinNCells trimming (ref :2227-2260)
         {
@@ -506,10 +518,145 @@ namespace mgb
         precond.transfer = &transfer;
         precond.timers   = &timers;
 
-        // outer FP64 operator on the finest level (ref :2262-2316) and right-hand side (ref :2324)
-        const DoFMap &fd = *levels.back().dofs;
-        if constexpr (std::is_same<LT, double>::value)
-          fine_op = levels.back().op.get();
+        finish_fine(*levels.back().dofs, levels.back().op.get());
+      }
+
+      // solve_with_local_smoothing (ref :1673-1873) + mg_solve wiring (ref :1082-1133)
+      void build_local_smoothing()
+      {
+        local_smoothing   = true;
+        const bool do_pmg = prm.type == "HPMG-local";
+        const std::vector<unsigned> level_degrees =
+          do_pmg ? polynomial_coarsening_sequence_bisect(prm.fe_degree_fine) : std::vector<unsigned>{prm.fe_degree_fine};
+        Mesh           active = Mesh::create(prm.geometry_type, prm.n_ref_global, prm.n_ref_local);
+        const unsigned nl     = (unsigned)active.n_global_levels(); // LS levels 0 .. nl-1
+        const bool     has_hanging = !active.uniform();
+        for (unsigned l = 0; l < nl; ++l)
+          meshes.push_back(active.level_mesh(int(l)));
+        meshes.push_back(std::move(active));
+        for (auto &m : meshes)
+          m.rebuild_index();
+        const unsigned max_level = (nl - 1) + (do_pmg ? (unsigned)level_degrees.size() : 0); // ref :1720-1723
+        levels.resize(max_level + 1);
+        level_edges.resize(nl);
+        // LS levels: all cells of level l, lowest degree, homogeneous Dirichlet only (ref :1746-1768)
+        for (unsigned l = 0; l < nl; ++l)
+          {
+            Level &L     = levels[l];
+            L.degree     = (int)level_degrees.front();
+            L.mesh_index = (int)l;
+            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[l], L.degree, n_ranks, rank, /*min_cells_per_rank=*/512));
+            level_edges[l]   = LevelEdges::build(meshes[l], *L.dofs);
+            OperatorSetup st = setup_from_dofmap(*L.dofs);
+            st.edge_constrained            = level_edges[l].edge_dofs.data();
+            st.n_edge_constrained          = (uint32_t)level_edges[l].edge_dofs.size();
+            st.has_edge_constrained_global = level_edges[l].any_global;
+            st.edge_cells                  = level_edges[l].edge_cells.data();
+            st.n_edge_cells                = (uint32_t)level_edges[l].edge_cells.size();
+            L.op = std::make_unique<OperatorT<LT>>(st);
+          }
+        // p-levels on the active mesh: Dirichlet + hanging-node constraints (ref :1770-1796)
+        for (unsigned l = nl; l <= max_level; ++l)
+          {
+            Level &L     = levels[l];
+            L.degree     = (int)level_degrees[l - nl];
+            L.mesh_index = (int)nl;
+            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], L.degree, n_ranks, rank, 512));
+            L.op         = std::make_unique<OperatorT<LT>>(setup_from_dofmap(*L.dofs));
+          }
+        // the active-mesh DoFs the LS transfer copies from / to (dof_handlers.front())
+        const DoFMap *active_low = nullptr;
+        if (do_pmg)
+          active_low = levels[nl].dofs.get();
+        else
+          {
+            fine_dofs_own = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], (int)prm.fe_degree_fine, n_ranks, rank, 512));
+            active_low    = fine_dofs_own.get();
+          }
+        // MGTransferMatrixFree::build (ref :1800-1802)
+        tmaps.resize(max_level + 1);
+        ls_transfer.transfers.resize(nl);
+        ls_transfer.operators.resize(nl);
+        for (unsigned l = 0; l < nl; ++l)
+          {
+            ls_transfer.operators[l] = levels[l].op.get();
+            ls_transfer.set_copy_indices(l, CopyIndices::build(*active_low, meshes[l], *levels[l].dofs));
+          }
+        for (unsigned l = 0; l + 1 < nl; ++l)
+          {
+            tmaps[l + 1] = TransferMap::build(meshes[l + 1], *levels[l + 1].dofs, meshes[l], *levels[l].dofs, /*local_smoothing=*/true);
+            ls_transfer.transfers[l + 1] =
+              std::make_unique<TwoLevelTransferT<LT>>(*levels[l + 1].dofs, *levels[l].dofs, tmaps[l + 1], *levels[l + 1].op, *levels[l].op);
+          }
+        // p-transfers between the active-mesh levels (ref :1804-1817)
+        transfer.min_level = nl;
+        transfer.transfers.resize(max_level >= nl ? max_level - nl + 1 : 0);
+        transfer.operators.resize(transfer.transfers.size());
+        for (unsigned l = nl; l <= max_level; ++l)
+          transfer.operators[l - nl] = levels[l].op.get();
+        for (unsigned l = nl; l < max_level; ++l)
+          {
+            tmaps[l + 1] = TransferMap::build(meshes[nl], *levels[l + 1].dofs, meshes[nl], *levels[l].dofs);
+            transfer.transfers[l + 1 - nl] =
+              std::make_unique<TwoLevelTransferT<LT>>(*levels[l + 1].dofs, *levels[l].dofs, tmaps[l + 1], *levels[l + 1].op, *levels[l].op);
+          }
+        for (unsigned l = 0; l <= max_level; ++l)
+          levels[l].smoother = std::make_unique<ChebyshevT<LT>>(*levels[l].op, (int)prm.mg_data.smoother.degree,
+                                                                prm.mg_data.smoother.smoothing_range,
+                                                                prm.mg_data.smoother.eig_cg_n_iterations);
+        if (prm.mg_data.coarse_solver.type == "cg_with_chebyshev")
+          coarse_cheb = std::make_unique<ChebyshevT<LT>>(*levels[0].op, (int)prm.mg_data.smoother.degree,
+                                                         prm.mg_data.smoother.smoothing_range, prm.mg_data.smoother.eig_cg_n_iterations);
+        coarse = std::make_unique<CoarseCGT<LT>>(*levels[0].op, coarse_cheb.get(), prm.mg_data.coarse_solver.maxiter,
+                                                 prm.mg_data.coarse_solver.abstol, prm.mg_data.coarse_solver.reltol);
+        // LS multigrid over [0, nl-1]; edge_in only on meshes with hanging nodes (ref :1101-1105, 1126-1130)
+        MultigridT<LT> &mls = do_pmg ? mg_inter : mg;
+        mls.min_level       = 0;
+        mls.max_level       = nl - 1;
+        for (unsigned l = 0; l < nl; ++l)
+          {
+            mls.matrices.push_back(levels[l].op.get());
+            mls.smoothers.push_back(levels[l].smoother.get());
+          }
+        mls.transfer = &ls_transfer;
+        mls.coarse   = coarse.get();
+        mls.edge_in  = has_hanging;
+        mls.timers   = &timers;
+        if (do_pmg)
+          {
+            precond_inter.mg       = &mg_inter;
+            precond_inter.transfer = &ls_transfer;
+            precond_inter.timers   = &timers;
+            coarse_apply.pmg       = &precond_inter;
+            mg.min_level           = nl;
+            mg.max_level           = max_level;
+            for (unsigned l = nl; l <= max_level; ++l)
+              {
+                mg.matrices.push_back(levels[l].op.get());
+                mg.smoothers.push_back(levels[l].smoother.get());
+              }
+            mg.transfer      = &transfer;
+            mg.coarse        = &coarse_apply;
+            mg.edge_in       = false;
+            mg.timers        = &timers;
+            precond.transfer = &transfer;
+          }
+        else
+          precond.transfer = &ls_transfer;
+        precond.mg     = &mg;
+        precond.timers = &timers;
+        if (do_pmg)
+          finish_fine(*levels.back().dofs, levels.back().op.get());
+        else
+          finish_fine(*fine_dofs_own, nullptr);
+      }
+
+      // outer FP64 operator on the active mesh (ref :2262-2316) and right-hand side (ref :2324)
+      void finish_fine(const DoFMap &fd, OperatorT<LT> *level_op)
+      {
+        fine_dofs = &fd;
+        if (std::is_same<LT, double>::value && level_op)
+          fine_op = reinterpret_cast<OperatorT<double> *>(level_op);
         else
           {
             fine_op_own = std::make_unique<OperatorT<double>>(setup_from_dofmap(fd));
@@ -532,7 +679,13 @@ namespace mgb
       const Mesh       &level_mesh(int l) const override { return meshes.at(levels.at(l).mesh_index); }
       void             *level_operator(int l) override { return levels.at(l).op.get(); }
       void             *level_smoother(int l) override { return levels.at(l).smoother.get(); }
-      void             *level_transfer(int l) override { return transfer.transfers.at(l).get(); }
+      void             *level_transfer(int l) override
+      {
+        if (local_smoothing && l < (int)ls_transfer.transfers.size())
+          return ls_transfer.transfers.at(l).get();
+        return transfer.transfers.at(l - transfer.min_level).get();
+      }
+      const DoFMap     &fine_dofmap() const override { return *fine_dofs; }
       OperatorT<double> &fine_operator() override { return *fine_op; }
       DVec<double>     &rhs() override { return rhs_; }
       DVec<double>     &solution() override { return solution_; }
@@ -563,7 +716,7 @@ namespace mgb
         r.final_residual    = ctl.last_value;
         r.coarse_iterations = coarse->collect_device_iterations();
         // every lazy initialisation has happened now: later V-cycles may be replayed from a CUDA graph
-        precond.allow_graph = coarse->single_kernel();
+        precond.allow_graph = coarse->single_kernel() && !local_smoothing;
         std::vector<std::array<double, N_STAGES + 2>> st(levels.size());
         for (auto &a : st)
           a.fill(0.0);
@@ -580,10 +733,10 @@ namespace mgb
         r.n_ref_global = (int)prm.n_ref_global;
         r.n_ref_local  = (int)prm.n_ref_local;
         r.n_levels     = (int)levels.size();
-        r.n_cells      = levels.back().dofs->n_cells_global;
+        r.n_cells      = fine_dofs->n_cells_global;
         r.n_cells_hn   = n_cells_hn;
         r.n_cells_n    = n_cells_n;
-        r.n_dofs       = levels.back().dofs->part.n_global;
+        r.n_dofs       = fine_dofs->part.n_global;
         r.sub_comm_size = n_ranks;
         const int its  = std::max(1, r.n_iterations);
         double    sum  = 0;

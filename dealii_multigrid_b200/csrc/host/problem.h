@@ -76,6 +76,7 @@ namespace mgb
     virtual void          *level_smoother(int l)            = 0; // ChebyshevT<LevelNumber>*
     virtual void          *level_transfer(int l)            = 0; // TwoLevelTransferT<LevelNumber>* (l-1 <-> l)
     virtual OperatorT<double> &fine_operator()              = 0;
+    virtual const DoFMap  &fine_dofmap() const              = 0; // active-mesh DoFs of the outer operator
     virtual DVec<double>  &rhs()                            = 0;
     virtual DVec<double>  &solution()                       = 0;
     virtual int            level_number_type() const        = 0;

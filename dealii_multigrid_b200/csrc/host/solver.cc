@@ -561,6 +561,36 @@ namespace mgb
     ++c.launches;
   }
 
+  template <typename T>
+  void LSTransferT<T>::copy_to_mg(std::vector<DVec<T>> &defect, unsigned minl, unsigned maxl, const DVec<double> &src, bool skip_top) const
+  {
+    if (skip_top)
+      throw std::logic_error("LSTransfer::copy_to_mg: the top level is not a plain copy");
+    Context &c = ctx();
+    for (unsigned l = minl; l <= maxl; ++l)
+      {
+        DVec<T> &d = defect[l - minl];
+        d.reinit_keep_layout(operators[l]->partitioner()); // zero: restriction adds into it
+        const uint32_t n = (uint32_t)copy[l].active_idx.n;
+        if (n)
+          idx_pair_copy<T, double>(d.data, copy[l].level_idx.ptr, src.data, copy[l].active_idx.ptr, n, c.stream), ++c.launches;
+      }
+  }
+
+  template <typename T>
+  void LSTransferT<T>::copy_from_mg(DVec<double> &dst, const std::vector<DVec<T>> &solution, unsigned minl, unsigned maxl) const
+  {
+    Context &c = ctx();
+    dst.zero(); // constrained (hanging) active DoFs are in no level's copy list
+    for (unsigned l = minl; l <= maxl; ++l)
+      {
+        const uint32_t n = (uint32_t)copy[l].active_idx.n;
+        if (n)
+          idx_pair_copy<double, T>(dst.data, copy[l].active_idx.ptr, solution[l - minl].data, copy[l].level_idx.ptr, n, c.stream),
+            ++c.launches;
+      }
+  }
+
   // ------------------------------------------------------------------------------------------ coarse solver
   template <typename T> void CoarseCGT<T>::setup_dense()
   {
@@ -646,13 +676,15 @@ namespace mgb
       return;
     Rec r{get(), get(), level, stage};
     MGB_CUDA(cudaEventRecord(r.a, ctx().stream));
+    open.push_back(recs.size()); // stages nest when a V-cycle is the coarse solver of another one (HPMG-local)
     recs.push_back(r);
   }
   void StageTimers::end()
   {
-    if (!enabled)
+    if (!enabled || open.empty())
       return;
-    MGB_CUDA(cudaEventRecord(recs.back().b, ctx().stream));
+    MGB_CUDA(cudaEventRecord(recs[open.back()].b, ctx().stream));
+    open.pop_back();
   }
   void StageTimers::collect(std::vector<std::array<double, N_STAGES + 2>> &times, int min_level)
   {
@@ -664,6 +696,7 @@ namespace mgb
         times[r.level - min_level][r.stage] += ms * 1e-3;
       }
     recs.clear();
+    open.clear();
     pool_next = 0;
   }
   StageTimers::~StageTimers()
@@ -742,7 +775,8 @@ namespace mgb
   {
     Context   &c = ctx();
     bool graph_ok = allow_graph && c.stream != nullptr && !(timers && timers->enabled) && !c.prof_enabled &&
-                    !(c.comm && c.comm->size() > 1) && std::is_same<T, double>::value && !mg->edge_in && src.data != dst.data;
+                    !(c.comm && c.comm->size() > 1) && std::is_same<T, double>::value && !mg->edge_in && src.data != dst.data &&
+                    transfer->top_level_is_plain_copy();
     if (graph_ok)
       {
         // only the aliasing path (no allocation, no copies) is captured
@@ -802,7 +836,7 @@ namespace mgb
         uint32_t                           no, ng;
         std::shared_ptr<DevicePartitioner> part;
         transfer->level_layout(mg->max_level, no, ng, part);
-        alias = !mg->edge_in && src.n_owned == no && src.n_ghost == ng && dst.n_owned == no && dst.n_ghost == ng && src.data != dst.data;
+        alias = transfer->top_level_is_plain_copy() && !mg->edge_in && src.n_owned == no && src.n_ghost == ng && dst.n_owned == no && dst.n_ghost == ng && src.data != dst.data;
         if (alias)
           {
             mg->defect[top].wrap(const_cast<double *>(src.data), no, ng, part);
@@ -854,6 +888,8 @@ namespace mgb
   template class TwoLevelTransferT<float>;
   template class GCTransferT<double>;
   template class GCTransferT<float>;
+  template class LSTransferT<double>;
+  template class LSTransferT<float>;
   template class MultigridT<double>;
   template class MultigridT<float>;
   template class PreconditionMGT<double>;

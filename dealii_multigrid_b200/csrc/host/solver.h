@@ -454,6 +454,9 @@ namespace mgb
     // layout of the level vectors on `level` (initialize_dof_vector of that level's operator)
     virtual void level_layout(unsigned level, uint32_t &n_owned, uint32_t &n_ghost, std::shared_ptr<DevicePartitioner> &part) const = 0;
     virtual void copy_from_mg(DVec<double> &dst, const std::vector<DVec<T>> &solution, unsigned min_level, unsigned max_level) const = 0;
+    // true if copy_to_mg / copy_from_mg only touch the top level and are plain copies there (global coarsening): the
+    // V-cycle may then work directly on the caller's vectors
+    virtual bool top_level_is_plain_copy() const { return true; }
   };
 
   // MGTransferGlobalCoarsening: vector of two-level transfers; transfers[l] connects l-1 and l
@@ -479,6 +482,44 @@ namespace mgb
       n_ghost = part->host.n_ghost;
     }
     void copy_from_mg(DVec<double> &dst, const std::vector<DVec<T>> &solution, unsigned minl, unsigned maxl) const override;
+  };
+
+  // MGTransferMatrixFree (local smoothing; multigrid_throughput.cc:1800-1802): level-to-level transfers
+  // over refined parents only + copy_indices between the active-mesh vector and the level vectors
+  template <typename T> class LSTransferT : public MGTransferBase<T>
+  {
+  public:
+    std::vector<std::unique_ptr<TwoLevelTransferT<T>>> transfers; // index l (entry 0 unused)
+    std::vector<const OperatorT<T> *>                  operators; // index l
+    struct Copy
+    {
+      DeviceBuffer<uint32_t> active_idx, level_idx;
+    };
+    std::vector<Copy> copy; // index l
+    void              set_copy_indices(unsigned level, const CopyIndices &ci)
+    {
+      if (copy.size() <= level)
+        copy.resize(level + 1);
+      copy[level].active_idx.upload(ci.active_idx.data(), ci.active_idx.size());
+      copy[level].level_idx.upload(ci.level_idx.data(), ci.level_idx.size());
+    }
+    void prolongate_and_add(unsigned to_level, DVec<T> &dst, const DVec<T> &src) const override
+    {
+      transfers[to_level]->prolongate_and_add(dst, src);
+    }
+    void restrict_and_add(unsigned from_level, DVec<T> &dst, const DVec<T> &src) const override
+    {
+      transfers[from_level]->restrict_and_add(dst, src);
+    }
+    void copy_to_mg(std::vector<DVec<T>> &defect, unsigned minl, unsigned maxl, const DVec<double> &src, bool skip_top = false) const override;
+    void level_layout(unsigned level, uint32_t &n_owned, uint32_t &n_ghost, std::shared_ptr<DevicePartitioner> &part) const override
+    {
+      part    = operators[level]->partitioner();
+      n_owned = part->host.n_owned;
+      n_ghost = part->host.n_ghost;
+    }
+    void copy_from_mg(DVec<double> &dst, const std::vector<DVec<T>> &solution, unsigned minl, unsigned maxl) const override;
+    bool top_level_is_plain_copy() const override { return false; }
   };
 
   // ------------------------------------------------------------------------------------------ multigrid
@@ -547,6 +588,7 @@ namespace mgb
       int         level, stage;
     };
     std::vector<Rec>         recs;
+    std::vector<size_t>      open; // indices of the records whose end event is still to come
     std::vector<cudaEvent_t> pool;
     size_t                   pool_next = 0;
     cudaEvent_t              get();

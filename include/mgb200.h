@@ -43,6 +43,8 @@ extern "C" {
 typedef struct mgb_mesh         mgb_mesh;
 typedef struct mgb_dofmap       mgb_dofmap;
 typedef struct mgb_transfer_map mgb_transfer_map;
+typedef struct mgb_level_edges  mgb_level_edges;
+typedef struct mgb_copy_indices mgb_copy_indices;
 typedef struct mgb_vector       mgb_vector;
 typedef struct mgb_operator     mgb_operator;
 typedef struct mgb_chebyshev    mgb_chebyshev;
@@ -78,6 +80,9 @@ int mgb_fe_p_embedding(int degree_fine, int degree_coarse, double *Pp);
 /* ---- stand-in setup: octree mesh (include/grid_generator.h, multigrid_throughput.cc:2048-2062) --- */
 int     mgb_mesh_create(const char *geometry_type, unsigned n_ref_global, unsigned n_ref_local, mgb_mesh **out);
 int     mgb_mesh_coarsen(const mgb_mesh *fine, mgb_mesh **out); /* one global-coarsening step (:2219-2224) */
+/* local-smoothing level of the refinement tree: ALL cells of that level, active or not
+ * (Triangulation::construct_multigrid_hierarchy, multigrid_throughput.cc:2044-2046) */
+int     mgb_mesh_level(const mgb_mesh *active, int level, mgb_mesh **out);
 int64_t mgb_mesh_n_cells(const mgb_mesh *m);
 int     mgb_mesh_n_levels(const mgb_mesh *m);
 int     mgb_mesh_get_cells(const mgb_mesh *m, uint32_t *level_x_y_z /* n_cells*4 */);
@@ -115,7 +120,7 @@ typedef struct
   int32_t         degree_fine, degree_coarse;
   int64_t         n_coarse_cells, n_fine_cells;
   const uint32_t *fine_first;  /* n_coarse_cells */
-  const uint8_t  *n_children;  /* n_coarse_cells: 1 or 8 */
+  const uint8_t  *n_children;  /* n_coarse_cells: 1 or 8 (local smoothing: 8 or 0) */
   const uint8_t  *weight_code; /* n_fine_slots*27: 0 -> weight 0, v -> 1/v */
   /* fine-side table indexed by fine_first (+child): single rank = the fine dofmap's own table; several ranks = the
    * children of the locally owned coarse cells in the numbering of the transfer's internal ghosted fine vector */
@@ -132,8 +137,33 @@ typedef struct
 } mgb_transfer_map_view;
 int  mgb_transfer_map_create(const mgb_mesh *mesh_fine, const mgb_dofmap *fine, const mgb_mesh *mesh_coarse, const mgb_dofmap *coarse,
                              mgb_transfer_map **out);
+/* MGTransferMatrixFree::build (multigrid_throughput.cc:1800-1802): the meshes are consecutive local-smoothing levels;
+ * a coarse cell has 8 children on the fine level or none (n_children 0) */
+int  mgb_transfer_map_create_ls(const mgb_mesh *level_fine, const mgb_dofmap *fine, const mgb_mesh *level_coarse,
+                                const mgb_dofmap *coarse, mgb_transfer_map **out);
 int  mgb_transfer_map_view_get(const mgb_transfer_map *t, mgb_transfer_map_view *view);
 void mgb_transfer_map_destroy(mgb_transfer_map *t);
+
+/* ---- stand-in setup: local smoothing (MGConstrainedDoFs, copy_indices) ------------------------------ */
+typedef struct
+{
+  uint32_t        n_edge_dofs, n_edge_cells;
+  int32_t         any_global;  /* include/operator.h:67-69 */
+  const uint32_t *edge_dofs;   /* owned local indices on the refinement edge of the level (include/operator.h:49-66) */
+  const uint32_t *edge_cells;  /* local cells touching an edge DoF (include/operator.h:71-99) */
+} mgb_level_edges_view;
+int  mgb_level_edges_create(const mgb_mesh *level_mesh, const mgb_dofmap *level_dofs, mgb_level_edges **out);
+int  mgb_level_edges_view_get(const mgb_level_edges *e, mgb_level_edges_view *view);
+void mgb_level_edges_destroy(mgb_level_edges *e);
+typedef struct
+{
+  uint32_t        n;
+  const uint32_t *active_idx, *level_idx; /* MGLevelGlobalTransfer::copy_indices[level] */
+} mgb_copy_indices_view;
+int  mgb_copy_indices_create(const mgb_dofmap *active_dofs, const mgb_mesh *level_mesh, const mgb_dofmap *level_dofs,
+                             mgb_copy_indices **out);
+int  mgb_copy_indices_view_get(const mgb_copy_indices *c, mgb_copy_indices_view *view);
+void mgb_copy_indices_destroy(mgb_copy_indices *c);
 
 /* ---- vectors ----------------------------------------------------------------------------------- */
 int  mgb_vector_create(uint32_t n_owned, uint32_t n_ghost, int number_type, mgb_vector **out);
@@ -181,6 +211,8 @@ typedef struct
 
 int  mgb_operator_create(const mgb_operator_desc *desc, mgb_operator **out);
 int  mgb_operator_create_from_dofmap(const mgb_dofmap *d, int number_type, mgb_operator **out);
+/* level operator of the local-smoothing hierarchy: Operator::reinit(..., mg_level) with its refinement-edge data */
+int  mgb_operator_create_level(const mgb_dofmap *level_dofs, const mgb_level_edges *edges, int number_type, mgb_operator **out);
 void mgb_operator_destroy(mgb_operator *op);
 int64_t mgb_operator_m(const mgb_operator *op);
 int  mgb_operator_initialize_dof_vector(const mgb_operator *op, mgb_vector **out);
@@ -228,6 +260,7 @@ const mgb_operator *mgb_problem_level_operator(const mgb_problem *p, int level);
 mgb_chebyshev      *mgb_problem_level_smoother(mgb_problem *p, int level);
 const mgb_transfer *mgb_problem_level_transfer(const mgb_problem *p, int level); /* between level-1 and level */
 const mgb_operator *mgb_problem_fine_operator(const mgb_problem *p);           /* outer FP64 operator        */
+const mgb_dofmap   *mgb_problem_fine_dofmap(const mgb_problem *p);             /* active-mesh DoFs of the outer operator */
 mgb_vector         *mgb_problem_rhs(mgb_problem *p);
 mgb_vector         *mgb_problem_solution(mgb_problem *p);
 /* PreconditionMG::vmult: one V-cycle, dst = M^-1 src (double vectors of the fine operator's layout) */

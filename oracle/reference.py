@@ -425,6 +425,8 @@ class MGTwoLevelTransfer:
         P1 = {8: fec.Ph, 1: (np.eye(nc) if pf == pc else p_embedding(pf, pc))}
         for c in range(coarse.n_cells):
             nch = int(n_children[c])
+            if nch == 0:
+                continue  # local smoothing: parent without children on the fine level
             P = P1[nch]
             P3 = np.einsum("Kk,Jj,Ii->KJIkji", P, P, P).reshape(P.shape[0] ** 3, nc ** 3)
             if coarse.mask[c] >> 3:
@@ -471,18 +473,30 @@ class Multigrid:
     """Multigrid<Vector>::cycle / level_v_step + PreconditionMG::vmult for a global-coarsening hierarchy
     (multigrid_throughput.cc:1091-1133)."""
 
-    def __init__(self, operators, smoothers, transfers, coarse, edge_in=False):
+    def __init__(self, operators, smoothers, transfers, coarse, edge_in=False, copy_indices=None):
+        """copy_indices: None (global coarsening: the top level IS the outer vector) or, for local smoothing, one
+        (active_idx, level_idx) pair of index arrays per level (MGLevelGlobalTransfer::copy_indices, SURVEY.md A.8)"""
         self.ops, self.smoothers, self.transfers, self.coarse, self.edge_in = operators, smoothers, transfers, coarse, edge_in
+        self.copy_indices = copy_indices
         self.max_level = len(operators) - 1
 
     def vmult(self, src):
-        """PreconditionMG::vmult with MGTransferGlobalCoarsening::copy_to_mg / copy_from_mg"""
+        """PreconditionMG::vmult: copy_to_mg, V-cycle, copy_from_mg"""
         self.defect = [np.zeros(op.m()) for op in self.ops]
-        self.defect[-1][:] = src
+        if self.copy_indices is None:
+            self.defect[-1][:] = src
+        else:
+            for l, (ai, li) in enumerate(self.copy_indices):
+                self.defect[l][li] = src[ai]
         self.solution = [np.zeros(op.m()) for op in self.ops]
         self.t = [np.zeros(op.m()) for op in self.ops]
         self.level_v_step(self.max_level)
-        return self.solution[-1].copy()
+        if self.copy_indices is None:
+            return self.solution[-1].copy()
+        dst = np.zeros_like(src)
+        for l, (ai, li) in enumerate(self.copy_indices):
+            dst[ai] = self.solution[l][li]
+        return dst
 
     def level_v_step(self, l):
         if l == 0:

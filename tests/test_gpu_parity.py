@@ -242,3 +242,111 @@ def test_cuda_graph_replay_matches_eager(gpu):
             mg.synchronize()
     finally:
         mg.set_stream(0)
+
+
+# ----------------------------------------------------------------------------------------------- local smoothing
+LS_OP_CASES = [("quadrant", 3, 2), ("quadrant", 4, 1), ("quadrant", 4, 4), ("annulus", 6, 2), ("circle", 4, 3)]
+
+
+@pytest.mark.parametrize("geometry,L,p", LS_OP_CASES)
+def test_level_operator_edge_handling(gpu, geometry, L, p):
+    """level operators of the LS hierarchy: vmult with refinement-edge DoFs as Dirichlet, vmult_interface_down/up,
+    inverse diagonal zeroed at the edge (include/operator.h:152-242)"""
+    mg = gpu
+    mesh = mg.Mesh(geometry, L)
+    seen_edges = False
+    for l in range(1, mesh.n_global_levels):
+        lm = mesh.level_mesh(l)
+        d = mg.DoFMap(lm, p)
+        e = mg.LevelEdges(lm, d)
+        maps = ref.LevelMaps.from_dofmap(d)
+        oracle = ref.Operator(maps, e.edge_dofs, e.edge_cells, e.any_global)
+        op = mg.Operator(d, edges=e)
+        seen_edges |= e.any_global
+        x = seeded(maps.n_dofs, 7 + l)
+        src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+        src.from_numpy(x)
+        dst.from_numpy(seeded(maps.n_dofs, 1))
+        op.vmult(dst, src)
+        y = dst.to_numpy()
+        assert rel_l2(y, oracle.vmult(x)) < PARITY_RTOL
+        np.testing.assert_array_equal(y[e.edge_dofs], x[e.edge_dofs])               # dst_edge = src_edge exactly
+        np.testing.assert_array_equal(src.to_numpy(), x)                             # src restored
+        op.vmult_interface_down(dst, src)
+        assert rel_l2(dst.to_numpy(), oracle.vmult_interface_down(x)) < PARITY_RTOL
+        op.vmult_interface_up(dst, src)
+        up = oracle.vmult_interface_up(x)
+        if e.any_global:
+            assert rel_l2(dst.to_numpy(), up) < PARITY_RTOL
+        else:
+            assert np.all(dst.to_numpy() == 0.0)
+        diag = op.initialize_dof_vector()
+        op.compute_inverse_diagonal(diag)
+        dd = diag.to_numpy()
+        assert rel_l2(dd, oracle.compute_inverse_diagonal()) < PARITY_RTOL
+        assert np.all(dd[e.edge_dofs] == 1.0)
+    assert seen_edges
+
+
+@pytest.mark.parametrize("geometry,L,p", [("quadrant", 3, 2), ("quadrant", 4, 4), ("annulus", 6, 1), ("circle", 4, 3), ("hypercube", 2, 2)])
+def test_local_smoothing_transfer(gpu, geometry, L, p):
+    """MGTransferMatrixFree::prolongate_and_add / restrict_and_add between consecutive LS levels (refined parents only)"""
+    mg = gpu
+    mesh = mg.Mesh(geometry, L)
+    for l in range(1, mesh.n_global_levels):
+        mf, mc = mesh.level_mesh(l), mesh.level_mesh(l - 1)
+        df, dc = mg.DoFMap(mf, p), mg.DoFMap(mc, p)
+        tm = mg.TransferMap(mf, df, mc, dc, local_smoothing=True)
+        assert set(tm.n_children().tolist()) <= {0, 8}
+        fine, coarse = ref.LevelMaps.from_dofmap(df), ref.LevelMaps.from_dofmap(dc)
+        oracle = ref.MGTwoLevelTransfer(fine, coarse, tm.fine_first(), tm.n_children())
+        opf, opc = mg.Operator(df), mg.Operator(dc)
+        T = mg.MGTwoLevelTransfer(df, dc, tm, opf, opc)
+        uc, uf = seeded(coarse.n_dofs, 1), seeded(fine.n_dofs, 2)
+        vc, vf = opc.initialize_dof_vector(), opf.initialize_dof_vector()
+        vc.from_numpy(uc)
+        vf.from_numpy(uf)
+        T.prolongate_and_add(vf, vc)
+        expect = uf.copy()
+        oracle.prolongate_and_add(expect, uc)
+        assert rel_l2(vf.to_numpy(), expect) < PARITY_RTOL
+        vc.from_numpy(uc)
+        vf.from_numpy(uf)
+        T.restrict_and_add(vc, vf)
+        expect = uc.copy()
+        oracle.restrict_and_add(expect, uf)
+        assert rel_l2(vc.to_numpy(), expect) < PARITY_RTOL
+
+
+LS_SOLVE_CASES = [("quadrant", 3, 2, "HMG-local", "cg"), ("quadrant", 4, 1, "HMG-local", "cg"), ("quadrant", 3, 4, "HMG-local", "cg_with_chebyshev"),
+                  ("hypercube", 3, 2, "HMG-local", "cg"), ("annulus", 6, 2, "HMG-local", "cg"), ("quadrant", 3, 4, "HPMG-local", "cg"),
+                  ("circle", 4, 2, "HPMG-local", "cg")]
+
+
+@pytest.mark.parametrize("geometry,L,p,mg_type,coarse", LS_SOLVE_CASES)
+def test_local_smoothing_vcycle_and_cg(gpu, geometry, L, p, mg_type, coarse):
+    """solve_with_local_smoothing (multigrid_throughput.cc:1673-1873): one V-cycle with copy_to_mg / copy_from_mg and the
+    edge_in matrix, then the full CG solve with identical iteration counts"""
+    from util import OracleHierarchyLS
+    mg = gpu
+    prob = mg.Problem(params(geometry, L, p, mg_type, coarse))
+    H = OracleHierarchyLS(geometry, L, p, mg_type, 3, coarse)
+    assert prob.n_levels == len(H.maps)
+    for l in range(prob.n_levels):
+        assert prob.level_n_dofs(l) == H.maps[l].n_dofs
+    n = H.fine_maps.n_dofs
+    assert prob.fine_dofmap().n_dofs_global == n
+    r = seeded(n)
+    r[H.fine_maps.constrained] = 0.0
+    src, dst = mg.Vector(n), mg.Vector(n)
+    src.from_numpy(r)
+    prob.vcycle(dst, src)
+    assert rel_l2(dst.to_numpy(), H.mg.vmult(r)) < 1e-11
+    b = prob.rhs().to_numpy()
+    x_ref, its_ref, ctl = H.solve(b.copy())
+    res = prob.solve_once()
+    assert res["n_iterations"] == its_ref
+    assert rel_l2(prob.solution().to_numpy(), x_ref) < 1e-9
+    assert res["n_dofs"] == n
+    res = prob.solve_once(True)                                                  # with stage timers (edge_pro column)
+    assert res["n_iterations"] == its_ref

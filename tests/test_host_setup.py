@@ -257,3 +257,98 @@ def test_partitioned_transfer_maps_are_consistent(geometry, L, p, kind, n_ranks)
         # every ghost group has a sender
         for j, o in enumerate(pa["ghost_ranks"]):
             assert df.rank in list(tms[o][0].partitioner()["import_ranks"])
+
+
+# ----------------------------------------------------------------------------------------------- local smoothing
+LS_SETUP_CASES = [("quadrant", 3, 2), ("quadrant", 4, 1), ("quadrant", 4, 3), ("annulus", 6, 2), ("circle", 4, 2), ("hypercube", 2, 3)]
+
+
+def _covered(points, cell_set, level):
+    """is each point strictly inside a cell of the level-`level` cell set?"""
+    h = 2.0 / 2 ** level
+    ijk = np.floor((points + 1.0) / h).astype(np.int64)
+    return np.array([tuple(c) in cell_set for c in ijk])
+
+
+@pytest.mark.parametrize("geometry,L,p", LS_SETUP_CASES)
+def test_level_meshes_and_refinement_edges(geometry, L, p):
+    """level l of the LS hierarchy = all ancestors at level l; edge DoFs = level DoFs on a face between a level cell and
+    the part of the domain not covered by level cells (MGTools::extract_inner_interface_dofs), checked geometrically
+    with probe points around every DoF; edge cells = cells touching such a DoF (include/operator.h:71-99)"""
+    mesh = mg.Mesh(geometry, L)
+    cells = mesh.cells().astype(np.int64)
+    for l in range(mesh.n_global_levels):
+        lm = mesh.level_mesh(l)
+        lc = lm.cells().astype(np.int64)
+        fine = cells[cells[:, 0] >= l]
+        anc = {tuple(int(v) >> int(c[0] - l) for v in c[1:]) for c in fine}
+        assert {tuple(c[1:]) for c in lc} == anc and np.all(lc[:, 0] == l) and len(lc) == len(anc)
+        d = mg.DoFMap(lm, p)
+        e = mg.LevelEdges(lm, d)
+        maps = ref.LevelMaps.from_dofmap(d)
+        xyz = maps.dof_coordinates()
+        assert not np.isnan(xyz).any()
+        eps = 1e-3 * 2.0 / 2 ** l
+        signs = np.array([[sx, sy, sz] for sz in (-1, 1) for sy in (-1, 1) for sx in (-1, 1)])
+        cov = np.stack([_covered(xyz + eps * s, anc, l) for s in signs], axis=1)               # (n_dofs, 8)
+        inside = np.stack([np.all(np.abs(xyz + eps * s) < 1.0, axis=1) for s in signs], axis=1)
+        on_edge = np.zeros(len(xyz), dtype=bool)
+        for a in range(8):
+            for dd in range(3):
+                b = a ^ (1 << dd)
+                on_edge |= inside[:, a] & inside[:, b] & (cov[:, a] != cov[:, b])
+        np.testing.assert_array_equal(np.nonzero(on_edge)[0], e.edge_dofs)
+        assert e.any_global == bool(on_edge.any())
+        touching = np.nonzero(on_edge[maps.own_idx].any(axis=1))[0]
+        np.testing.assert_array_equal(touching, e.edge_cells)
+        assert len(maps.constrained) == np.count_nonzero(np.any(np.abs(np.abs(xyz) - 1.0) < 1e-12, axis=1))  # Dirichlet only
+
+
+@pytest.mark.parametrize("geometry,L,p", LS_SETUP_CASES)
+def test_copy_indices_cover_the_active_dofs_once(geometry, L, p):
+    """copy_indices: pairs connect DoFs at the same point; every active DoF that is not a hanging node is in
+    exactly one level's list, hanging nodes in none; level DoFs on the refinement edge are never copied"""
+    mesh = mg.Mesh(geometry, L)
+    act = mg.DoFMap(mesh, p)
+    amaps = ref.LevelMaps.from_dofmap(act)
+    axyz = amaps.dof_coordinates()
+    count = np.zeros(amaps.n_dofs, dtype=int)
+    for l in range(mesh.n_global_levels):
+        lm = mesh.level_mesh(l)
+        d = mg.DoFMap(lm, p)
+        ci = mg.CopyIndices(act, lm, d)
+        lxyz = ref.LevelMaps.from_dofmap(d).dof_coordinates()
+        np.testing.assert_allclose(axyz[ci.active_idx], lxyz[ci.level_idx], rtol=0, atol=1e-13)
+        assert len(np.unique(ci.level_idx)) == len(ci.level_idx)
+        assert not np.intersect1d(ci.level_idx, mg.LevelEdges(lm, d).edge_dofs).size
+        count[ci.active_idx] += 1
+    dirichlet = np.any(np.abs(np.abs(axyz) - 1.0) < 1e-12, axis=1)
+    hanging = np.zeros(amaps.n_dofs, dtype=bool)
+    hanging[amaps.constrained] = True
+    hanging &= ~dirichlet
+    np.testing.assert_array_equal(count[~dirichlet], np.where(hanging, 0, 1)[~dirichlet])
+    assert count[dirichlet].max() <= 1  # boundary DoFs that are hanging nodes as well are in no list (their value is 0)
+
+
+@pytest.mark.parametrize("geometry,L,p", [("quadrant", 3, 2), ("quadrant", 4, 1), ("annulus", 6, 1), ("hypercube", 2, 2)])
+def test_ls_transfer_map(geometry, L, p):
+    mesh = mg.Mesh(geometry, L)
+    for l in range(1, mesh.n_global_levels):
+        mf, mc = mesh.level_mesh(l), mesh.level_mesh(l - 1)
+        df, dc = mg.DoFMap(mf, p), mg.DoFMap(mc, p)
+        tm = mg.TransferMap(mf, df, mc, dc, local_smoothing=True)
+        nch = tm.n_children().astype(int)
+        assert set(nch.tolist()) <= {0, 8} and nch.sum() == mf.n_cells
+        cc, fc, first = mc.cells().astype(np.int64), mf.cells().astype(np.int64), tm.fine_first()
+        for c in np.nonzero(nch == 8)[0]:
+            np.testing.assert_array_equal(fc[first[c]][1:] >> 1, cc[c][1:])
+        fine, coarse = ref.LevelMaps.from_dofmap(df), ref.LevelMaps.from_dofmap(dc)
+        # prolongation reproduces a coarse FE function that vanishes on the boundary on the refined part of the level
+        P = ref.MGTwoLevelTransfer(fine, coarse, first, nch)
+        f = lambda x: np.prod(1.0 - x ** 2, axis=1) * (1.0 + 0.3 * x[:, 0] - 0.2 * x[:, 1] * x[:, 2]) if p >= 2 else np.prod(1.0 - np.abs(x), axis=1)
+        if p >= 4 or p == 1:
+            uc = f(coarse.dof_coordinates())
+            uf = np.zeros(fine.n_dofs)
+            P.prolongate_and_add(uf, uc)
+            if p >= 4:
+                np.testing.assert_allclose(uf, f(fine.dof_coordinates()), atol=1e-12)

@@ -133,3 +133,25 @@ def test_vcycle_pcg_converges_mesh_independently(geometry, L, p, mg_type, max_it
     assert 1 <= its <= max_its, its
     A = ref.assemble_matrix(maps)
     assert np.linalg.norm(A @ x - rhs) <= 1.0001e-4 * np.linalg.norm(rhs)
+
+
+@pytest.mark.parametrize("geometry,L,p,mg_type", [("quadrant", 3, 2, "HMG-local"), ("quadrant", 4, 1, "HMG-local"), ("circle", 4, 2, "HMG-local"),
+                                                   ("quadrant", 3, 4, "HPMG-local")])
+def test_local_smoothing_oracle_pins(geometry, L, p, mg_type):
+    """substitute pins of the local-smoothing restatement (no deal.II golden vectors exist): the LS V-cycle
+    with edge_in is a SYMMETRIC preconditioner, CG with it converges to the same solution as with global coarsening, in a
+    comparable number of iterations"""
+    from util import OracleHierarchy, OracleHierarchyLS, seeded
+    H = OracleHierarchyLS(geometry, L, p, mg_type)
+    G = OracleHierarchy(geometry, L, p, "HMG-global")
+    b = ref.assemble_rhs_constant(H.fine_maps)
+    x, its, _ = H.solve(b, 1e-10)
+    xg, itg, _ = G.solve(b, 1e-10)
+    assert np.linalg.norm(x - xg) < 1e-9 * np.linalg.norm(xg)
+    assert abs(its - itg) <= 2
+    n = len(b)
+    u, v = seeded(n, 1), seeded(n, 2)
+    u[H.fine_maps.constrained] = 0.0
+    v[H.fine_maps.constrained] = 0.0
+    a, c = u @ H.mg.vmult(v), v @ H.mg.vmult(u)
+    assert abs(a - c) < 1e-10 * abs(a)

@@ -61,6 +61,55 @@ class OracleHierarchy:
         return x, its, ctl
 
 
+class OracleHierarchyLS:
+    """oracle multigrid for solve_with_local_smoothing (multigrid_throughput.cc:1673-1873): HMG-local, or HPMG-local with
+    the LS V-cycle nested as the coarse solver of the p-multigrid on the active mesh"""
+
+    def __init__(self, geometry, n_ref_global, degree, mg_type="HMG-local", smoother_degree=3, coarse="cg"):
+        self.mesh = mg.Mesh(geometry, n_ref_global)
+        nl = self.mesh.n_global_levels
+        degrees = ref.polynomial_coarsening_sequence_bisect(degree) if mg_type == "HPMG-local" else [degree]
+        has_hanging = len(set(self.mesh.cells()[:, 0].tolist())) > 1
+        self.level_meshes = [self.mesh.level_mesh(l) for l in range(nl)]
+        self.level_dofmaps = [mg.DoFMap(m, degrees[0]) for m in self.level_meshes]
+        self.level_edges = [mg.LevelEdges(m, d) for m, d in zip(self.level_meshes, self.level_dofmaps)]
+        self.level_maps = [ref.LevelMaps.from_dofmap(d) for d in self.level_dofmaps]
+        self.level_ops = [ref.Operator(m, e.edge_dofs, e.edge_cells, e.any_global) for m, e in zip(self.level_maps, self.level_edges)]
+        self.active_dofmaps = [mg.DoFMap(self.mesh, d) for d in degrees]
+        self.active_maps = [ref.LevelMaps.from_dofmap(d) for d in self.active_dofmaps]
+        self.copy = [mg.CopyIndices(self.active_dofmaps[0], m, d) for m, d in zip(self.level_meshes, self.level_dofmaps)]
+        self.ls_tmaps = [None] + [mg.TransferMap(self.level_meshes[l], self.level_dofmaps[l], self.level_meshes[l - 1],
+                                                 self.level_dofmaps[l - 1], local_smoothing=True) for l in range(1, nl)]
+        self.ls_transfers = [None] + [ref.MGTwoLevelTransfer(self.level_maps[l], self.level_maps[l - 1], self.ls_tmaps[l].fine_first(),
+                                                             self.ls_tmaps[l].n_children()) for l in range(1, nl)]
+        cheb = lambda op: ref.PreconditionChebyshev(op, smoother_degree, 20.0, 20)
+        self.level_smoothers = [cheb(op) for op in self.level_ops]
+        self.coarse = ref.CoarseGridCG(self.level_ops[0], cheb(self.level_ops[0]) if coarse == "cg_with_chebyshev" else None)
+        self.mg_ls = ref.Multigrid(self.level_ops, self.level_smoothers, self.ls_transfers, self.coarse, edge_in=has_hanging,
+                                   copy_indices=[(c.active_idx.astype(np.int64), c.level_idx.astype(np.int64)) for c in self.copy])
+        if mg_type == "HPMG-local":
+            self.active_ops = [ref.Operator(m) for m in self.active_maps]
+            self.p_tmaps = [None] + [mg.TransferMap(self.mesh, self.active_dofmaps[i], self.mesh, self.active_dofmaps[i - 1])
+                                     for i in range(1, len(degrees))]
+            self.p_transfers = [None] + [ref.MGTwoLevelTransfer(self.active_maps[i], self.active_maps[i - 1], self.p_tmaps[i].fine_first(),
+                                                                self.p_tmaps[i].n_children()) for i in range(1, len(degrees))]
+            self.active_smoothers = [cheb(op) for op in self.active_ops]
+            self.mg = ref.Multigrid(self.active_ops, self.active_smoothers, self.p_transfers, self.mg_ls.vmult)
+            self.fine_op = self.active_ops[-1]
+        else:
+            self.mg = self.mg_ls
+            self.fine_op = ref.Operator(self.active_maps[-1])
+        self.maps = self.level_maps + (self.active_maps if mg_type == "HPMG-local" else [])
+        self.ops = self.level_ops + (self.active_ops if mg_type == "HPMG-local" else [])
+        self.fine_maps = self.active_maps[-1]
+
+    def solve(self, rhs, reltol=1e-4):
+        x = np.zeros_like(rhs)
+        ctl = ref.ReductionControl(10000, 1e-20, reltol)
+        its = ref.solver_cg(self.fine_op.vmult, x, rhs, self.mg.vmult, ctl)
+        return x, its, ctl
+
+
 def params(geometry="hypercube", n_ref=3, degree=2, mg_type="HMG-global", coarse="cg", number="double", smoother_degree=3,
            simulation="Constant", reltol=1e-4):
     return {"Type": mg_type, "GeometryType": geometry, "NRefGlobal": str(n_ref), "NRefLocal": "0", "Degree": str(degree),
