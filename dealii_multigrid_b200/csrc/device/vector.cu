@@ -19,7 +19,14 @@ namespace mgb
   namespace
   {
     constexpr int BLOCK      = 256;
-    constexpr int RED_BLOCKS = 148 * 4; // reduction grid: 4 CTAs per SM
+    constexpr int RED_BLOCKS = 148 * 8; // reduction grid: 8 CTAs per SM (full occupancy at 256 threads)
+
+    // reduction grid: a function of n only (fixed summation order for a fixed vector length)
+    inline int red_grid(size_t n)
+    {
+      const size_t b = (n + 2 * BLOCK - 1) / (2 * BLOCK);
+      return int(b < 1 ? 1 : (b > size_t(RED_BLOCKS) ? size_t(RED_BLOCKS) : b));
+    }
 
     inline int stream_grid(size_t n)
     {
@@ -120,14 +127,27 @@ namespace mgb
         }
     }
 
+    // The reduction loops are unrolled four times with independent accumulators (memory-level parallelism); the
+    // summation order is a function of the launch configuration only, so results are reproducible run to run.
     template <typename T>
     __global__ void __launch_bounds__(BLOCK)
       k_dot(const T *__restrict__ x, const T *__restrict__ y, size_t n, double *result, double *scratch, unsigned *ticket)
     {
-      double v = 0;
-      for (size_t i = blockIdx.x * size_t(BLOCK) + threadIdx.x; i < n; i += size_t(gridDim.x) * BLOCK)
-        v += double(x[i]) * double(y[i]);
-      block_reduce_and_finish(v, result, scratch, ticket);
+      const size_t stride = size_t(gridDim.x) * BLOCK;
+      size_t       i      = blockIdx.x * size_t(BLOCK) + threadIdx.x;
+      double       v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+      for (; i + 3 * stride < n; i += 4 * stride)
+        {
+          const T x0 = x[i], x1 = x[i + stride], x2 = x[i + 2 * stride], x3 = x[i + 3 * stride];
+          const T y0 = y[i], y1 = y[i + stride], y2 = y[i + 2 * stride], y3 = y[i + 3 * stride];
+          v0 += double(x0) * double(y0);
+          v1 += double(x1) * double(y1);
+          v2 += double(x2) * double(y2);
+          v3 += double(x3) * double(y3);
+        }
+      for (; i < n; i += stride)
+        v0 += double(x[i]) * double(y[i]);
+      block_reduce_and_finish((v0 + v1) + (v2 + v3), result, scratch, ticket);
     }
     template <typename T>
     __global__ void __launch_bounds__(BLOCK) k_sum(const T *__restrict__ x, size_t n, double *result, double *scratch, unsigned *ticket)
@@ -141,14 +161,24 @@ namespace mgb
     __global__ void __launch_bounds__(BLOCK)
       k_add_and_dot(T *__restrict__ g, T a, const T *__restrict__ h, size_t n, double *result, double *scratch, unsigned *ticket)
     {
-      double v = 0;
-      for (size_t i = blockIdx.x * size_t(BLOCK) + threadIdx.x; i < n; i += size_t(gridDim.x) * BLOCK)
+      const size_t stride = size_t(gridDim.x) * BLOCK;
+      size_t       i      = blockIdx.x * size_t(BLOCK) + threadIdx.x;
+      double       v0 = 0, v1 = 0;
+      for (; i + stride < n; i += 2 * stride)
+        {
+          const T g0 = g[i] + a * h[i], g1 = g[i + stride] + a * h[i + stride];
+          g[i]          = g0;
+          g[i + stride] = g1;
+          v0 += double(g0) * double(g0);
+          v1 += double(g1) * double(g1);
+        }
+      for (; i < n; i += stride)
         {
           const T gi = g[i] + a * h[i];
           g[i]       = gi;
-          v += double(gi) * double(gi);
+          v0 += double(gi) * double(gi);
         }
-      block_reduce_and_finish(v, result, scratch, ticket);
+      block_reduce_and_finish(v0 + v1, result, scratch, ticket);
     }
 
     // SolverCG's two vector updates of one iteration in one pass: x += a d;  g += a h;  result = g.g
@@ -156,15 +186,28 @@ namespace mgb
     __global__ void __launch_bounds__(BLOCK) k_cg_update(T *__restrict__ x, T *__restrict__ g, T a, const T *__restrict__ d,
                                                          const T *__restrict__ h, size_t n, double *result, double *scratch, unsigned *ticket)
     {
-      double v = 0;
-      for (size_t i = blockIdx.x * size_t(BLOCK) + threadIdx.x; i < n; i += size_t(gridDim.x) * BLOCK)
+      const size_t stride = size_t(gridDim.x) * BLOCK;
+      size_t       i      = blockIdx.x * size_t(BLOCK) + threadIdx.x;
+      double       v0 = 0, v1 = 0;
+      for (; i + stride < n; i += 2 * stride)
+        {
+          const T d0 = d[i], d1 = d[i + stride], h0 = h[i], h1 = h[i + stride];
+          const T x0 = x[i], x1 = x[i + stride], g0 = g[i] + a * h0, g1 = g[i + stride] + a * h1;
+          x[i]          = x0 + a * d0;
+          x[i + stride] = x1 + a * d1;
+          g[i]          = g0;
+          g[i + stride] = g1;
+          v0 += double(g0) * double(g0);
+          v1 += double(g1) * double(g1);
+        }
+      for (; i < n; i += stride)
         {
           x[i] += a * d[i];
           const T gi = g[i] + a * h[i];
           g[i]       = gi;
-          v += double(gi) * double(gi);
+          v0 += double(gi) * double(gi);
         }
-      block_reduce_and_finish(v, result, scratch, ticket);
+      block_reduce_and_finish(v0 + v1, result, scratch, ticket);
     }
     template <typename T>
     __global__ void k_idx_residual(T *__restrict__ dst, const T *__restrict__ a, const T *__restrict__ b, const uint32_t *__restrict__ idx, uint32_t n)
@@ -273,25 +316,25 @@ namespace mgb
   template <typename T>
   void vec_dot(const T *x, const T *y, size_t n, double *result_dev, double *scratch, unsigned *ticket, cudaStream_t s)
   {
-    k_dot<T><<<RED_BLOCKS, BLOCK, 0, s>>>(x, y, n, result_dev, scratch, ticket);
+    k_dot<T><<<red_grid(n), BLOCK, 0, s>>>(x, y, n, result_dev, scratch, ticket);
     MGB_CUDA(cudaGetLastError());
   }
   template <typename T> void vec_sum(const T *x, size_t n, double *result_dev, double *scratch, unsigned *ticket, cudaStream_t s)
   {
-    k_sum<T><<<RED_BLOCKS, BLOCK, 0, s>>>(x, n, result_dev, scratch, ticket);
+    k_sum<T><<<red_grid(n), BLOCK, 0, s>>>(x, n, result_dev, scratch, ticket);
     MGB_CUDA(cudaGetLastError());
   }
   template <typename T>
   void vec_add_and_dot(T *g, T a, const T *h, size_t n, double *result_dev, double *scratch, unsigned *ticket, cudaStream_t s)
   {
-    k_add_and_dot<T><<<RED_BLOCKS, BLOCK, 0, s>>>(g, a, h, n, result_dev, scratch, ticket);
+    k_add_and_dot<T><<<red_grid(n), BLOCK, 0, s>>>(g, a, h, n, result_dev, scratch, ticket);
     MGB_CUDA(cudaGetLastError());
   }
 
   template <typename T>
   void vec_cg_update(T *x, T *g, T a, const T *d, const T *h, size_t n, double *result_dev, double *scratch, unsigned *ticket, cudaStream_t s)
   {
-    k_cg_update<T><<<RED_BLOCKS, BLOCK, 0, s>>>(x, g, a, d, h, n, result_dev, scratch, ticket);
+    k_cg_update<T><<<red_grid(n), BLOCK, 0, s>>>(x, g, a, d, h, n, result_dev, scratch, ticket);
     MGB_CUDA(cudaGetLastError());
   }
 

@@ -339,6 +339,17 @@ namespace mgb
       return d;
     }
 
+    // Levels with fewer cells per rank than this live on the first ranks only (DoFMap::build): a level of ~30k cells costs
+    // less on one B200 than the 16 halo exchanges per V-cycle that partitioning it over 8 GPUs adds (each ~25 us).
+    int64_t min_cells_per_rank()
+    {
+      static const int64_t v = [] {
+        const char *e = std::getenv("MGB_MIN_CELLS_PER_RANK");
+        return e ? std::max<int64_t>(1, std::atoll(e)) : int64_t(32768);
+      }();
+      return v;
+    }
+
     OperatorSetup setup_from_dofmap(const DoFMap &dm)
     {
       OperatorSetup s;
@@ -474,7 +485,7 @@ namespace mgb
                 L.degree     = level_degrees[std::max<int>(0, int(l) - int(n_trias) + 1)];
                 L.mesh_index = std::min(l, n_trias - 1);
               }
-            L.dofs = std::make_unique<DoFMap>(DoFMap::build(meshes[L.mesh_index], L.degree, n_ranks, rank, /*min_cells_per_rank=*/512));
+            L.dofs = std::make_unique<DoFMap>(DoFMap::build(meshes[L.mesh_index], L.degree, n_ranks, rank, min_cells_per_rank()));
             L.op   = std::make_unique<OperatorT<LT>>(setup_from_dofmap(*L.dofs));
           }
         // two-level transfers (ref :1600-1604)
@@ -545,7 +556,7 @@ namespace mgb
             Level &L     = levels[l];
             L.degree     = (int)level_degrees.front();
             L.mesh_index = (int)l;
-            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[l], L.degree, n_ranks, rank, /*min_cells_per_rank=*/512));
+            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[l], L.degree, n_ranks, rank, min_cells_per_rank()));
             level_edges[l]   = LevelEdges::build(meshes[l], *L.dofs);
             OperatorSetup st = setup_from_dofmap(*L.dofs);
             st.edge_constrained            = level_edges[l].edge_dofs.data();
@@ -561,7 +572,7 @@ namespace mgb
             Level &L     = levels[l];
             L.degree     = (int)level_degrees[l - nl];
             L.mesh_index = (int)nl;
-            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], L.degree, n_ranks, rank, 512));
+            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], L.degree, n_ranks, rank, min_cells_per_rank()));
             L.op         = std::make_unique<OperatorT<LT>>(setup_from_dofmap(*L.dofs));
           }
         // the active-mesh DoFs the LS transfer copies from / to (dof_handlers.front())
@@ -570,7 +581,7 @@ namespace mgb
           active_low = levels[nl].dofs.get();
         else
           {
-            fine_dofs_own = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], (int)prm.fe_degree_fine, n_ranks, rank, 512));
+            fine_dofs_own = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], (int)prm.fe_degree_fine, n_ranks, rank, min_cells_per_rank()));
             active_low    = fine_dofs_own.get();
           }
         // MGTransferMatrixFree::build (ref :1800-1802)
@@ -667,7 +678,9 @@ namespace mgb
         {
           std::vector<double> b;
           assemble_rhs(meshes.back(), fd, prm.simulation_type, b);
-          MGB_CUDA(cudaMemcpy(rhs_.data, b.data(), b.size() * sizeof(double), cudaMemcpyHostToDevice));
+          // on the library's stream (a blocking copy on the legacy stream could overtake the zero-fill of rhs_ above)
+          MGB_CUDA(cudaMemcpyAsync(rhs_.data, b.data(), b.size() * sizeof(double), cudaMemcpyHostToDevice, ctx().stream));
+          MGB_CUDA(cudaStreamSynchronize(ctx().stream));
           rhs_.compress_add();
         }
         n_cells_hn = fd.n_cells_hanging;

@@ -1,5 +1,7 @@
 #include "solver.h"
 
+#include <cstdlib>
+
 #include "comm.h"
 
 #include <algorithm>
@@ -603,7 +605,7 @@ namespace mgb
       return;
     dense_ = true;
     dense_its_.alloc(1);
-    MGB_CUDA(cudaMemset(dense_its_.ptr, 0, sizeof(int)));
+    MGB_CUDA(cudaMemsetAsync(dense_its_.ptr, 0, sizeof(int), c.stream));
     const int n = (int)p.n_owned;
     if (n == 0)
       return;
@@ -652,8 +654,9 @@ namespace mgb
     if (dense_ && dense_its_.n)
       {
         int its = 0;
-        MGB_CUDA(cudaMemcpy(&its, dense_its_.ptr, sizeof(int), cudaMemcpyDeviceToHost));
-        MGB_CUDA(cudaMemset(dense_its_.ptr, 0, sizeof(int)));
+        MGB_CUDA(cudaMemcpyAsync(&its, dense_its_.ptr, sizeof(int), cudaMemcpyDeviceToHost, ctx().stream));
+        MGB_CUDA(cudaMemsetAsync(dense_its_.ptr, 0, sizeof(int), ctx().stream));
+        MGB_CUDA(cudaStreamSynchronize(ctx().stream));
         total_iterations += its;
       }
     return total_iterations;
@@ -771,11 +774,23 @@ namespace mgb
       cudaGraphExecDestroy(g.exec);
   }
 
+  // NCCL point-to-point calls can be stream-captured (every rank captures and replays the same sequence); the
+  // environment variable MGB_GRAPH_MULTIRANK=0 falls back to eager launches on several ranks
+  static bool graph_multirank()
+  {
+    static const bool on = [] {
+      const char *e = std::getenv("MGB_GRAPH_MULTIRANK");
+      return !(e && e[0] == '0');
+    }();
+    return on;
+  }
+
   template <typename T> void PreconditionMGT<T>::vmult(DVec<double> &dst, const DVec<double> &src)
   {
     Context   &c = ctx();
     bool graph_ok = allow_graph && c.stream != nullptr && !(timers && timers->enabled) && !c.prof_enabled &&
-                    !(c.comm && c.comm->size() > 1) && std::is_same<T, double>::value && !mg->edge_in && src.data != dst.data &&
+                    !(c.comm && c.comm->size() > 1 && !graph_multirank()) && std::is_same<T, double>::value && !mg->edge_in &&
+                    src.data != dst.data &&
                     transfer->top_level_is_plain_copy();
     if (graph_ok)
       {

@@ -16,6 +16,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
 def main():
+    os.environ.setdefault("MGB_MIN_CELLS_PER_RANK", "64")  # partition the small parity meshes too
     import torch
     import torch.distributed as dist
     import dealii_multigrid_b200 as mg
@@ -24,6 +25,9 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     mg.init(local)
+    stream = torch.cuda.Stream()  # non-default stream: after the first solve the V-cycle is replayed from a CUDA graph
+    torch.cuda.set_stream(stream)
+    mg.set_stream(stream.cuda_stream)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     uid = [mg.comm_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
@@ -53,7 +57,16 @@ def main():
         e_rhs = rel_l2(prob.rhs().to_numpy(d.n_owned), b[lo:hi])
         _, its, _ = H.solve(b.copy())
         res = prob.solve_once()
-        good = e_vmult < 1e-12 and e_vc < 1e-11 and e_rhs < 1e-13 and res["n_iterations"] == its
+        x1 = prob.solution().to_numpy(d.n_owned)
+        res2 = prob.solve_once()          # V-cycle captured (NCCL ghost exchange included) and replayed
+        res3 = prob.solve_once()
+        e_graph = rel_l2(prob.solution().to_numpy(d.n_owned), x1) if d.n_owned else 0.0
+        src.from_numpy(r[lo:hi])
+        prob.vcycle(dst, src)
+        prob.vcycle(dst, src)
+        e_vc = max(e_vc, rel_l2(dst.to_numpy(d.n_owned), H.mg.vmult(r)[lo:hi]))
+        good = (e_vmult < 1e-12 and e_vc < 1e-11 and e_rhs < 1e-13 and res["n_iterations"] == its == res2["n_iterations"] == res3["n_iterations"]
+                and e_graph < 1e-12)
         ok &= good
         print(f"[rank {rank}/{world}] {geometry} L={L} p={p} {mg_type}: owned={d.n_owned} ghost={d.n_ghost} vmult={e_vmult:.1e} "
               f"vcycle={e_vc:.1e} rhs={e_rhs:.1e} its={res['n_iterations']} (oracle {its}) {'OK' if good else 'FAIL'}", flush=True)
