@@ -101,6 +101,7 @@ SIGNATURES = {
     "mgb_profile_stop": (C.c_int, [c_f64p, c_i64p]),
     "mgb_comm_unique_id": (C.c_int, [P, C.c_char_p]),
     "mgb_comm_init": (C.c_int, [P, C.c_int, C.c_int, C.c_char_p]),
+    "mgb_comm_enable_peer_exchange": (C.c_int, [C.POINTER(C.c_int)]),
     "mgb_comm_finalize": (C.c_int, []),
     "mgb_fe_1d": (C.c_int, [C.c_int, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p]),
     "mgb_fe_1d_fdm": (C.c_int, [C.c_int, c_f64p, c_f64p]),

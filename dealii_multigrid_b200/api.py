@@ -76,6 +76,13 @@ def comm_init(unique_id, rank, size, libnccl_path=None):
     _check(_lib.load().mgb_comm_init(buf, rank, size, libnccl_path.encode() if libnccl_path else None))
 
 
+def comm_enable_peer_exchange():
+    """collective: back the partitioners created so far with peer-mapped staging memory (NVLink ghost exchange)"""
+    on = C.c_int(0)
+    _check(_lib.load().mgb_comm_enable_peer_exchange(C.byref(on)))
+    return bool(on.value)
+
+
 def comm_finalize():
     _check(_lib.load().mgb_comm_finalize())
 

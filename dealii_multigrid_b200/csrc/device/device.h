@@ -57,6 +57,28 @@ namespace mgb
   // d = (|d| > 1e-10) ? 1/d : 1   (include/operator.h:240-241)
   template <typename T> void invert_diagonal(T *d, size_t n, cudaStream_t s);
 
+  // ---------------------------------------------------------------- ghost exchange over NVLink peer memory (halo.cu)
+  constexpr int HALO_MAX_PEERS = 16;
+  struct HaloSide // the peers this rank sends to (or receives from) in one direction of the exchange
+  {
+    int                 n = 0;
+    uint32_t            off[HALO_MAX_PEERS + 1] = {}; // element ranges of the peers in the pack list / ghost tail / staging slot
+    char               *remote_stage[HALO_MAX_PEERS] = {};      // send: slot 0 of my range in the peer's staging block (mapped)
+    size_t              remote_slot_bytes[HALO_MAX_PEERS] = {}; // send: distance to slot 1 there
+    unsigned long long *remote_flag[HALO_MAX_PEERS] = {}; // send: the peer's "ready" flag for me; recv: the peer's "consumed" flag for me
+    unsigned long long *local_flag[HALO_MAX_PEERS]  = {}; // send: my "consumed" flag from the peer; recv: my "ready" flag from the peer
+  };
+  struct HaloDir // one direction: owner -> ghoster (update_ghost_values) or ghoster -> owner (compress)
+  {
+    HaloSide            send, recv;
+    char               *stage      = nullptr; // my staging block: 2 slots of 8-byte elements
+    size_t              slot_bytes = 0;
+    unsigned long long *epoch      = nullptr; // device counter of completed exchanges
+    unsigned           *ticket     = nullptr; // [2]: last-block detection of the send and the recv kernel
+  };
+  template <typename T>
+  void halo_exchange(const HaloDir &hd, bool ghost_direction, T *vec, uint32_t n_owned, const uint32_t *import_indices, cudaStream_t s);
+
   // ---------------------------------------------------------------- cell kernels (operator.cu)
   struct CellData
   {

@@ -207,9 +207,18 @@ int mgb_comm_init(const void *id, int rank, int size, const char *libnccl_path)
     ctx().comm = create_nccl_comm(id, rank, size, libnccl_path);
   });
 }
+int mgb_comm_enable_peer_exchange(int *enabled)
+{
+  return guarded([&] {
+    const bool on = p2p_back_partitioners();
+    if (enabled)
+      *enabled = on ? 1 : 0;
+  });
+}
 int mgb_comm_finalize(void)
 {
   return guarded([&] {
+    p2p_release_all(); // collective: peers may still acknowledge into our staging segments
     delete ctx().comm;
     ctx().comm = nullptr;
   });

@@ -24,6 +24,8 @@ namespace mgb
     virtual void exchange(const std::vector<Msg> &sends, const std::vector<Msg> &recvs, cudaStream_t s) = 0;
     virtual void allreduce_sum(double *dev, int n, cudaStream_t s)                                       = 0;
     virtual void allreduce_max(double *dev, int n, cudaStream_t s)                                       = 0;
+    // host-to-host all-gather of `bytes` per rank (setup only; synchronises the stream)
+    virtual void allgather_host(const void *send, void *recv, size_t bytes, cudaStream_t s) = 0;
   };
   // NCCL-backed communicator; `unique_id` is the 128-byte ncclUniqueId broadcast by the launcher
   // (torch.distributed in bench.py / tests).  libnccl.so.2 is resolved with dlopen at run time.

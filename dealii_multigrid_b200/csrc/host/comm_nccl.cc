@@ -29,6 +29,7 @@ namespace mgb
       int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t)                            = nullptr;
       int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t)                                  = nullptr;
       int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t)               = nullptr;
+      int (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t)                    = nullptr;
       const char *(*GetErrorString)(int)                                                               = nullptr;
     };
 
@@ -62,6 +63,7 @@ namespace mgb
       a.Send           = reinterpret_cast<decltype(a.Send)>(sym("ncclSend"));
       a.Recv           = reinterpret_cast<decltype(a.Recv)>(sym("ncclRecv"));
       a.AllReduce      = reinterpret_cast<decltype(a.AllReduce)>(sym("ncclAllReduce"));
+      a.AllGather      = reinterpret_cast<decltype(a.AllGather)>(sym("ncclAllGather"));
       a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
       return a;
     }
@@ -109,6 +111,18 @@ namespace mgb
       void allreduce_max(double *dev, int n, cudaStream_t s) override
       {
         check(a_, a_.AllReduce(dev, dev, (size_t)n, ncclFloat64, ncclMax, comm_, s), "ncclAllReduce");
+      }
+
+      void allgather_host(const void *send, void *recv, size_t bytes, cudaStream_t s) override
+      {
+        char *dev = nullptr;
+        if (cudaMalloc((void **)&dev, bytes * size_t(size_ + 1)) != cudaSuccess)
+          throw std::runtime_error("allgather_host: cudaMalloc failed");
+        cudaMemcpyAsync(dev, send, bytes, cudaMemcpyHostToDevice, s);
+        check(a_, a_.AllGather(dev, dev + bytes, bytes, ncclInt8, comm_, s), "ncclAllGather");
+        cudaMemcpyAsync(recv, dev + bytes, bytes * size_t(size_), cudaMemcpyDeviceToHost, s);
+        cudaStreamSynchronize(s);
+        cudaFree(dev);
       }
 
     private:

@@ -339,13 +339,14 @@ namespace mgb
       return d;
     }
 
-    // Levels with fewer cells per rank than this live on the first ranks only (DoFMap::build): a level of ~30k cells costs
-    // less on one B200 than the 16 halo exchanges per V-cycle that partitioning it over 8 GPUs adds (each ~25 us).
+    // Levels with fewer cells per rank than this live on the first ranks only (DoFMap::build) and need no halo exchange.
+    // Measured on 8 B200 (hypercube L=7, p=4): 512 -> 21.9 ms per solve, 32768 (levels up to 2.1M DoFs on rank 0 alone)
+    // -> 24.6 ms: one exchange costs only ~14 us, less than serialising a whole level on one GPU.
     int64_t min_cells_per_rank()
     {
       static const int64_t v = [] {
         const char *e = std::getenv("MGB_MIN_CELLS_PER_RANK");
-        return e ? std::max<int64_t>(1, std::atoll(e)) : int64_t(32768);
+        return e ? std::max<int64_t>(1, std::atoll(e)) : int64_t(512);
       }();
       return v;
     }
@@ -685,6 +686,8 @@ namespace mgb
         }
         n_cells_hn = fd.n_cells_hanging;
         n_cells_n  = fd.n_cells - fd.n_cells_hanging;
+        // several ranks: map the neighbours' staging memory so that ghost exchanges go over NVLink peer stores (collective)
+        p2p_back_partitioners();
       }
 
       int               n_levels() const override { return (int)levels.size(); }

@@ -71,7 +71,10 @@ namespace mgb
         send_buf.alloc(p.n_ghost);
         recv_buf.alloc(p.n_ghost);
       }
+    if (ctx().comm && ctx().comm->size() > 1)
+      p2p_register(this);
   }
+  DevicePartitioner::~DevicePartitioner() { p2p_unregister(this); }
 
   // ------------------------------------------------------------------------------------------ vector
   namespace
@@ -123,6 +126,12 @@ namespace mgb
     Context &c = ctx();
     if (!c.comm)
       throw std::runtime_error("update_ghost_values: vector has ghosts but no communicator is set");
+    if (part->p2p)
+      {
+        halo_exchange<T>(part->p2p->ghost, true, data, n_owned, part->import_indices.ptr, c.stream);
+        c.launches += 2;
+        return;
+      }
     const Partitioner &p   = part->host;
     T                 *snd = reinterpret_cast<T *>(part->send_buf.ptr);
     if (!p.import_indices.empty())
@@ -146,6 +155,13 @@ namespace mgb
     Context &c = ctx();
     if (!c.comm)
       throw std::runtime_error("compress: vector has ghosts but no communicator is set");
+    if (part->p2p)
+      {
+        // the send kernel zeroes the ghost tail after reading it (compress ends with zero_out_ghost_values)
+        halo_exchange<T>(part->p2p->compress, false, data, n_owned, part->import_indices.ptr, c.stream);
+        c.launches += 2;
+        return;
+      }
     const Partitioner &p   = part->host;
     T                 *rcv = reinterpret_cast<T *>(part->recv_buf.ptr);
     std::vector<Msg>   sends, recvs;

@@ -85,15 +85,32 @@ namespace mgb
 
   // ------------------------------------------------------------------------------------------ partitioner
   // Device copy of Utilities::MPI::Partitioner + the exchange buffers.
+  // peer-memory backing of one partitioner (host/p2p.cc, device/halo.cu): when present, ghost exchanges are two small
+  // kernels storing straight into the neighbours' staging blocks over NVLink instead of NCCL send/recv groups
+  struct P2PBacking
+  {
+    HaloDir               ghost, compress;
+    std::shared_ptr<void> segment; // keeps the mapped segments alive
+  };
   struct DevicePartitioner
   {
     Partitioner            host;
     DeviceBuffer<uint32_t> import_indices;
-    // type-erased exchange buffers (sized for double)
-    DeviceBuffer<double> send_buf, recv_buf;
+    // type-erased exchange buffers (sized for double) of the NCCL path
+    DeviceBuffer<double>        send_buf, recv_buf;
+    std::unique_ptr<P2PBacking> p2p;
     explicit DevicePartitioner(const Partitioner &p);
+    ~DevicePartitioner();
+    DevicePartitioner(const DevicePartitioner &) = delete;
+    DevicePartitioner &operator=(const DevicePartitioner &) = delete;
     bool trivial() const { return host.n_ghost == 0 && host.import_indices.empty(); }
   };
+  // collective over all ranks: back every partitioner created since the last call with peer-mapped staging memory;
+  // returns false (NCCL path stays in use) on one rank, without peer access, or with MGB_P2P=0
+  bool p2p_back_partitioners();
+  void p2p_release_all(); // collective, before the communicator is destroyed
+  void p2p_register(DevicePartitioner *p);
+  void p2p_unregister(DevicePartitioner *p);
 
   // ------------------------------------------------------------------------------------------ vector
   template <typename T> struct DVec

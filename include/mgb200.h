@@ -66,6 +66,11 @@ int mgb_profile_stop(double *total_ms, int64_t *n_launches);
 /* NCCL communicator for ghost exchange and reductions; unique_id = 128-byte ncclUniqueId */
 int mgb_comm_unique_id(void *out128, const char *libnccl_path);
 int mgb_comm_init(const void *unique_id128, int rank, int size, const char *libnccl_path);
+/* collective: back the partitioners of every operator / transfer created so far with peer-mapped staging memory
+ * (cudaIpc); their update_ghost_values / compress(add) then run as NVLink peer stores instead of NCCL send/recv.
+ * mgb_problem_create calls it itself.  Opt-in: environment variable MGB_P2P=1; *enabled = 0 if the ranks stay on the
+ * NCCL send/recv path (variable unset, no peer access). */
+int mgb_comm_enable_peer_exchange(int *enabled);
 int mgb_comm_finalize(void);
 
 /* ---- 1-D finite element data (host; FE_Q(degree) + QGauss(degree+1) on [0,1]) ------------------- */
