@@ -11,8 +11,9 @@ Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]` pri
   * `roofline`: the dominant kernel (finest-level FP64 Laplace cell loop), timed live with CUDA-event pairs on the
     launching stream around every launch inside the timed region (mgb_profile_start/stop);
     algorithmic bytes = 16 B/DoF (read src once, write dst once; SURVEY.md 8(d));
-  * `cpu_baseline` / `--impl reference`: the CPU restatement of the reference algorithm under oracle/ timed on the
-    host cores (deal.II itself cannot be built here: SURVEY.md 8(c)).
+  * `cpu_baseline` / `--impl reference`: the threaded C restatement of the reference's CPU algorithm (oracle/mgcpu.c:
+    deal.II's 12-sweep cell kernel, Chebyshev, transfers, V-cycle, CG; OpenMP over coloured cells, thread count autotuned)
+    timed on the host cores on a bounded sample (deal.II itself cannot be built here: SURVEY.md 8(c)).
 Workload: BASELINE.json configs[1] -- 3-D hypercube Poisson, global coarsening, p=4, FP64 V-cycle, coarse CG.
 N>1: one rank per GPU (torchrun), z-order partition of the same mesh (strong scaling), NCCL ghost exchange.
 """
@@ -93,27 +94,29 @@ def measured_peaks():
 
 # ------------------------------------------------------------------------------------------------ CPU arm (oracle)
 def cpu_solve_sample(n_ref, degree, steps, warmup):
-    """time the CPU restatement (oracle/) of the same solve on a bounded sample of the workload"""
-    import numpy as np
+    """time the threaded C restatement of the reference's CPU algorithm (oracle/mgcpu.c) on a bounded sample of the workload:
+    the same solver on a smaller hypercube, on as many host threads as speed the operator up (autotuned)"""
     import dealii_multigrid_b200 as mg  # host-side map generator only (no GPU call)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from util import OracleHierarchy
+    from util import mesh_sequence
     from oracle import reference as ref
+    from oracle.cpu_solver import CpuMultigrid
 
-    H = OracleHierarchy("hypercube", n_ref, degree, "HMG-global", 3, "cg")
-    b = ref.assemble_rhs_constant(H.maps[-1])
-    n = H.maps[-1].n_dofs
-    for s in H.smoothers:
-        s.estimate_eigenvalues()
+    meshes = mesh_sequence("hypercube", n_ref)
+    dofmaps = [mg.DoFMap(m, degree) for m in meshes]
+    tmaps = [None] + [mg.TransferMap(meshes[l], dofmaps[l], meshes[l - 1], dofmaps[l - 1]) for l in range(1, len(meshes))]
+    M = CpuMultigrid(dofmaps, tmaps, 3, 20.0, 20)
+    threads = M.autotune_threads()
+    b = ref.assemble_rhs_constant(M.maps[-1])
+    n = M.maps[-1].n_dofs
     best, its = 1e300, 0
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        _, its, _ = H.solve(b.copy())
+        _, its, _, _ = M.solve(b)
         dt = time.perf_counter() - t0
         if i >= warmup:
             best = min(best, dt)
-    return {"n_dofs": n, "n_iterations": its, "seconds": best, "value": n * its / best,
-            "cores": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1)) if False else 1}
+    return {"n_dofs": n, "n_iterations": its, "seconds": best, "value": n * its / best, "cores": threads}
 
 
 def run_reference(args):
@@ -121,8 +124,8 @@ def run_reference(args):
     if rank != 0:
         return
     n_ref = args.cpu_nref
-    r = cpu_solve_sample(n_ref, args.degree, max(1, args.steps), 0 if args.steps else 0)
-    sample = f"{workload_name(n_ref, args.degree, 'double')}: best of {max(1, args.steps)} solves, numpy oracle (deal.II unavailable)"
+    r = cpu_solve_sample(n_ref, args.degree, max(1, args.steps), min(args.warmup, 1))
+    sample = f"{workload_name(n_ref, args.degree, 'double')}: best of {max(1, args.steps)} solves, threaded C restatement oracle/mgcpu.c on {r['cores']} thread(s) (deal.II itself cannot be built here)"
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": r["seconds"] * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -238,7 +241,7 @@ def run_ours(args):
     if world == 1 and not args.no_cpu:
         c = cpu_solve_sample(args.cpu_nref, args.degree, 1, 0)
         cpu = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
-               "sample": f"{workload_name(args.cpu_nref, args.degree, 'double')}: 1 solve ({c['seconds']:.1f} s), numpy oracle"}
+               "sample": f"{workload_name(args.cpu_nref, args.degree, 'double')}: 1 solve ({c['seconds']:.1f} s), threaded C restatement oracle/mgcpu.c on {c['cores']} thread(s)"}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -271,7 +274,7 @@ def main():
     ap.add_argument("--nref", type=int, default=7, help="NRefGlobal of the GPU workload (7: 513^3 = 135 005 697 DoFs)")
     ap.add_argument("--degree", type=int, default=4)
     ap.add_argument("--number", default="double", choices=["double", "float"], help="MGNumberType")
-    ap.add_argument("--cpu-nref", type=int, default=4, help="NRefGlobal of the bounded CPU sample")
+    ap.add_argument("--cpu-nref", type=int, default=5, help="NRefGlobal of the bounded CPU sample (5: 129^3 = 2 146 689 DoFs)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -155,3 +155,36 @@ def test_local_smoothing_oracle_pins(geometry, L, p, mg_type):
     v[H.fine_maps.constrained] = 0.0
     a, c = u @ H.mg.vmult(v), v @ H.mg.vmult(u)
     assert abs(a - c) < 1e-10 * abs(a)
+
+
+@pytest.mark.parametrize("L,p", [(3, 2), (2, 4), (3, 1)])
+def test_c_restatement_matches_numpy_oracle(L, p):
+    """oracle/mgcpu.c (the timed host baseline of bench.py) against oracle/reference.py: operator, eigenvalue estimate,
+    transfers, one V-cycle and the full CG solve on hypercube hierarchies"""
+    from oracle.cpu_solver import CpuMultigrid
+    from util import OracleHierarchy, rel_l2, seeded
+    H = OracleHierarchy("hypercube", L, p, "HMG-global")
+    M = CpuMultigrid(H.dofmaps, H.tmaps)
+    top = len(H.maps) - 1
+    n = H.maps[-1].n_dofs
+    x = seeded(n)
+    assert rel_l2(M.vmult(top, x), H.ops[-1].vmult(x)) < 1e-13
+    for l in range(1, top + 1):
+        H.smoothers[l].estimate_eigenvalues()
+        assert abs(M.lambda_max(l) - H.smoothers[l].lmax) < 1e-10 * H.smoothers[l].lmax
+    uc, uf = seeded(H.maps[top - 1].n_dofs, 1), seeded(n, 2)
+    a, b = uf.copy(), uf.copy()
+    M.prolongate_and_add(top, a, uc)
+    H.transfers[top].prolongate_and_add(b, uc)
+    assert rel_l2(a, b) < 1e-13
+    a, b = uc.copy(), uc.copy()
+    M.restrict_and_add(top, a, uf)
+    H.transfers[top].restrict_and_add(b, uf)
+    assert rel_l2(a, b) < 1e-13
+    r = x.copy()
+    r[H.maps[-1].constrained] = 0.0
+    assert rel_l2(M.vcycle(r), H.mg.vmult(r)) < 1e-12
+    rhs = ref.assemble_rhs_constant(H.maps[-1])
+    xs, its, res, _ = M.solve(rhs)
+    xr, itr, ctl = H.solve(rhs.copy())
+    assert its == itr and rel_l2(xs, xr) < 1e-11 and abs(res - ctl.last_value) < 1e-10 * ctl.initial_value
