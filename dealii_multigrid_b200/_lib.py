@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmgb200.so")
+LIB_PATH = os.environ.get("MGB200_LIB") or os.path.join(_HERE, "lib", "libmgb200.so")  # MGB200_LIB: kernel-variant experiments
 
 c_u8p = C.POINTER(C.c_uint8)
 c_u16p = C.POINTER(C.c_uint16)

@@ -121,9 +121,15 @@ namespace mgb
   {
     static constexpr int n   = P + 1;
     static constexpr int CW  = 32 / n;          // cells per warp
-    static constexpr int W   = P <= 4 ? 4 : 2;  // warps per block
+#ifndef MGB_SLAB_W
+#define MGB_SLAB_W 4
+#endif
+#ifndef MGB_SLAB_MINB
+#define MGB_SLAB_MINB 3
+#endif
+    static constexpr int W   = P <= 4 ? MGB_SLAB_W : 2;  // warps per block
     static constexpr int CPB = CW * W;          // cells per block
-    static constexpr int MIN_BLOCKS = P <= 4 ? 3 : 2; // resident blocks per SM the register allocation must allow
+    static constexpr int MIN_BLOCKS = P <= 4 ? MGB_SLAB_MINB : 2; // resident blocks per SM the register allocation must allow
   };
 
   // warp-level version of hanging_node_sweeps for the padded slab layout; `u` = the warp's cells, tb = their 32-word records (word 27 = mask | level << 16)

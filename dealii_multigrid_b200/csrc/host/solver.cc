@@ -35,6 +35,29 @@ namespace mgb
     MGB_CUDA(cudaMallocHost((void **)&host_result, 8 * sizeof(double)));
   }
 
+  bool Context::overlap_ready()
+  {
+    static const bool enabled = [] {
+      // opt-in: measured on 2 and 8 B200 (hypercube L=7, p=4) the split cell loop hides nothing that matters -- the
+      // exchange latency that limits strong scaling sits on the coarse levels, whose interior kernels are shorter than
+      // one exchange (profiles/r1h_multigpu_notes.txt)
+      const char *e = std::getenv("MGB_OVERLAP");
+      return e && e[0] == '1';
+    }();
+    if (!enabled || !comm || comm->size() < 2 || stream == nullptr)
+      return false;
+    if (!comm_stream)
+      {
+        MGB_CUDA(cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i)
+          {
+            MGB_CUDA(cudaEventCreateWithFlags(&ev_fork[i], cudaEventDisableTiming));
+            MGB_CUDA(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
+          }
+      }
+    return true;
+  }
+
   void Context::prof_begin(long long n_cells)
   {
     if (!prof_enabled || n_cells != prof_cells)
@@ -119,16 +142,17 @@ namespace mgb
     return finish_reduction() / double(n_global);
   }
 
-  template <typename T> void DVec<T>::update_ghost_values() const
+  template <typename T> void DVec<T>::update_ghost_values(cudaStream_t on) const
   {
     if (!part || part->trivial())
       return;
-    Context &c = ctx();
+    Context           &c      = ctx();
+    const cudaStream_t stream = on ? on : c.stream;
     if (!c.comm)
       throw std::runtime_error("update_ghost_values: vector has ghosts but no communicator is set");
     if (part->p2p)
       {
-        halo_exchange<T>(part->p2p->ghost, true, data, n_owned, part->import_indices.ptr, c.stream);
+        halo_exchange<T>(part->p2p->ghost, true, data, n_owned, part->import_indices.ptr, stream);
         c.launches += 2;
         return;
       }
@@ -136,7 +160,7 @@ namespace mgb
     T                 *snd = reinterpret_cast<T *>(part->send_buf.ptr);
     if (!p.import_indices.empty())
       {
-        idx_gather<T>(snd, data, part->import_indices.ptr, (uint32_t)p.import_indices.size(), c.stream);
+        idx_gather<T>(snd, data, part->import_indices.ptr, (uint32_t)p.import_indices.size(), stream);
         ++c.launches;
       }
     std::vector<Msg> sends, recvs;
@@ -145,20 +169,21 @@ namespace mgb
     for (size_t i = 0; i < p.ghost_ranks.size(); ++i)
       recvs.push_back(
         Msg{p.ghost_ranks[i], data + n_owned + p.ghost_offsets[i], size_t(p.ghost_offsets[i + 1] - p.ghost_offsets[i]) * sizeof(T)});
-    c.comm->exchange(sends, recvs, c.stream);
+    c.comm->exchange(sends, recvs, stream);
   }
 
-  template <typename T> void DVec<T>::compress_add()
+  template <typename T> void DVec<T>::compress_add(cudaStream_t on)
   {
     if (!part || part->trivial())
       return;
-    Context &c = ctx();
+    Context           &c      = ctx();
+    const cudaStream_t stream = on ? on : c.stream;
     if (!c.comm)
       throw std::runtime_error("compress: vector has ghosts but no communicator is set");
     if (part->p2p)
       {
         // the send kernel zeroes the ghost tail after reading it (compress ends with zero_out_ghost_values)
-        halo_exchange<T>(part->p2p->compress, false, data, n_owned, part->import_indices.ptr, c.stream);
+        halo_exchange<T>(part->p2p->compress, false, data, n_owned, part->import_indices.ptr, stream);
         c.launches += 2;
         return;
       }
@@ -170,13 +195,14 @@ namespace mgb
         Msg{p.ghost_ranks[i], data + n_owned + p.ghost_offsets[i], size_t(p.ghost_offsets[i + 1] - p.ghost_offsets[i]) * sizeof(T)});
     for (size_t i = 0; i < p.import_ranks.size(); ++i)
       recvs.push_back(Msg{p.import_ranks[i], rcv + p.import_offsets[i], size_t(p.import_offsets[i + 1] - p.import_offsets[i]) * sizeof(T)});
-    c.comm->exchange(sends, recvs, c.stream);
+    c.comm->exchange(sends, recvs, stream);
     if (!p.import_indices.empty())
       {
-        idx_scatter_add<T>(data, rcv, part->import_indices.ptr, (uint32_t)p.import_indices.size(), c.stream);
+        idx_scatter_add<T>(data, rcv, part->import_indices.ptr, (uint32_t)p.import_indices.size(), stream);
         ++c.launches;
       }
-    zero_out_ghost_values();
+    if (n_ghost)
+      vec_set<T>(data + n_owned, T(0), n_ghost, stream), ++c.launches;
   }
 
   // ------------------------------------------------------------------------------------------ tridiagonal eigenvalues
@@ -271,6 +297,20 @@ namespace mgb
     if (!s.partitioner)
       throw std::runtime_error("Operator: partitioner required");
     part_ = std::make_shared<DevicePartitioner>(*s.partitioner);
+    if (s.partitioner->n_ghost > 0)
+      {
+        // cells reading ghost entries must wait for the exchange; all the others can run beside it
+        std::vector<uint32_t> boundary, interior;
+        for (long long c = 0; c < s.n_cells; ++c)
+          {
+            bool touches = false;
+            for (int e = 0; e < 27 && !touches; ++e)
+              touches = (s.entity_table[size_t(c) * 27 + e] & INDEX_MASK) >= s.partitioner->n_owned;
+            (touches ? boundary : interior).push_back(uint32_t(c));
+          }
+        boundary_cells_.upload(boundary.data(), boundary.size());
+        interior_cells_.upload(interior.data(), interior.size());
+      }
   }
 
   template <typename T> void OperatorT<T>::cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_only, double alpha) const
@@ -278,6 +318,31 @@ namespace mgb
     Context &c  = ctx();
     CellData cd = cd_;
     cd.root_length *= alpha; // the cell matrices are linear in h = root_length / 2^level
+    const bool overlap = !edge_only && !c.prof_enabled && boundary_cells_.n > 0 && interior_cells_.n > 0 && c.overlap_ready();
+    if (overlap)
+      {
+        // ghost exchange of src on the second stream beside the first half of the interior cells; boundary cells once the
+        // ghosts have arrived; compress of dst beside the second half of the interior cells (the unpack adds atomically)
+        const long long n_int = (long long)interior_cells_.n, half = n_int / 2;
+        MGB_CUDA(cudaEventRecord(c.ev_fork[0], c.stream));
+        MGB_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_fork[0], 0));
+        src.update_ghost_values(c.comm_stream);
+        MGB_CUDA(cudaEventRecord(c.ev_join[0], c.comm_stream));
+        if (zero_dst)
+          dst.zero();
+        if (half > 0)
+          cell_laplace_apply<T>(cd, src.data, dst.data, interior_cells_.ptr, half, c.stream), ++c.launches;
+        MGB_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join[0], 0));
+        cell_laplace_apply<T>(cd, src.data, dst.data, boundary_cells_.ptr, (long long)boundary_cells_.n, c.stream), ++c.launches;
+        MGB_CUDA(cudaEventRecord(c.ev_fork[1], c.stream));
+        MGB_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_fork[1], 0));
+        dst.compress_add(c.comm_stream);
+        MGB_CUDA(cudaEventRecord(c.ev_join[1], c.comm_stream));
+        cell_laplace_apply<T>(cd, src.data, dst.data, interior_cells_.ptr + half, n_int - half, c.stream), ++c.launches;
+        MGB_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join[1], 0));
+        src.zero_out_ghost_values();
+        return;
+      }
     src.update_ghost_values();
     if (zero_dst)
       dst.zero();

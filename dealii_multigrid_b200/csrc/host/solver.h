@@ -28,6 +28,11 @@ namespace mgb
     unsigned    *red_ticket  = nullptr;
     double      *host_result = nullptr; // pinned
     Comm        *comm        = nullptr;
+    // several ranks: second stream + events that let the ghost exchange of a cell loop run beside the interior cells
+    // (fork/join with events, so the pattern is also captured into the V-cycle's CUDA graph)
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t  ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
+    bool         overlap_ready();
     long long    launches    = 0; // kernels enqueued by this library (bench.py's gpu_launches)
     void         ensure();
     // live timing of the dominant kernel (bench.py's roofline): CUDA-event pairs around every cell-loop
@@ -223,9 +228,9 @@ namespace mgb
         reinit_like(o);
     }
     double mean_value(long long n_global) const;
-    // ghost exchange
-    void update_ghost_values() const;
-    void compress_add();
+    // ghost exchange (on the library's stream, or on `on` when given)
+    void update_ghost_values(cudaStream_t on = nullptr) const;
+    void compress_add(cudaStream_t on = nullptr);
     void zero_out_ghost_values() const
     {
       if (n_ghost)
@@ -403,6 +408,8 @@ namespace mgb
     DeviceBuffer<uint16_t>             mask_;
     DeviceBuffer<uint8_t>              level_;
     DeviceBuffer<uint32_t>             constrained_, edge_, edge_cells_;
+    // several ranks: cells that read ghost entries (boundary) and the others (interior), for overlapping the exchange
+    DeviceBuffer<uint32_t>             boundary_cells_, interior_cells_;
     mutable DeviceBuffer<T>            edge_src_vals_;
     mutable DVec<T>                    src_copy_;
     bool                               has_edge_global_ = false;
