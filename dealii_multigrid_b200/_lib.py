@@ -47,7 +47,8 @@ class LevelEdgesView(C.Structure):
 
 
 class CopyIndicesView(C.Structure):
-    _fields_ = [("n", C.c_uint32), ("active_idx", c_u32p), ("level_idx", c_u32p)]
+    _fields_ = [("n", C.c_uint32), ("active_idx", c_u32p), ("level_idx", c_u32p), ("distributed", C.c_int32),
+                ("owned_begin", C.c_int64), ("n_owned", C.c_uint32), ("n_ghost", C.c_uint32), ("ghost_global", c_i64p)]
 
 
 class OperatorDesc(C.Structure):
@@ -122,7 +123,7 @@ SIGNATURES = {
     "mgb_level_edges_create": (C.c_int, [P, P, PP]),
     "mgb_level_edges_view_get": (C.c_int, [P, C.POINTER(LevelEdgesView)]),
     "mgb_level_edges_destroy": (None, [P]),
-    "mgb_copy_indices_create": (C.c_int, [P, P, P, PP]),
+    "mgb_copy_indices_create": (C.c_int, [P, P, P, P, PP]),
     "mgb_copy_indices_view_get": (C.c_int, [P, C.POINTER(CopyIndicesView)]),
     "mgb_copy_indices_destroy": (None, [P]),
     "mgb_transfer_map_view_get": (C.c_int, [P, C.POINTER(TransferMapView)]),

@@ -248,14 +248,18 @@ class LevelEdges:
 class CopyIndices:
     """copy_indices[level] of MGTransferMatrixFree: (active-vector index, level-vector index) pairs"""
 
-    def __init__(self, active_dofs, level_mesh, level_dofs):
+    def __init__(self, active_dofs, level_mesh, level_dofs, active_mesh=None):
         lib = _lib.load()
         h = C.c_void_p()
-        _check(lib.mgb_copy_indices_create(active_dofs._h, level_mesh._h, level_dofs._h, C.byref(h)))
+        _check(lib.mgb_copy_indices_create(active_dofs._h, active_mesh._h if active_mesh is not None else None, level_mesh._h,
+                                           level_dofs._h, C.byref(h)))
         v = _lib.CopyIndicesView()
         _check(lib.mgb_copy_indices_view_get(h, C.byref(v)))
         self.active_idx = _arr(v.active_idx, v.n, np.uint32)
         self.level_idx = _arr(v.level_idx, v.n, np.uint32)
+        self.distributed = bool(v.distributed)
+        self.owned_begin, self.n_owned, self.n_ghost = int(v.owned_begin), int(v.n_owned), int(v.n_ghost)
+        self.ghost_global = _arr(v.ghost_global, v.n_ghost, np.int64)
         lib.mgb_copy_indices_destroy(h)
 
 

@@ -399,20 +399,26 @@ int mgb_level_edges_view_get(const mgb_level_edges *e, mgb_level_edges_view *v)
   });
 }
 void mgb_level_edges_destroy(mgb_level_edges *e) { delete e; }
-int  mgb_copy_indices_create(const mgb_dofmap *active_dofs, const mgb_mesh *level_mesh, const mgb_dofmap *level_dofs, mgb_copy_indices **out)
+int  mgb_copy_indices_create(const mgb_dofmap *active_dofs, const mgb_mesh *active_mesh, const mgb_mesh *level_mesh,
+                             const mgb_dofmap *level_dofs, mgb_copy_indices **out)
 {
   return guarded([&] {
     auto h = std::make_unique<mgb_copy_indices>();
-    h->c   = CopyIndices::build(*active_dofs->d, level_mesh->m, *level_dofs->d);
+    h->c   = CopyIndices::build(*active_dofs->d, level_mesh->m, *level_dofs->d, active_mesh ? &active_mesh->m : nullptr);
     *out   = h.release();
   });
 }
 int mgb_copy_indices_view_get(const mgb_copy_indices *c, mgb_copy_indices_view *v)
 {
   return guarded([&] {
-    v->n          = (uint32_t)c->c.active_idx.size();
-    v->active_idx = c->c.active_idx.data();
-    v->level_idx  = c->c.level_idx.data();
+    v->n            = (uint32_t)c->c.active_idx.size();
+    v->active_idx   = c->c.active_idx.data();
+    v->level_idx    = c->c.level_idx.data();
+    v->distributed  = c->c.distributed ? 1 : 0;
+    v->owned_begin  = c->c.part.owned_begin;
+    v->n_owned      = c->c.part.n_owned;
+    v->n_ghost      = c->c.part.n_ghost;
+    v->ghost_global = c->c.part.ghost_global.data();
   });
 }
 void mgb_copy_indices_destroy(mgb_copy_indices *c) { delete c; }

@@ -718,10 +718,14 @@ namespace mgb
     return le;
   }
 
-  CopyIndices CopyIndices::build(const DoFMap &ad, const Mesh &lm, const DoFMap &ld)
+  CopyIndices CopyIndices::build(const DoFMap &ad, const Mesh &lm, const DoFMap &ld, const Mesh *active_mesh)
   {
     if (ad.n_ranks > 1 || ld.n_ranks > 1)
-      throw std::runtime_error("CopyIndices: local smoothing on several ranks is not available yet (copy_indices_global_mine)");
+      {
+        if (!active_mesh)
+          throw std::runtime_error("CopyIndices: the active mesh is needed on several ranks");
+        return build_distributed(ad, *active_mesh, lm, ld);
+      }
     if (ad.degree != ld.degree)
       throw std::runtime_error("CopyIndices: degrees differ");
     CopyIndices      ci;
@@ -764,6 +768,133 @@ namespace mgb
           ci.active_idx.push_back(sg.a + uint32_t(k));
           ci.level_idx.push_back(sg.b + uint32_t(k));
         }
+    return ci;
+  }
+
+  CopyIndices CopyIndices::build_distributed(const DoFMap &ad, const Mesh &am, const Mesh &lm, const DoFMap &ld)
+  {
+    if (!ad.global_entities || !ld.global_entities)
+      throw std::runtime_error("CopyIndices: the DoF maps do not carry the global numbering");
+    if (ad.degree != ld.degree || ad.n_ranks != ld.n_ranks)
+      throw std::runtime_error("CopyIndices: incompatible DoF maps");
+    CopyIndices ci;
+    ci.distributed       = true;
+    const int        R = ad.n_ranks, me = ad.rank, level = ld.mesh_max_level;
+    const EntityKeys KA{ad.mesh_max_level}, KL{level};
+    int              esize[27];
+    for (int e = 0; e < 27; ++e)
+      esize[e] = ipow(ad.degree - 1, entity_dim(e));
+    FlatMap edge;
+    refinement_edge_entities(lm, KL, edge);
+    const int64_t a_begin = ad.rank_dof_begin[me], a_end = ad.rank_dof_begin[me + 1];
+    const int64_t l_begin = ld.rank_dof_begin[me], l_end = ld.rank_dof_begin[me + 1];
+    const auto    owner   = [](const std::vector<int64_t> &begin, int64_t g) {
+      return int(std::upper_bound(begin.begin(), begin.end(), g) - begin.begin()) - 1;
+    };
+    struct Seg
+    {
+      int64_t a, l;
+      int     size;
+      bool    operator<(const Seg &o) const { return a < o.a; }
+      bool    operator==(const Seg &o) const { return a == o.a; }
+    };
+    struct Ent
+    {
+      int64_t base;
+      int     size;
+      bool    operator<(const Ent &o) const { return base < o.base; }
+      bool    operator==(const Ent &o) const { return base == o.base; }
+    };
+    std::vector<Seg>              mine;    // pairs whose active DoF this rank owns
+    std::vector<Ent>              ghosts;  // their level DoFs owned elsewhere
+    std::vector<std::vector<Ent>> imports(R); // level DoFs of mine that the pairs of rank r refer to
+    FlatMap                       seen;    // active entity base -> 1 (each active entity once)
+    for (const Cell &c : am.cells)
+      {
+        if (c.level != level)
+          continue;
+        for (int e = 0; e < 27; ++e)
+          {
+            if (esize[e] == 0 || edge.find(KL(level, c.x, c.y, c.z, e)) >= 0)
+              continue;
+            const int64_t ga = ad.global_entities->find(KA(c.level, c.x, c.y, c.z, e));
+            const int64_t gl = ld.global_entities->find(KL(level, c.x, c.y, c.z, e));
+            if (ga < 0 || gl < 0)
+              throw std::runtime_error("CopyIndices: entity lookup failed");
+            if (seen.find(uint64_t(ga)) >= 0)
+              continue;
+            seen.insert(uint64_t(ga), 1);
+            const int ra = owner(ad.rank_dof_begin, ga), rl = owner(ld.rank_dof_begin, gl);
+            if (ra == me)
+              {
+                mine.push_back(Seg{ga, gl, esize[e]});
+                if (rl != me)
+                  ghosts.push_back(Ent{gl, esize[e]});
+              }
+            else if (rl == me)
+              imports[ra].push_back(Ent{gl, esize[e]});
+          }
+      }
+    const auto uniq = [](std::vector<Ent> &v) {
+      std::sort(v.begin(), v.end());
+      v.erase(std::unique(v.begin(), v.end()), v.end());
+    };
+    uniq(ghosts);
+    Partitioner &P = ci.part;
+    P.n_global     = ld.part.n_global;
+    P.owned_begin  = l_begin;
+    P.n_owned      = uint32_t(l_end - l_begin);
+    std::vector<uint32_t> ghost_off(ghosts.size() + 1, 0);
+    for (size_t g = 0; g < ghosts.size(); ++g)
+      ghost_off[g + 1] = ghost_off[g] + uint32_t(ghosts[g].size);
+    P.n_ghost = ghost_off.back();
+    P.ghost_global.resize(P.n_ghost);
+    {
+      int own = -1;
+      for (size_t g = 0; g < ghosts.size(); ++g)
+        {
+          for (int k = 0; k < ghosts[g].size; ++k)
+            P.ghost_global[ghost_off[g] + k] = ghosts[g].base + k;
+          const int o = owner(ld.rank_dof_begin, ghosts[g].base);
+          if (o != own)
+            {
+              P.ghost_ranks.push_back(o);
+              P.ghost_offsets.push_back(ghost_off[g]);
+              own = o;
+            }
+        }
+      P.ghost_offsets.push_back(P.n_ghost);
+    }
+    P.import_offsets.push_back(0);
+    for (int r = 0; r < R; ++r)
+      {
+        if (imports[r].empty())
+          continue;
+        uniq(imports[r]);
+        P.import_ranks.push_back(r);
+        for (const Ent &en : imports[r])
+          for (int k = 0; k < en.size; ++k)
+            P.import_indices.push_back(uint32_t(en.base - l_begin + k));
+        P.import_offsets.push_back(uint32_t(P.import_indices.size()));
+      }
+    std::sort(mine.begin(), mine.end());
+    for (const Seg &sg : mine)
+      {
+        uint32_t lbase;
+        if (sg.l >= l_begin && sg.l < l_end)
+          lbase = uint32_t(sg.l - l_begin);
+        else
+          {
+            const auto it = std::lower_bound(ghosts.begin(), ghosts.end(), Ent{sg.l, 0});
+            lbase         = P.n_owned + ghost_off[it - ghosts.begin()];
+          }
+        for (int k = 0; k < sg.size; ++k)
+          {
+            ci.active_idx.push_back(uint32_t(sg.a - a_begin + k));
+            ci.level_idx.push_back(lbase + uint32_t(k));
+          }
+      }
+    (void)a_end;
     return ci;
   }
 } // namespace mgb

@@ -141,9 +141,19 @@ namespace mgb
   // copy_indices of MGLevelGlobalTransfer: pairs (active-vector index, level-vector index) of the DoFs of
   // the ACTIVE cells living on this level, refinement-edge DoFs of the level skipped (fill_copy_indices with
   // skip_interface_dofs = true).
+  // Several ranks: the active DoF and its level DoF may belong to different ranks (copy_indices_global_mine /
+  // copy_indices_level_mine in deal.II).  The owner of the ACTIVE DoF holds the pair; level_idx then refers to an
+  // auxiliary ghosted level vector with the layout `part` (owned range of the level + the foreign level DoFs of this
+  // rank's pairs): copy_to_mg writes into it and compresses, copy_from_mg updates its ghosts and reads.
   struct CopyIndices
   {
     std::vector<uint32_t> active_idx, level_idx;
-    static CopyIndices build(const DoFMap &active_dofs, const Mesh &level_mesh, const DoFMap &level_dofs);
+    bool                  distributed = false;
+    Partitioner           part;
+    // active_mesh: the active mesh of active_dofs (several ranks only; every rank derives all ranks' lists from it)
+    static CopyIndices build(const DoFMap &active_dofs, const Mesh &level_mesh, const DoFMap &level_dofs, const Mesh *active_mesh = nullptr);
+
+  private:
+    static CopyIndices build_distributed(const DoFMap &active_dofs, const Mesh &active_mesh, const Mesh &level_mesh, const DoFMap &level_dofs);
   };
 } // namespace mgb

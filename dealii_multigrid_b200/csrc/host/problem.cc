@@ -592,7 +592,7 @@ namespace mgb
         for (unsigned l = 0; l < nl; ++l)
           {
             ls_transfer.operators[l] = levels[l].op.get();
-            ls_transfer.set_copy_indices(l, CopyIndices::build(*active_low, meshes[l], *levels[l].dofs));
+            ls_transfer.set_copy_indices(l, CopyIndices::build(*active_low, meshes[l], *levels[l].dofs, &meshes[nl]));
           }
         for (unsigned l = 0; l + 1 < nl; ++l)
           {

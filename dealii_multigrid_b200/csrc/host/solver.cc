@@ -655,7 +655,17 @@ namespace mgb
         DVec<T> &d = defect[l - minl];
         d.reinit_keep_layout(operators[l]->partitioner()); // zero: restriction adds into it
         const uint32_t n = (uint32_t)copy[l].active_idx.n;
-        if (n)
+        if (copy[l].part)
+          {
+            // the owner of the active DoF writes into the ghosted level vector; compress delivers to the level owner
+            DVec<T> &tmp = copy[l].tmp;
+            tmp.reinit_keep_layout(copy[l].part);
+            if (n)
+              idx_pair_copy<T, double>(tmp.data, copy[l].level_idx.ptr, src.data, copy[l].active_idx.ptr, n, c.stream), ++c.launches;
+            tmp.compress_add();
+            d.copy_from(tmp);
+          }
+        else if (n)
           idx_pair_copy<T, double>(d.data, copy[l].level_idx.ptr, src.data, copy[l].active_idx.ptr, n, c.stream), ++c.launches;
       }
   }
@@ -668,7 +678,16 @@ namespace mgb
     for (unsigned l = minl; l <= maxl; ++l)
       {
         const uint32_t n = (uint32_t)copy[l].active_idx.n;
-        if (n)
+        if (copy[l].part)
+          {
+            DVec<T> &tmp = copy[l].tmp;
+            tmp.reinit_keep_layout(copy[l].part);
+            tmp.copy_from(solution[l - minl]);
+            tmp.update_ghost_values();
+            if (n)
+              idx_pair_copy<double, T>(dst.data, copy[l].active_idx.ptr, tmp.data, copy[l].level_idx.ptr, n, c.stream), ++c.launches;
+          }
+        else if (n)
           idx_pair_copy<double, T>(dst.data, copy[l].active_idx.ptr, solution[l - minl].data, copy[l].level_idx.ptr, n, c.stream),
             ++c.launches;
       }

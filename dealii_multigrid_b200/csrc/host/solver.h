@@ -9,6 +9,7 @@
 
 #include <array>
 #include <cmath>
+#include <deque>
 #include <functional>
 #include <memory>
 #include <stdexcept>
@@ -518,14 +519,19 @@ namespace mgb
     struct Copy
     {
       DeviceBuffer<uint32_t> active_idx, level_idx;
+      // several ranks: layout of the auxiliary ghosted level vector the pairs refer to (CopyIndices::part)
+      std::shared_ptr<DevicePartitioner> part;
+      mutable DVec<T>                    tmp;
     };
-    std::vector<Copy> copy; // index l
+    std::deque<Copy> copy; // index l (deque: Copy holds a non-movable vector)
     void              set_copy_indices(unsigned level, const CopyIndices &ci)
     {
       if (copy.size() <= level)
         copy.resize(level + 1);
       copy[level].active_idx.upload(ci.active_idx.data(), ci.active_idx.size());
       copy[level].level_idx.upload(ci.level_idx.data(), ci.level_idx.size());
+      if (ci.distributed)
+        copy[level].part = std::make_shared<DevicePartitioner>(ci.part);
     }
     void prolongate_and_add(unsigned to_level, DVec<T> &dst, const DVec<T> &src) const override
     {

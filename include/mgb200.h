@@ -164,9 +164,16 @@ typedef struct
 {
   uint32_t        n;
   const uint32_t *active_idx, *level_idx; /* MGLevelGlobalTransfer::copy_indices[level] */
+  /* several ranks: the pairs are held by the owner of the ACTIVE DoF; level_idx refers to an auxiliary ghosted level vector
+   * [level's owned range | ghost_global] (copy_indices_global_mine / copy_indices_level_mine of deal.II) */
+  int32_t         distributed;
+  int64_t         owned_begin;
+  uint32_t        n_owned, n_ghost;
+  const int64_t  *ghost_global;
 } mgb_copy_indices_view;
-int  mgb_copy_indices_create(const mgb_dofmap *active_dofs, const mgb_mesh *level_mesh, const mgb_dofmap *level_dofs,
-                             mgb_copy_indices **out);
+/* active_mesh: the mesh of active_dofs; needed on several ranks only (may be NULL on one rank) */
+int  mgb_copy_indices_create(const mgb_dofmap *active_dofs, const mgb_mesh *active_mesh, const mgb_mesh *level_mesh,
+                             const mgb_dofmap *level_dofs, mgb_copy_indices **out);
 int  mgb_copy_indices_view_get(const mgb_copy_indices *c, mgb_copy_indices_view *view);
 void mgb_copy_indices_destroy(mgb_copy_indices *c);
 

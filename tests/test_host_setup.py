@@ -352,3 +352,27 @@ def test_ls_transfer_map(geometry, L, p):
             P.prolongate_and_add(uf, uc)
             if p >= 4:
                 np.testing.assert_allclose(uf, f(fine.dof_coordinates()), atol=1e-12)
+
+
+@pytest.mark.parametrize("n_ranks", [2, 3])
+@pytest.mark.parametrize("geometry,L,p", [("quadrant", 4, 2), ("annulus", 6, 1)])
+def test_partitioned_copy_indices_are_consistent(geometry, L, p, n_ranks):
+    """several ranks: the pairs held by the owners of the active DoFs, mapped to global indices, are exactly the serial pairs"""
+    mesh = mg.Mesh(geometry, L)
+    act = mg.DoFMap(mesh, p)
+    for l in range(mesh.n_global_levels):
+        lm = mesh.level_mesh(l)
+        serial = mg.CopyIndices(act, lm, mg.DoFMap(lm, p))
+        expect = set(zip(serial.active_idx.tolist(), serial.level_idx.tolist()))
+        got = set()
+        for r in range(n_ranks):
+            ar, lr = mg.DoFMap(mesh, p, n_ranks, r), mg.DoFMap(lm, p, n_ranks, r)
+            ci = mg.CopyIndices(ar, lm, lr, active_mesh=mesh)
+            assert ci.distributed and ci.n_owned == lr.n_owned and ci.owned_begin == lr.owned_begin
+            assert np.all(ci.active_idx < ar.n_owned)
+            lg = np.where(ci.level_idx < ci.n_owned, ci.level_idx.astype(np.int64) + ci.owned_begin,
+                          ci.ghost_global[np.maximum(ci.level_idx.astype(np.int64) - ci.n_owned, 0)] if ci.n_ghost else 0)
+            pairs = set(zip((ci.active_idx.astype(np.int64) + ar.owned_begin).tolist(), lg.tolist()))
+            assert not (pairs & got)
+            got |= pairs
+        assert got == expect

@@ -20,7 +20,7 @@ def main():
     import torch
     import torch.distributed as dist
     import dealii_multigrid_b200 as mg
-    from util import OracleHierarchy, params, rel_l2, seeded
+    from util import OracleHierarchy, OracleHierarchyLS, params, rel_l2, seeded
 
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -34,10 +34,16 @@ def main():
     mg.comm_init(uid[0], rank, world)
     ok = True
     for geometry, L, p, mg_type, coarse in [("hypercube", 3, 2, "HMG-global", "cg"), ("quadrant", 4, 4, "HMG-global", "cg"),
-                                            ("annulus", 5, 4, "HPMG", "cg_with_chebyshev"), ("quadrant", 3, 4, "PMG", "cg")]:
+                                            ("annulus", 5, 4, "HPMG", "cg_with_chebyshev"), ("quadrant", 3, 4, "PMG", "cg"),
+                                            ("quadrant", 4, 2, "HMG-local", "cg"), ("annulus", 6, 1, "HMG-local", "cg"),
+                                            ("quadrant", 4, 4, "HPMG-local", "cg")]:
         prob = mg.Problem(params(geometry, L, p, mg_type, coarse), world, rank)
-        H = OracleHierarchy(geometry, L, p, mg_type, 3, coarse)
-        d = prob.level_dofmap(prob.n_levels - 1)
+        if mg_type.endswith("local"):
+            H = OracleHierarchyLS(geometry, L, p, mg_type, 3, coarse)
+            H.maps, H.ops = [H.fine_maps], [H.fine_op]  # only the outer operator is compared level-wise below
+        else:
+            H = OracleHierarchy(geometry, L, p, mg_type, 3, coarse)
+        d = prob.fine_dofmap()
         lo, hi = d.owned_begin, d.owned_begin + d.n_owned
         n = H.maps[-1].n_dofs
         x = seeded(n)
