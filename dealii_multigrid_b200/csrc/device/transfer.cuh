@@ -20,6 +20,10 @@
 namespace mgb
 {
   constexpr int TRANSFER_WARPS = 4;
+  // resident blocks per SM the register allocation must allow: the kernels wait on their global loads (ncu: 8.4 warps
+  // stalled on long scoreboard per issue at 12 warps/SM), so occupancy pays more than the few spilled bytes cost --
+  // measured on B200, hypercube L=7 p=4: prolongation 1.30 -> 1.01 ms, restriction 1.07 -> 0.84 ms from 3 to 5 blocks
+  constexpr int transfer_min_blocks(int pf) { return pf <= 4 ? 5 : 2; }
 
   template <typename T> struct TransferMat
   {
@@ -49,7 +53,7 @@ namespace mgb
   }
 
   template <int PC, int PF, bool HMODE, bool PROLONGATE, typename T>
-  __global__ void __launch_bounds__(TRANSFER_WARPS * 32)
+  __global__ void __launch_bounds__(TRANSFER_WARPS * 32, transfer_min_blocks(PF))
     k_transfer(const long long n_coarse, const uint32_t *__restrict__ coarse_ctab, const int coarse_any_hanging,
                const uint32_t *__restrict__ fine_own, const uint32_t *__restrict__ fine_first, const uint8_t *__restrict__ n_children,
                const uint8_t *__restrict__ weight_code, const __grid_constant__ TransferMat<T> Pm, T *__restrict__ dst,

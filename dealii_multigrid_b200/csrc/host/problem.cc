@@ -732,7 +732,7 @@ namespace mgb
         r.final_residual    = ctl.last_value;
         r.coarse_iterations = coarse->collect_device_iterations();
         // every lazy initialisation has happened now: later V-cycles may be replayed from a CUDA graph
-        precond.allow_graph = coarse->single_kernel() && !local_smoothing;
+        precond.allow_graph = coarse->single_kernel();
         std::vector<std::array<double, N_STAGES + 2>> st(levels.size());
         for (auto &a : st)
           a.fill(0.0);

@@ -888,18 +888,19 @@ namespace mgb
   template <typename T> void PreconditionMGT<T>::vmult(DVec<double> &dst, const DVec<double> &src)
   {
     Context   &c = ctx();
+    const bool plain = transfer->top_level_is_plain_copy();
     bool graph_ok = allow_graph && c.stream != nullptr && !(timers && timers->enabled) && !c.prof_enabled &&
-                    !(c.comm && c.comm->size() > 1 && !graph_multirank()) && std::is_same<T, double>::value && !mg->edge_in &&
-                    src.data != dst.data &&
-                    transfer->top_level_is_plain_copy();
-    if (graph_ok)
+                    !(c.comm && c.comm->size() > 1 && !graph_multirank()) && src.data != dst.data;
+    if (graph_ok && plain)
       {
-        // only the aliasing path (no allocation, no copies) is captured
+        // global coarsening: only the aliasing path (no allocation, no copies) is captured
         uint32_t                           no, ng;
         std::shared_ptr<DevicePartitioner> part;
         transfer->level_layout(mg->max_level, no, ng, part);
-        graph_ok = src.n_owned == no && src.n_ghost == ng && dst.n_owned == no && dst.n_ghost == ng;
+        graph_ok = std::is_same<T, double>::value && !mg->edge_in && src.n_owned == no && src.n_ghost == ng && dst.n_owned == no &&
+                   dst.n_ghost == ng;
       }
+    // local smoothing: copy_to_mg / copy_from_mg are index kernels between fixed buffers, captured with the cycle
     if (!graph_ok)
       {
         vmult_eager(dst, src);

@@ -350,3 +350,34 @@ def test_local_smoothing_vcycle_and_cg(gpu, geometry, L, p, mg_type, coarse):
     assert res["n_dofs"] == n
     res = prob.solve_once(True)                                                  # with stage timers (edge_pro column)
     assert res["n_iterations"] == its_ref
+
+
+@pytest.mark.parametrize("mg_type", ["HMG-local", "HPMG-local"])
+def test_cuda_graph_replay_local_smoothing(gpu, mg_type):
+    """the LS V-cycle (copy_to_mg, edge_in, copy_from_mg; for HPMG-local nested as the coarse solver) replayed from a CUDA graph"""
+    import torch
+    from util import OracleHierarchyLS
+    mg = gpu
+    stream = torch.cuda.Stream()
+    try:
+        with torch.cuda.stream(stream):
+            mg.set_stream(stream.cuda_stream)
+            prob = mg.Problem(params("quadrant", 4, 2, mg_type, "cg"))
+            H = OracleHierarchyLS("quadrant", 4, 2, mg_type, 3, "cg")
+            _, its_ref, _ = H.solve(prob.rhs().to_numpy())
+            r1 = prob.solve_once()
+            x1 = prob.solution().to_numpy()
+            r2 = prob.solve_once()
+            r3 = prob.solve_once()
+            assert r1["n_iterations"] == r2["n_iterations"] == r3["n_iterations"] == its_ref
+            assert rel_l2(prob.solution().to_numpy(), x1) < 1e-12
+            v = seeded(x1.size)
+            v[H.fine_maps.constrained] = 0.0
+            src, dst = prob.fine_operator().initialize_dof_vector(), prob.fine_operator().initialize_dof_vector()
+            src.from_numpy(v)
+            prob.vcycle(dst, src)
+            prob.vcycle(dst, src)
+            assert rel_l2(dst.to_numpy(), H.mg.vmult(v)) < 1e-11
+            mg.synchronize()
+    finally:
+        mg.set_stream(0)
