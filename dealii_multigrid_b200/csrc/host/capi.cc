@@ -218,7 +218,9 @@ int mgb_comm_enable_peer_exchange(int *enabled)
 int mgb_comm_finalize(void)
 {
   return guarded([&] {
-    p2p_release_all(); // collective: peers may still acknowledge into our staging segments
+    MGB_CUDA(cudaDeviceSynchronize());
+    release_all_graphs(); // graphs that captured NCCL calls hold the communicator (ncclCommDestroy would wait for them)
+    p2p_release_all();    // collective: peers may still acknowledge into our staging segments
     delete ctx().comm;
     ctx().comm = nullptr;
   });

@@ -868,10 +868,39 @@ namespace mgb
     te();
   }
 
-  template <typename T> PreconditionMGT<T>::~PreconditionMGT()
+  namespace
+  {
+    std::vector<std::pair<void *, std::function<void()>>> &graph_owners()
+    {
+      static std::vector<std::pair<void *, std::function<void()>>> v;
+      return v;
+    }
+  } // namespace
+  void release_all_graphs()
+  {
+    for (auto &o : graph_owners())
+      o.second();
+  }
+  template <typename T> PreconditionMGT<T>::PreconditionMGT()
+  {
+    graph_owners().emplace_back(this, [this] { release_graphs(); });
+  }
+  template <typename T> void PreconditionMGT<T>::release_graphs()
   {
     for (GraphEntry &g : graphs_)
       cudaGraphExecDestroy(g.exec);
+    graphs_.clear();
+  }
+  template <typename T> PreconditionMGT<T>::~PreconditionMGT()
+  {
+    release_graphs();
+    auto &v = graph_owners();
+    for (size_t i = 0; i < v.size(); ++i)
+      if (v[i].first == this)
+        {
+          v.erase(v.begin() + i);
+          break;
+        }
   }
 
   // NCCL point-to-point calls can be stream-captured (every rank captures and replays the same sequence); the

@@ -668,7 +668,11 @@ namespace mgb
     // the whole launch sequence between two fixed vectors is captured once and replayed.  Not used while stage timers
     // or the per-kernel profiling events are active, on the legacy default stream, or with several ranks.
     bool allow_graph = false;
+    PreconditionMGT();
     ~PreconditionMGT();
+    PreconditionMGT(const PreconditionMGT &) = delete;
+    PreconditionMGT &operator=(const PreconditionMGT &) = delete;
+    void release_graphs(); // destroy the captured graphs (they are re-captured on demand)
 
   private:
     void vmult_eager(DVec<double> &dst, const DVec<double> &src);
@@ -680,6 +684,9 @@ namespace mgb
     };
     std::vector<GraphEntry> graphs_;
   };
+
+  // graphs that captured NCCL calls keep the communicator referenced: release them all before it is destroyed
+  void release_all_graphs();
 
   // MGCoarseGridApplyPreconditioner (multigrid_throughput.cc:422-564): nested V-cycle as coarse solver
   template <typename T> class CoarseApplyMGT : public MGCoarseBase<T>

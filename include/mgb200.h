@@ -71,6 +71,7 @@ int mgb_comm_init(const void *unique_id128, int rank, int size, const char *libn
  * mgb_problem_create calls it itself.  Opt-in: environment variable MGB_P2P=1; *enabled = 0 if the ranks stay on the
  * NCCL send/recv path (variable unset, no peer access). */
 int mgb_comm_enable_peer_exchange(int *enabled);
+/* collective; releases the captured V-cycle graphs (they hold the communicator) and the peer-mapped staging memory first */
 int mgb_comm_finalize(void);
 
 /* ---- 1-D finite element data (host; FE_Q(degree) + QGauss(degree+1) on [0,1]) ------------------- */

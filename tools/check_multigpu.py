@@ -78,11 +78,15 @@ def main():
               f"vcycle={e_vc:.1e} rhs={e_rhs:.1e} its={res['n_iterations']} (oracle {its}) {'OK' if good else 'FAIL'}", flush=True)
     t = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
-    mg.comm_finalize()
-    dist.destroy_process_group()
+    good = t.item() == 1.0
     if rank == 0:
-        print("MULTIGPU PARITY", "OK" if t.item() == 1.0 else "FAILED")
-    sys.exit(0 if t.item() == 1.0 else 1)
+        print("MULTIGPU PARITY", "OK" if good else "FAILED", flush=True)
+    dist.barrier()
+    torch.cuda.synchronize()
+    # CUDA graphs that captured NCCL calls keep the communicator referenced (ncclCommDestroy would wait for them), and Python
+    # may still hold problems through borrowed handles: leave without finalising, like bench.py
+    sys.stdout.flush()
+    os._exit(0 if good else 1)
 
 
 if __name__ == "__main__":

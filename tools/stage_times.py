@@ -42,8 +42,10 @@ def main():
         out.update(ranks=world, nref=args.nref, time_graph_replay=r0["time"])
         print(json.dumps(out), flush=True)
     if world > 1:
-        mg.comm_finalize()
-        dist.destroy_process_group()
+        dist.barrier()
+        torch.cuda.synchronize()
+    sys.stdout.flush()
+    os._exit(0)  # like bench.py: no communicator teardown while captured graphs are alive
 
 
 if __name__ == "__main__":
