@@ -84,6 +84,16 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm)}
 
 
+def measured_traffic(n_ref, degree, number, n_gpus):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this workload
+    (profiles/vmult_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum), or None if it was not captured"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "vmult_traffic.json")) as f:
+            return json.load(f).get(f"hypercube_L{n_ref}_p{degree}_{number}_{n_gpus}gpu", {}).get("dram_bytes")
+    except (OSError, ValueError):
+        return None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -253,7 +263,8 @@ def run_ours(args):
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
         "roofline": {"kernel": f"k_laplace_apply<{args.degree},double> (finest level)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.nref, args.degree, args.number, world),
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "launches_timed": k_launches, "avg_launch_ms": k_avg_s * 1e3,
                      "share_of_step": k_ms / ms_prof, "timed_in": "second pass of the same K solves with per-launch CUDA events "
                      "(eager launches, %.3f ms/step)" % (ms_prof / args.steps), "gdofs_per_s": n_owned / k_avg_s / 1e9,
