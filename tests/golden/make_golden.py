@@ -16,10 +16,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 sys.path.insert(0, os.path.dirname(HERE))
 
-from util import OracleHierarchy, seeded  # noqa: E402
+from util import make_oracle, seeded  # noqa: E402
 
 CASES = [("hypercube", 2, 4, "HMG-global", "cg"), ("quadrant", 3, 2, "HMG-global", "cg"), ("annulus", 4, 2, "HPMG", "cg_with_chebyshev"),
-         ("quadrant", 3, 4, "PMG", "cg")]
+         ("quadrant", 3, 4, "PMG", "cg"), ("quadrant", 3, 2, "HMG-local", "cg"), ("circle", 4, 2, "HPMG-local", "cg")]
 
 
 def case_name(c):
@@ -29,21 +29,23 @@ def case_name(c):
 def generate(c):
     from oracle import reference as ref
     geometry, L, p, mg_type, coarse = c
-    H = OracleHierarchy(geometry, L, p, mg_type, 3, coarse)
-    n = H.maps[-1].n_dofs
+    H = make_oracle(geometry, L, p, mg_type, 3, coarse)
+    n = H.fine_maps.n_dofs
     x = seeded(n)
     r = x.copy()
-    r[H.maps[-1].constrained] = 0.0
-    b = ref.assemble_rhs_constant(H.maps[-1])
+    r[H.fine_maps.constrained] = 0.0
+    b = ref.assemble_rhs_constant(H.fine_maps)
     sol, its, ctl = H.solve(b.copy())
     for s in H.smoothers:
         s.estimate_eigenvalues()
-    return dict(n_dofs=n, level_dofs=np.array([m.n_dofs for m in H.maps]), vmult=H.ops[-1].vmult(x),
-                inverse_diagonal=H.ops[-1].compute_inverse_diagonal(), vcycle=H.mg.vmult(r), rhs=b, solution=sol,
+    return dict(n_dofs=n, level_dofs=np.array([m.n_dofs for m in H.maps]), vmult=H.fine_op.vmult(x),
+                inverse_diagonal=H.fine_op.compute_inverse_diagonal(), vcycle=H.mg.vmult(r), rhs=b, solution=sol,
                 n_iterations=its, final_residual=ctl.last_value, lambda_max=np.array([s.lmax for s in H.smoothers]))
 
 
 if __name__ == "__main__":
     for c in CASES:
+        if os.path.exists(os.path.join(HERE, case_name(c) + ".npz")) and "--all" not in sys.argv:
+            continue  # existing fixtures stay frozen; pass --all to regenerate everything
         np.savez_compressed(os.path.join(HERE, case_name(c) + ".npz"), **generate(c))
         print("wrote", case_name(c))

@@ -54,11 +54,19 @@ class OracleHierarchy:
         self.coarse = ref.CoarseGridCG(self.ops[0], cheb)
         self.mg = ref.Multigrid(self.ops, self.smoothers, self.transfers, self.coarse)
 
+        self.fine_maps, self.fine_op = self.maps[-1], self.ops[-1]
+
     def solve(self, rhs, reltol=1e-4):
         x = np.zeros_like(rhs)
         ctl = ref.ReductionControl(10000, 1e-20, reltol)
         its = ref.solver_cg(self.ops[-1].vmult, x, rhs, self.mg.vmult, ctl)
         return x, its, ctl
+
+
+def make_oracle(geometry, n_ref_global, degree, mg_type, smoother_degree=3, coarse="cg"):
+    """oracle hierarchy for any multigrid Type of the reference's JSON input"""
+    cls = OracleHierarchyLS if mg_type.endswith("-local") else OracleHierarchy
+    return cls(geometry, n_ref_global, degree, mg_type, smoother_degree, coarse)
 
 
 class OracleHierarchyLS:
@@ -101,6 +109,7 @@ class OracleHierarchyLS:
             self.fine_op = ref.Operator(self.active_maps[-1])
         self.maps = self.level_maps + (self.active_maps if mg_type == "HPMG-local" else [])
         self.ops = self.level_ops + (self.active_ops if mg_type == "HPMG-local" else [])
+        self.smoothers = self.level_smoothers + (self.active_smoothers if mg_type == "HPMG-local" else [])
         self.fine_maps = self.active_maps[-1]
 
     def solve(self, rhs, reltol=1e-4):
