@@ -86,6 +86,9 @@ def main():
     # CUDA graphs that captured NCCL calls keep the communicator referenced (ncclCommDestroy would wait for them), and Python
     # may still hold problems through borrowed handles: leave without finalising, like bench.py
     sys.stdout.flush()
+    if os.environ.get("MGB_CHECK_FINALIZE") == "1":  # exercise mgb_comm_finalize (releases the captured graphs first)
+        mg.comm_finalize()
+        print(f"[rank {rank}] comm_finalize returned", flush=True)
     os._exit(0 if good else 1)
 
 
