@@ -115,6 +115,10 @@ SIGNATURES = {
     "mgb_mesh_get_cells": (C.c_int, [P, c_u32p]),
     "mgb_mesh_destroy": (None, [P]),
     "mgb_dofmap_create": (C.c_int, [P, C.c_int, C.c_int, C.c_int, PP]),
+    "mgb_dofmap_create_partitioned": (C.c_int, [P, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int64), PP]),
+    "mgb_partition_sequence": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_int64)]),
+    "mgb_partition_first_child": (C.c_int, [P, P, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "mgb_mesh_hanging_cells": (C.c_int, [P, C.POINTER(C.c_uint8)]),
     "mgb_dofmap_view_get": (C.c_int, [P, C.POINTER(DofmapView)]),
     "mgb_dofmap_expand": (C.c_int, [P, C.c_int, c_u32p]),
     "mgb_dofmap_destroy": (None, [P]),

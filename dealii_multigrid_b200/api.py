@@ -152,21 +152,57 @@ class Mesh:
         _check(self._lib.mgb_mesh_get_cells(self._h, out.ctypes.data_as(_lib.c_u32p)))
         return out
 
+    def hanging_cells(self):
+        """per leaf: does the cell carry a hanging-node constraint (Helper::is_constrained, multigrid_throughput.cc:231-268)"""
+        out = np.zeros(self.n_cells, dtype=np.uint8)
+        _check(self._lib.mgb_mesh_hanging_cells(self._h, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out.astype(bool)
+
     def __del__(self):
         if getattr(self, "_h", None):
             self._lib.mgb_mesh_destroy(self._h)
             self._h = None
 
 
+def partition_sequence(policy_name, meshes, n_ranks, min_cells_per_rank=1):
+    """Morton ranges of every rank on every mesh of a coarse -> fine sequence under one of the reference's
+    `PartitionerName` policies (multigrid_throughput.cc:2066-2174); returns an (n_meshes, n_ranks+1) int64 array"""
+    lib = _lib.load()
+    hs = (C.c_void_p * len(meshes))(*[m._h for m in meshes])
+    out = np.zeros((len(meshes), n_ranks + 1), dtype=np.int64)
+    _check(lib.mgb_partition_sequence(policy_name.encode(), hs, len(meshes), n_ranks, min_cells_per_rank,
+                                      out.ctypes.data_as(C.POINTER(C.c_int64))))
+    return out
+
+
+def first_child_boundaries(parents, children, child_begin):
+    """ownership with the first child (FirstChildPolicy, level cells of local smoothing)"""
+    lib = _lib.load()
+    cb = np.ascontiguousarray(child_begin, dtype=np.int64)
+    out = np.zeros_like(cb)
+    _check(lib.mgb_partition_first_child(parents._h, children._h, len(cb) - 1, cb.ctypes.data_as(C.POINTER(C.c_int64)),
+                                         out.ctypes.data_as(C.POINTER(C.c_int64))))
+    return out
+
+
 class DoFMap:
     """FE_Q(degree) DoFs + constraints + partitioner (DoFHandler/AffineConstraints/MatrixFree stand-in)."""
 
-    def __init__(self, mesh=None, degree=1, n_ranks=1, rank=0, _handle=None, _owner=None):
+    def __init__(self, mesh=None, degree=1, n_ranks=1, rank=0, cell_begin=None, _handle=None, _owner=None):
         self._lib = _lib.load()
         self._owner = _owner  # keeps a Problem alive for borrowed handles
         if _handle is not None:
             self._h = _handle
             self._borrowed = True
+        elif cell_begin is not None:  # explicit partition (partition_sequence / first_child_boundaries)
+            cb = np.ascontiguousarray(cell_begin, dtype=np.int64)
+            if cb.shape != (n_ranks + 1,):
+                raise ValueError("cell_begin must hold n_ranks+1 offsets")
+            h = C.c_void_p()
+            _check(self._lib.mgb_dofmap_create_partitioned(mesh._h, degree, n_ranks, rank, cb.ctypes.data_as(C.POINTER(C.c_int64)),
+                                                           C.byref(h)))
+            self._h = h
+            self._borrowed = False
         else:
             h = C.c_void_p()
             _check(self._lib.mgb_dofmap_create(mesh._h, degree, n_ranks, rank, C.byref(h)))

@@ -2,6 +2,7 @@
 #include "mgb200.h"
 
 #include "comm.h"
+#include "partition.h"
 #include "problem.h"
 
 #include <cstring>
@@ -318,6 +319,49 @@ int mgb_dofmap_create(const mgb_mesh *m, int degree, int n_ranks, int rank, mgb_
     h->owned = std::make_unique<DoFMap>(DoFMap::build(m->m, degree, n_ranks, rank));
     h->d     = h->owned.get();
     *out     = h.release();
+  });
+}
+int mgb_dofmap_create_partitioned(const mgb_mesh *m, int degree, int n_ranks, int rank, const int64_t *cell_begin, mgb_dofmap **out)
+{
+  return guarded([&] {
+    if (degree > MAX_DEGREE)
+      throw std::runtime_error("degree > MAX_DEGREE");
+    if (!cell_begin || n_ranks < 1)
+      throw std::runtime_error("mgb_dofmap_create_partitioned: cell_begin[n_ranks+1] required");
+    auto h   = std::make_unique<mgb_dofmap>();
+    h->owned = std::make_unique<DoFMap>(DoFMap::build(m->m, degree, n_ranks, rank, std::vector<int64_t>(cell_begin, cell_begin + n_ranks + 1)));
+    h->d     = h->owned.get();
+    *out     = h.release();
+  });
+}
+int mgb_partition_sequence(const char *policy_name, const mgb_mesh *const *meshes, int n_meshes, int n_ranks, int64_t min_cells_per_rank,
+                           int64_t *cell_begin)
+{
+  return guarded([&] {
+    // the policy only reads the meshes; copy them into the contiguous sequence its interface takes
+    std::vector<Mesh> seq;
+    seq.reserve(n_meshes);
+    for (int i = 0; i < n_meshes; ++i)
+      seq.push_back(meshes[i]->m);
+    for (auto &m : seq)
+      m.rebuild_index();
+    const auto b = PartitionPolicy::parse(policy_name ? policy_name : "").sequence(seq, n_ranks, std::max<int64_t>(1, min_cells_per_rank));
+    for (int i = 0; i < n_meshes; ++i)
+      std::copy(b[i].begin(), b[i].end(), cell_begin + size_t(i) * (n_ranks + 1));
+  });
+}
+int mgb_partition_first_child(const mgb_mesh *parents, const mgb_mesh *children, int n_ranks, const int64_t *child_begin, int64_t *cell_begin)
+{
+  return guarded([&] {
+    const auto b = first_child_boundaries(parents->m, children->m, std::vector<int64_t>(child_begin, child_begin + n_ranks + 1));
+    std::copy(b.begin(), b.end(), cell_begin);
+  });
+}
+int mgb_mesh_hanging_cells(const mgb_mesh *m, uint8_t *flags)
+{
+  return guarded([&] {
+    const auto f = cells_with_hanging_nodes(m->m);
+    std::copy(f.begin(), f.end(), flags);
   });
 }
 int mgb_dofmap_view_get(const mgb_dofmap *h, mgb_dofmap_view *v)

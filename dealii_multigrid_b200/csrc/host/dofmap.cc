@@ -1,4 +1,5 @@
 #include "dofmap.h"
+#include "partition.h"
 
 #include <algorithm>
 #include <stdexcept>
@@ -139,10 +140,36 @@ namespace mgb
     }
   } // namespace
 
+  std::vector<char> cells_with_hanging_nodes(const Mesh &mesh)
+  {
+    const EntityKeys  K{mesh.max_level()};
+    std::vector<char> out(mesh.cells.size());
+    uint64_t          own[27], eval[27];
+    for (size_t i = 0; i < mesh.cells.size(); ++i)
+      {
+        uint16_t mask;
+        analyse_cell(mesh, K, mesh.cells[i], own, eval, mask);
+        out[i] = (mask >> 3) != 0;
+      }
+    return out;
+  }
+
   DoFMap DoFMap::build(const Mesh &mesh, int degree, int n_ranks, int rank, int64_t min_cells_per_rank)
+  {
+    const int64_t nc = (int64_t)mesh.cells.size();
+    return build(mesh, degree, n_ranks, rank,
+                 equal_boundaries(nc, n_ranks, nc / std::max<int64_t>(1, min_cells_per_rank)));
+  }
+
+  DoFMap DoFMap::build(const Mesh &mesh, int degree, int n_ranks, int rank, const std::vector<int64_t> &cell_begin)
   {
     if (degree < 1)
       throw std::runtime_error("DoFMap: degree must be >= 1");
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks)
+      throw std::runtime_error("DoFMap: rank outside [0, n_ranks)");
+    if ((int)cell_begin.size() != n_ranks + 1 || cell_begin.front() != 0 || cell_begin.back() != (int64_t)mesh.cells.size() ||
+        !std::is_sorted(cell_begin.begin(), cell_begin.end()))
+      throw std::runtime_error("DoFMap: cell_begin must hold n_ranks+1 ascending offsets from 0 to n_cells");
     DoFMap dm;
     dm.degree         = degree;
     dm.n_ranks        = n_ranks;
@@ -155,10 +182,6 @@ namespace mgb
     for (int e = 0; e < 27; ++e)
       esize[e] = ipow(degree - 1, entity_dim(e));
 
-    std::vector<int64_t> cell_begin(n_ranks + 1);
-    const int64_t n_active = std::max<int64_t>(1, std::min<int64_t>(n_ranks, nc / std::max<int64_t>(1, min_cells_per_rank)));
-    for (int r = 0; r <= n_ranks; ++r)
-      cell_begin[r] = (nc * std::min<int64_t>(r, n_active)) / n_active;
     dm.cell_begin = cell_begin[rank];
     dm.n_cells    = cell_begin[rank + 1] - cell_begin[rank];
 

@@ -87,6 +87,9 @@ namespace mgb
     // only (the coarse levels of a global-coarsening hierarchy then live on few GPUs or on rank 0 alone and need no
     // halo exchange; the two-level transfers move the data between the different partitions)
     static DoFMap build(const Mesh &mesh, int degree, int n_ranks = 1, int rank = 0, int64_t min_cells_per_rank = 1);
+    // the same with an explicit partition: rank r owns the Morton range [cell_begin[r], cell_begin[r+1]) (ranks may be
+    // empty); see partition.h for the policies that produce such ranges
+    static DoFMap build(const Mesh &mesh, int degree, int n_ranks, int rank, const std::vector<int64_t> &cell_begin);
 
     // expand to the lexicographic (p+1)^3 index map (what MatrixFree stores); flags kept in bit 31
     void expand(const std::vector<uint32_t> &table, std::vector<uint32_t> &out) const;

@@ -1,4 +1,5 @@
 #include "problem.h"
+#include "partition.h"
 
 #include <algorithm>
 #include <chrono>
@@ -402,6 +403,20 @@ namespace mgb
       CGWork<double>                     cgw;
       long long                          n_cells_hn = 0, n_cells_n = 0;
       int                                n_ranks = 1, rank = 0;
+      std::vector<std::vector<int64_t>>  mesh_begin; // per mesh: the Morton range of every rank (partition.h)
+
+      // `PartitionerName`, or the integer `Partitioner` when no name is given (ref :2074-2104)
+      PartitionPolicy partition_policy() const
+      {
+        static const char *by_number[] = {"DefaultPolicy", "MinimalGranularityPolicy-40", "CellWeightPolicy-1.0",
+                                          "CellWeightPolicy-1.5", "CellWeightPolicy-2.0", "CellWeightPolicy-2.5",
+                                          "FirstChildPolicy", "BalancedGranularityPartitionPolicy"};
+        if (!prm.policy_name.empty())
+          return PartitionPolicy::parse(prm.policy_name);
+        if (prm.p >= 8)
+          throw std::runtime_error("Partitioner " + std::to_string(prm.p) + " is not implemented");
+        return PartitionPolicy::parse(by_number[prm.p]);
+      }
 
       Problem(const RunParameters &prm_, int n_ranks_, int rank_)
         : n_ranks(n_ranks_)
@@ -457,6 +472,7 @@ namespace mgb
           for (auto &m : meshes)
             m.rebuild_index();
         }
+        mesh_begin = partition_policy().sequence(meshes, n_ranks, min_cells_per_rank());
         const auto     level_degrees = polynomial_coarsening_sequence_bisect(prm.fe_degree_fine);
         const unsigned n_trias       = (unsigned)meshes.size();
         unsigned       max_level     = 0;
@@ -486,7 +502,7 @@ namespace mgb
                 L.degree     = level_degrees[std::max<int>(0, int(l) - int(n_trias) + 1)];
                 L.mesh_index = std::min(l, n_trias - 1);
               }
-            L.dofs = std::make_unique<DoFMap>(DoFMap::build(meshes[L.mesh_index], L.degree, n_ranks, rank, min_cells_per_rank()));
+            L.dofs = std::make_unique<DoFMap>(DoFMap::build(meshes[L.mesh_index], L.degree, n_ranks, rank, mesh_begin[L.mesh_index]));
             L.op   = std::make_unique<OperatorT<LT>>(setup_from_dofmap(*L.dofs));
           }
         // two-level transfers (ref :1600-1604)
@@ -548,6 +564,25 @@ namespace mgb
         meshes.push_back(std::move(active));
         for (auto &m : meshes)
           m.rebuild_index();
+        // active mesh: the policy's (optionally weighted) Morton split.  Level cells live with their first child (p4est /
+        // deal.II level ownership, SURVEY A.1: no vertical communication in the level transfers) on every level that
+        // gives each rank min_cells_per_rank() cells; smaller levels are consolidated on the first ranks, where they need no
+        // halo exchange.  MGB_LS_LEVEL_PARTITION=first_child / equal forces one rule on all levels.
+        mesh_begin.resize(nl + 1);
+        mesh_begin[nl] = partition_policy().fine(meshes[nl], n_ranks, min_cells_per_rank());
+        {
+          const char       *e    = std::getenv("MGB_LS_LEVEL_PARTITION");
+          const std::string rule = e ? e : "";
+          for (unsigned l = 0; l < nl; ++l)
+            {
+              const int64_t nc    = (int64_t)meshes[l].cells.size();
+              const bool    small = nc / min_cells_per_rank() < n_ranks;
+              if (rule == "equal" || (rule != "first_child" && small))
+                mesh_begin[l] = PartitionPolicy().fine(meshes[l], n_ranks, min_cells_per_rank());
+              else
+                mesh_begin[l] = first_child_boundaries(meshes[l], meshes[nl], mesh_begin[nl]);
+            }
+        }
         const unsigned max_level = (nl - 1) + (do_pmg ? (unsigned)level_degrees.size() : 0); // ref :1720-1723
         levels.resize(max_level + 1);
         level_edges.resize(nl);
@@ -557,7 +592,7 @@ namespace mgb
             Level &L     = levels[l];
             L.degree     = (int)level_degrees.front();
             L.mesh_index = (int)l;
-            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[l], L.degree, n_ranks, rank, min_cells_per_rank()));
+            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[l], L.degree, n_ranks, rank, mesh_begin[l]));
             level_edges[l]   = LevelEdges::build(meshes[l], *L.dofs);
             OperatorSetup st = setup_from_dofmap(*L.dofs);
             st.edge_constrained            = level_edges[l].edge_dofs.data();
@@ -573,7 +608,7 @@ namespace mgb
             Level &L     = levels[l];
             L.degree     = (int)level_degrees[l - nl];
             L.mesh_index = (int)nl;
-            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], L.degree, n_ranks, rank, min_cells_per_rank()));
+            L.dofs       = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], L.degree, n_ranks, rank, mesh_begin[nl]));
             L.op         = std::make_unique<OperatorT<LT>>(setup_from_dofmap(*L.dofs));
           }
         // the active-mesh DoFs the LS transfer copies from / to (dof_handlers.front())
@@ -582,7 +617,7 @@ namespace mgb
           active_low = levels[nl].dofs.get();
         else
           {
-            fine_dofs_own = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], (int)prm.fe_degree_fine, n_ranks, rank, min_cells_per_rank()));
+            fine_dofs_own = std::make_unique<DoFMap>(DoFMap::build(meshes[nl], (int)prm.fe_degree_fine, n_ranks, rank, mesh_begin[nl]));
             active_low    = fine_dofs_own.get();
           }
         // MGTransferMatrixFree::build (ref :1800-1802)

@@ -116,6 +116,22 @@ typedef struct
 } mgb_dofmap_view;
 
 int  mgb_dofmap_create(const mgb_mesh *m, int degree, int n_ranks, int rank, mgb_dofmap **out);
+/* the same with an explicit partition: rank r owns the Morton range [cell_begin[r], cell_begin[r+1]) */
+int  mgb_dofmap_create_partitioned(const mgb_mesh *m, int degree, int n_ranks, int rank, const int64_t *cell_begin /* n_ranks+1 */,
+                                   mgb_dofmap **out);
+/* Partition policies selected by `PartitionerName` (multigrid_throughput.cc:2066-2174; RepartitioningPolicyTools and the
+ * reference's BalancedGranularityPartitionPolicy, :372-419): "DefaultPolicy", "MinimalGranularityPolicy-N",
+ * "BalancedGranularityPartitionPolicy", "CellWeightPolicy-W" (hanging_nodes_weighting, :276-292), "FirstChildPolicy[-W]".
+ * meshes: coarse -> fine coarsening sequence; cell_begin: n_meshes * (n_ranks+1) Morton offsets.  Unknown names fail
+ * like the reference's ExcNotImplemented. */
+int  mgb_partition_sequence(const char *policy_name, const mgb_mesh *const *meshes, int n_meshes, int n_ranks,
+                            int64_t min_cells_per_rank, int64_t *cell_begin);
+/* ownership "with the first child" (FirstChildPolicy; level cells of local smoothing): cell_begin of `parents` from the
+ * partition of `children` */
+int  mgb_partition_first_child(const mgb_mesh *parents, const mgb_mesh *children, int n_ranks, const int64_t *child_begin,
+                               int64_t *cell_begin /* n_ranks+1 */);
+/* per leaf: 1 if the cell has a hanging-node constraint on a face or edge (Helper::is_constrained, :231-268) */
+int  mgb_mesh_hanging_cells(const mgb_mesh *m, uint8_t *flags /* n_cells */);
 int  mgb_dofmap_view_get(const mgb_dofmap *d, mgb_dofmap_view *view);
 /* expand an entity table to the lexicographic (p+1)^3 index map per cell (flag kept in bit 31) */
 int  mgb_dofmap_expand(const mgb_dofmap *d, int which /*0 eval, 1 own*/, uint32_t *out /* n_cells*(p+1)^3 */);

@@ -169,13 +169,28 @@ def test_transfer_map_weights(geometry, L, p):
     np.testing.assert_array_equal(w_prod, w[fine.own_idx])
 
 
+POLICIES = [None, "CellWeightPolicy-2.5", "FirstChildPolicy", "FirstChildPolicy-2.0", "MinimalGranularityPolicy-40",
+            "BalancedGranularityPartitionPolicy"]
+
+
+def _ranges(policy, seq, n_ranks):
+    """cell_begin per mesh of the coarse -> fine sequence (None: the default equal split inside DoFMap)"""
+    return [None] * len(seq) if policy is None else list(mg.partition_sequence(policy, seq, n_ranks))
+
+
+@pytest.mark.parametrize("policy", POLICIES)
 @pytest.mark.parametrize("n_ranks", [2, 3, 8])
 @pytest.mark.parametrize("geometry,L,p", [("hypercube", 2, 2), ("quadrant", 4, 3)])
-def test_partitioned_dofmaps_are_consistent(geometry, L, p, n_ranks):
-    """rank-local maps describe the same global numbering as the serial map; ghost/import lists match pairwise"""
-    mesh = mg.Mesh(geometry, L)
+def test_partitioned_dofmaps_are_consistent(geometry, L, p, n_ranks, policy):
+    """rank-local maps describe the same global numbering as the serial map; ghost/import lists match pairwise -- for the
+    default split and for every PartitionerName policy (ranks may then be empty, also in the middle of the rank order)"""
+    seq = mesh_sequence(geometry, L)
+    level = len(seq) - 1 if policy in (None, "CellWeightPolicy-2.5") else len(seq) - 2  # policies that act on coarse meshes
+    mesh, cb = seq[level], _ranges(policy, seq, n_ranks)[level]
     serial = mg.DoFMap(mesh, p)
-    parts = [mg.DoFMap(mesh, p, n_ranks, r) for r in range(n_ranks)]
+    parts = [mg.DoFMap(mesh, p, n_ranks, r, cell_begin=cb) for r in range(n_ranks)]
+    if cb is not None:
+        assert [d.cell_begin for d in parts] == list(cb[:-1])
     assert sum(d.n_owned for d in parts) == serial.n_dofs_global
     assert sum(d.n_cells for d in parts) == serial.n_cells
     s_eval = serial.eval_table()
@@ -217,20 +232,14 @@ def test_fast_diagonalisation_of_the_1d_pencil(p):
         assert np.abs(T3.T @ (D[:, None] * T3) - A).max() < 1e-13 * np.abs(A).max()
 
 
-@pytest.mark.parametrize("n_ranks", [2, 3, 8])
-@pytest.mark.parametrize("geometry,L,p,kind", [("hypercube", 2, 2, "h"), ("quadrant", 4, 3, "h"), ("quadrant", 3, 4, "p"), ("annulus", 5, 1, "h")])
-def test_partitioned_transfer_maps_are_consistent(geometry, L, p, kind, n_ranks):
-    """several ranks: the coarse cells of a rank may have children on other ranks; the transfer's own fine-side table,
-    weights and ghost/import lists must describe the serial transfer in the global numbering"""
-    seq = mesh_sequence(geometry, L)
-    (mf, pf), (mc, pc) = ((seq[-1], p), (seq[-2], p)) if kind == "h" else ((seq[-1], p), (seq[-1], max(p // 2, 1)))
+def _check_partitioned_transfer(mf, pf, mc, pc, cbf, cbc, n_ranks, ls=False):
     sf, sc = mg.DoFMap(mf, pf), mg.DoFMap(mc, pc)
-    st = mg.TransferMap(mf, sf, mc, sc)
+    st = mg.TransferMap(mf, sf, mc, sc, local_smoothing=ls)
     s_own, s_first, s_nch, s_w = sf.own_table(), st.fine_first(), st.n_children(), st.weight_code()
     tms = []
     for r in range(n_ranks):
-        df, dc = mg.DoFMap(mf, pf, n_ranks, r), mg.DoFMap(mc, pc, n_ranks, r)
-        tm = mg.TransferMap(mf, df, mc, dc)
+        df, dc = mg.DoFMap(mf, pf, n_ranks, r, cell_begin=cbf), mg.DoFMap(mc, pc, n_ranks, r, cell_begin=cbc)
+        tm = mg.TransferMap(mf, df, mc, dc, local_smoothing=ls)
         tms.append((tm, df))
         assert tm.distributed and tm.n_coarse_cells == dc.n_cells
         pt = tm.partitioner()
@@ -257,6 +266,19 @@ def test_partitioned_transfer_maps_are_consistent(geometry, L, p, kind, n_ranks)
         # every ghost group has a sender
         for j, o in enumerate(pa["ghost_ranks"]):
             assert df.rank in list(tms[o][0].partitioner()["import_ranks"])
+
+
+@pytest.mark.parametrize("policy", [None, "FirstChildPolicy-2.0", "CellWeightPolicy-1.5"])
+@pytest.mark.parametrize("n_ranks", [2, 3, 8])
+@pytest.mark.parametrize("geometry,L,p,kind", [("hypercube", 2, 2, "h"), ("quadrant", 4, 3, "h"), ("quadrant", 3, 4, "p"), ("annulus", 5, 1, "h")])
+def test_partitioned_transfer_maps_are_consistent(geometry, L, p, kind, n_ranks, policy):
+    """several ranks: the coarse cells of a rank may have children on other ranks; the transfer's own fine-side table,
+    weights and ghost/import lists must describe the serial transfer in the global numbering"""
+    seq = mesh_sequence(geometry, L)
+    cbs = _ranges(policy, seq, n_ranks)
+    (mf, pf), (mc, pc) = ((seq[-1], p), (seq[-2], p)) if kind == "h" else ((seq[-1], p), (seq[-1], max(p // 2, 1)))
+    cbf, cbc = (cbs[-1], cbs[-2]) if kind == "h" else (cbs[-1], cbs[-1])
+    _check_partitioned_transfer(mf, pf, mc, pc, cbf, cbc, n_ranks)
 
 
 # ----------------------------------------------------------------------------------------------- local smoothing
@@ -354,19 +376,23 @@ def test_ls_transfer_map(geometry, L, p):
                 np.testing.assert_allclose(uf, f(fine.dof_coordinates()), atol=1e-12)
 
 
+@pytest.mark.parametrize("first_child", [False, True])
 @pytest.mark.parametrize("n_ranks", [2, 3])
 @pytest.mark.parametrize("geometry,L,p", [("quadrant", 4, 2), ("annulus", 6, 1)])
-def test_partitioned_copy_indices_are_consistent(geometry, L, p, n_ranks):
-    """several ranks: the pairs held by the owners of the active DoFs, mapped to global indices, are exactly the serial pairs"""
+def test_partitioned_copy_indices_are_consistent(geometry, L, p, n_ranks, first_child):
+    """several ranks: the pairs held by the owners of the active DoFs, mapped to global indices, are exactly the serial pairs;
+    level cells split evenly, or owned by the owner of their first child (deal.II's level ownership)"""
     mesh = mg.Mesh(geometry, L)
     act = mg.DoFMap(mesh, p)
+    act_begin = mg.partition_sequence("CellWeightPolicy-2.0" if first_child else "DefaultPolicy", [mesh], n_ranks)[0]
     for l in range(mesh.n_global_levels):
         lm = mesh.level_mesh(l)
+        lvl_begin = mg.first_child_boundaries(lm, mesh, act_begin) if first_child else None
         serial = mg.CopyIndices(act, lm, mg.DoFMap(lm, p))
         expect = set(zip(serial.active_idx.tolist(), serial.level_idx.tolist()))
         got = set()
         for r in range(n_ranks):
-            ar, lr = mg.DoFMap(mesh, p, n_ranks, r), mg.DoFMap(lm, p, n_ranks, r)
+            ar, lr = mg.DoFMap(mesh, p, n_ranks, r, cell_begin=act_begin), mg.DoFMap(lm, p, n_ranks, r, cell_begin=lvl_begin)
             ci = mg.CopyIndices(ar, lm, lr, active_mesh=mesh)
             assert ci.distributed and ci.n_owned == lr.n_owned and ci.owned_begin == lr.owned_begin
             assert np.all(ci.active_idx < ar.n_owned)
@@ -376,3 +402,87 @@ def test_partitioned_copy_indices_are_consistent(geometry, L, p, n_ranks):
             assert not (pairs & got)
             got |= pairs
         assert got == expect
+
+
+# ----------------------------------------------------------------------------------------------- partition policies
+def _first_leaf_owner(parents, children, child_begin):
+    """independent restatement: owner of the leaf of `children` whose start corner is the parent's start corner"""
+    pc, cc = parents.cells().astype(np.int64), children.cells().astype(np.int64)
+    lmax = int(cc[:, 0].max())
+    start = {tuple((cc[i, 1:] << (lmax - cc[i, 0])).tolist()): i for i in range(len(cc))}
+    leaf = np.array([start[tuple((c[1:] << (lmax - c[0])).tolist())] for c in pc])
+    return np.searchsorted(np.asarray(child_begin)[1:], leaf, side="right")
+
+
+@pytest.mark.parametrize("n_ranks", [3, 8])
+@pytest.mark.parametrize("geometry,L", [("quadrant", 4), ("annulus", 6), ("hypercube", 3)])
+def test_partition_policies(geometry, L, n_ranks):
+    """PartitionerName policies (multigrid_throughput.cc:2066-2174) on a global-coarsening sequence"""
+    seq = mesh_sequence(geometry, L)
+    nc = np.array([m.n_cells for m in seq])
+    owner = lambda cb, n: np.searchsorted(cb[1:], np.arange(n), side="right")
+
+    d = mg.partition_sequence("DefaultPolicy", seq, n_ranks)
+    for k, m in enumerate(seq):
+        used = max(1, min(n_ranks, nc[k]))                                # fewer cells than ranks: the first ranks only
+        np.testing.assert_array_equal(d[k], (nc[k] * np.minimum(np.arange(n_ranks + 1), used)) // used)
+    np.testing.assert_array_equal(mg.partition_sequence("", seq, n_ranks), d)
+
+    g = mg.partition_sequence("MinimalGranularityPolicy-40", seq, n_ranks)
+    for k in range(len(seq)):
+        used = max(1, min(n_ranks, nc[k] // 40))
+        sizes = np.diff(g[k])
+        assert np.count_nonzero(sizes) == used and np.all(sizes[used:] == 0) and sizes[:used].max() - sizes[:used].min() <= 1
+
+    hang = seq[-1].hanging_cells()
+    np.testing.assert_array_equal(hang, (mg.DoFMap(seq[-1], 1).mask() >> 3) != 0)
+    w = mg.partition_sequence("CellWeightPolicy-2.5", seq, n_ranks)
+    for k, m in enumerate(seq):
+        weights = np.where(m.hanging_cells(), 2.5, 1.0)
+        per_rank = np.bincount(owner(w[k], nc[k]), weights=weights, minlength=n_ranks)
+        assert np.all(np.diff(w[k]) >= 0) and w[k][0] == 0 and w[k][-1] == nc[k]
+        assert per_rank.max() - weights.sum() / n_ranks <= 2.5 + 1e-9     # no rank exceeds its share by more than one cell
+    if hang.any() and n_ranks == 3:                                      # (8 ranks = the 8 octants: symmetric meshes split evenly anyway)
+        assert not np.array_equal(w[-1], d[-1])
+    np.testing.assert_array_equal(mg.partition_sequence("CellWeightPolicy-1.0", seq, n_ranks), d)
+
+    f = mg.partition_sequence("FirstChildPolicy", seq, n_ranks)
+    np.testing.assert_array_equal(f[-1], d[-1])
+    for k in range(len(seq) - 1):
+        np.testing.assert_array_equal(owner(f[k], nc[k]), _first_leaf_owner(seq[k], seq[k + 1], f[k + 1]))
+        np.testing.assert_array_equal(f[k], mg.first_child_boundaries(seq[k], seq[k + 1], f[k + 1]))
+    np.testing.assert_array_equal(mg.partition_sequence("FirstChildPolicy-2.5", seq, n_ranks)[-1], w[-1])
+
+    b = mg.partition_sequence("BalancedGranularityPartitionPolicy", seq, n_ranks)
+    procs = n_ranks
+    np.testing.assert_array_equal(b[-1], d[-1])
+    for k in range(len(seq) - 2, -1, -1):
+        grain = min(200, 8 * nc[k] // procs + 1)                         # multigrid_throughput.cc:397-398
+        procs = max(1, min(n_ranks, nc[k] // grain))
+        assert np.count_nonzero(np.diff(b[k])) == procs
+
+    with pytest.raises(RuntimeError):
+        mg.partition_sequence("NoSuchPolicy", seq, n_ranks)
+
+
+def test_level_cells_live_with_their_first_child():
+    """local smoothing: level owner of a cell = owner of its first child, recursively"""
+    mesh = mg.Mesh("quadrant", 4)
+    act = mg.partition_sequence("DefaultPolicy", [mesh], 3)[0]
+    for l in range(mesh.n_global_levels):
+        lm = mesh.level_mesh(l)
+        cb = mg.first_child_boundaries(lm, mesh, act)
+        np.testing.assert_array_equal(np.searchsorted(cb[1:], np.arange(lm.n_cells), side="right"), _first_leaf_owner(lm, mesh, act))
+
+
+@pytest.mark.parametrize("first_child", [False, True])
+@pytest.mark.parametrize("n_ranks", [2, 3])
+@pytest.mark.parametrize("geometry,L,p", [("quadrant", 4, 2), ("annulus", 6, 1)])
+def test_partitioned_ls_transfer_maps_are_consistent(geometry, L, p, n_ranks, first_child):
+    """MGTransferMatrixFree level transfers on several ranks, level cells split evenly or living with their first child"""
+    mesh = mg.Mesh(geometry, L)
+    act_begin = mg.partition_sequence("DefaultPolicy", [mesh], n_ranks)[0]
+    lms = [mesh.level_mesh(l) for l in range(mesh.n_global_levels)]
+    cbs = [mg.first_child_boundaries(lm, mesh, act_begin) if first_child else None for lm in lms]
+    for l in range(1, len(lms)):
+        _check_partitioned_transfer(lms[l], p, lms[l - 1], p, cbs[l], cbs[l - 1], n_ranks, ls=True)

@@ -33,11 +33,22 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     mg.comm_init(uid[0], rank, world)
     ok = True
-    for geometry, L, p, mg_type, coarse in [("hypercube", 3, 2, "HMG-global", "cg"), ("quadrant", 4, 4, "HMG-global", "cg"),
-                                            ("annulus", 5, 4, "HPMG", "cg_with_chebyshev"), ("quadrant", 3, 4, "PMG", "cg"),
-                                            ("quadrant", 4, 2, "HMG-local", "cg"), ("annulus", 6, 1, "HMG-local", "cg"),
-                                            ("quadrant", 4, 4, "HPMG-local", "cg")]:
-        prob = mg.Problem(params(geometry, L, p, mg_type, coarse), world, rank)
+    cases = [("hypercube", 3, 2, "HMG-global", "cg", "DefaultPolicy"), ("quadrant", 4, 4, "HMG-global", "cg", "DefaultPolicy"),
+             ("annulus", 5, 4, "HPMG", "cg_with_chebyshev", "DefaultPolicy"), ("quadrant", 3, 4, "PMG", "cg", "DefaultPolicy"),
+             ("quadrant", 4, 2, "HMG-local", "cg", "DefaultPolicy"), ("annulus", 6, 1, "HMG-local", "cg", "DefaultPolicy"),
+             ("quadrant", 4, 4, "HPMG-local", "cg", "DefaultPolicy"),
+             # PartitionerName policies (multigrid_throughput.cc:2066-2174): the result must not depend on the partition
+             ("quadrant", 4, 4, "HMG-global", "cg", "FirstChildPolicy"), ("quadrant", 4, 2, "HMG-global", "cg", "CellWeightPolicy-2.5"),
+             ("annulus", 5, 4, "HPMG", "cg", "FirstChildPolicy-2.0"), ("quadrant", 4, 2, "HMG-global", "cg", "MinimalGranularityPolicy-40"),
+             ("quadrant", 4, 2, "HMG-global", "cg", "BalancedGranularityPartitionPolicy"),
+             ("quadrant", 4, 2, "HMG-local", "cg", "CellWeightPolicy-2.0")]
+    only = os.environ.get("MGB_CHECK_ONLY")  # e.g. "Policy": run the cases whose description contains the string
+    for geometry, L, p, mg_type, coarse, policy in cases:
+        if only and only not in f"{geometry} {mg_type} {policy}":
+            continue
+        prm = params(geometry, L, p, mg_type, coarse)
+        prm["PartitionerName"] = policy
+        prob = mg.Problem(prm, world, rank)
         if mg_type.endswith("local"):
             H = OracleHierarchyLS(geometry, L, p, mg_type, 3, coarse)
             H.maps, H.ops = [H.fine_maps], [H.fine_op]  # only the outer operator is compared level-wise below
@@ -74,7 +85,7 @@ def main():
         good = (e_vmult < 1e-12 and e_vc < 1e-11 and e_rhs < 1e-13 and res["n_iterations"] == its == res2["n_iterations"] == res3["n_iterations"]
                 and e_graph < 1e-12)
         ok &= good
-        print(f"[rank {rank}/{world}] {geometry} L={L} p={p} {mg_type}: owned={d.n_owned} ghost={d.n_ghost} vmult={e_vmult:.1e} "
+        print(f"[rank {rank}/{world}] {geometry} L={L} p={p} {mg_type} {policy}: owned={d.n_owned} ghost={d.n_ghost} vmult={e_vmult:.1e} "
               f"vcycle={e_vc:.1e} rhs={e_rhs:.1e} its={res['n_iterations']} (oracle {its}) {'OK' if good else 'FAIL'}", flush=True)
     t = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
