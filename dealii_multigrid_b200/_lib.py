@@ -71,6 +71,11 @@ class OperatorDesc(C.Structure):
     ]
 
 
+class Statistics(C.Structure):
+    _fields_ = [("workload_eff", C.c_double), ("workload_path_max", C.c_double), ("vertical_eff", C.c_double),
+                ("horizontal_eff", C.c_double), ("mem_total", C.c_double), ("verbose", C.c_int32)]
+
+
 class Result(C.Structure):
     _fields_ = [
         ("dim", C.c_int32), ("degree", C.c_int32), ("n_ref_global", C.c_int32), ("n_ref_local", C.c_int32),
@@ -119,6 +124,10 @@ SIGNATURES = {
     "mgb_partition_sequence": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_int64)]),
     "mgb_partition_first_child": (C.c_int, [P, P, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "mgb_mesh_hanging_cells": (C.c_int, [P, C.POINTER(C.c_uint8)]),
+    "mgb_hierarchy_statistics": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(Statistics),
+                                           C.POINTER(C.c_int64)]),
+    "mgb_problem_n_meshes": (C.c_int, [P]),
+    "mgb_problem_statistics": (C.c_int, [P, C.POINTER(Statistics), C.POINTER(C.c_int64)]),
     "mgb_dofmap_view_get": (C.c_int, [P, C.POINTER(DofmapView)]),
     "mgb_dofmap_expand": (C.c_int, [P, C.c_int, c_u32p]),
     "mgb_dofmap_destroy": (None, [P]),

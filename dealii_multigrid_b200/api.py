@@ -175,6 +175,28 @@ def partition_sequence(policy_name, meshes, n_ranks, min_cells_per_rank=1):
     return out
 
 
+_LEVEL_COLUMNS = ("n_cells_min", "n_cells_max", "n_cells_sum", "vertical_local", "vertical_remote", "horizontal_local",
+                  "horizontal_remote")
+
+
+def _statistics_dict(st, per_level):
+    out = {k: getattr(st, k) for k in ("workload_eff", "workload_path_max", "vertical_eff", "horizontal_eff", "mem_total")}
+    out["levels"] = [dict(zip(_LEVEL_COLUMNS, map(int, row))) for row in per_level]
+    return out
+
+
+def hierarchy_statistics(meshes, cell_begin, n_ranks):
+    """MGTools::print_multigrid_statistics (include/mg_tools.h:267-513) of a partitioned hierarchy: meshes coarse -> fine
+    (a coarsening sequence, or the level meshes of local smoothing), cell_begin from partition_sequence"""
+    lib = _lib.load()
+    hs = (C.c_void_p * len(meshes))(*[m._h for m in meshes])
+    cb = np.ascontiguousarray(cell_begin, dtype=np.int64).reshape(len(meshes), n_ranks + 1)
+    st, per = _lib.Statistics(), np.zeros((len(meshes), len(_LEVEL_COLUMNS)), dtype=np.int64)
+    _check(lib.mgb_hierarchy_statistics(hs, len(meshes), n_ranks, cb.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(st),
+                                        per.ctypes.data_as(C.POINTER(C.c_int64))))
+    return _statistics_dict(st, per)
+
+
 def first_child_boundaries(parents, children, child_begin):
     """ownership with the first child (FirstChildPolicy, level cells of local smoothing)"""
     lib = _lib.load()
@@ -593,6 +615,13 @@ class Problem:
 
     def level_degree(self, l):
         return int(self._lib.mgb_problem_level_degree(self._h, l))
+
+    def statistics(self):
+        """workload / vertical / horizontal efficiency of the partitioned hierarchy (the reference's Verbosity columns)"""
+        st = _lib.Statistics()
+        per = np.zeros((int(self._lib.mgb_problem_n_meshes(self._h)), len(_LEVEL_COLUMNS)), dtype=np.int64)
+        _check(self._lib.mgb_problem_statistics(self._h, C.byref(st), per.ctypes.data_as(C.POINTER(C.c_int64))))
+        return _statistics_dict(st, per)
 
     def level_dofmap(self, l):
         return DoFMap(_handle=C.c_void_p(self._lib.mgb_problem_level_dofmap(self._h, l)), _owner=self)

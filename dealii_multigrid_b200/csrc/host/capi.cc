@@ -364,6 +364,42 @@ int mgb_mesh_hanging_cells(const mgb_mesh *m, uint8_t *flags)
     std::copy(f.begin(), f.end(), flags);
   });
 }
+namespace
+{
+  void export_statistics(const HierarchyStatistics &st, mgb_statistics *out, int64_t *per_level)
+  {
+    out->workload_eff      = st.workload_eff;
+    out->workload_path_max = st.workload_path_max;
+    out->vertical_eff      = st.vertical_eff;
+    out->horizontal_eff    = st.horizontal_eff;
+    out->mem_total         = st.mem_total;
+    out->verbose           = 0;
+    if (per_level)
+      for (size_t l = 0; l < st.levels.size(); ++l)
+        {
+          const auto &L = st.levels[l];
+          int64_t    *o = per_level + l * MGB_STATISTICS_LEVEL_VALUES;
+          o[0] = L.n_cells_min, o[1] = L.n_cells_max, o[2] = L.n_cells_sum, o[3] = L.vertical_local, o[4] = L.vertical_remote;
+          o[5] = L.horizontal_local, o[6] = L.horizontal_remote;
+        }
+  }
+} // namespace
+int mgb_hierarchy_statistics(const mgb_mesh *const *meshes, int n_meshes, int n_ranks, const int64_t *cell_begin, mgb_statistics *out,
+                             int64_t *per_level)
+{
+  return guarded([&] {
+    std::vector<const Mesh *>         ms;
+    std::vector<std::vector<int64_t>> cb;
+    for (int i = 0; i < n_meshes; ++i)
+      {
+        ms.push_back(&meshes[i]->m);
+        cb.emplace_back(cell_begin + size_t(i) * (n_ranks + 1), cell_begin + size_t(i + 1) * (n_ranks + 1));
+        if (cb.back().front() != 0 || cb.back().back() != (int64_t)meshes[i]->m.cells.size())
+          throw std::runtime_error("mgb_hierarchy_statistics: cell_begin does not span the mesh");
+      }
+    export_statistics(hierarchy_statistics(ms, cb, n_ranks), out, per_level);
+  });
+}
 int mgb_dofmap_view_get(const mgb_dofmap *h, mgb_dofmap_view *v)
 {
   return guarded([&] {
@@ -1006,6 +1042,14 @@ const mgb_transfer *mgb_problem_level_transfer(const mgb_problem *p, int l)
 }
 const mgb_operator *mgb_problem_fine_operator(const mgb_problem *p) { return p->fine_op.get(); }
 const mgb_dofmap   *mgb_problem_fine_dofmap(const mgb_problem *p) { return p->fine_dofmap.get(); }
+int mgb_problem_n_meshes(const mgb_problem *p) { return (int)p->p->statistics_levels(); }
+int mgb_problem_statistics(const mgb_problem *p, mgb_statistics *out, int64_t *per_level)
+{
+  return guarded([&] {
+    export_statistics(p->p->statistics(), out, per_level);
+    out->verbose = p->p->prm.verbose ? 1 : 0;
+  });
+}
 mgb_vector         *mgb_problem_rhs(mgb_problem *p) { return p->rhs.get(); }
 mgb_vector         *mgb_problem_solution(mgb_problem *p) { return p->solution.get(); }
 

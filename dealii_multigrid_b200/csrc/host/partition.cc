@@ -61,7 +61,8 @@ namespace mgb
             leaf    = children.locate(level, x, y, z, rel);
             if (rel <= 0)
               break;
-            ++level; // subdivided further: descend into the first child
+            if (++level > 30) // subdivided further: descend into the first child
+              throw std::runtime_error("first_child_boundaries: the child mesh does not cover the parent mesh");
             x *= 2, y *= 2, z *= 2;
           }
         if (leaf < 0 || leaf < last)
@@ -167,5 +168,140 @@ namespace mgb
           }
       }
     return out;
+  }
+
+  namespace
+  {
+    inline int owner_of(const std::vector<int64_t> &begin, int64_t cell)
+    {
+      return int(std::upper_bound(begin.begin() + 1, begin.end(), cell) - (begin.begin() + 1));
+    }
+
+    // leaves of `mesh` whose closure touches the closure of cell c (face, edge or corner neighbours, hanging or not)
+    template <typename F>
+    void for_each_touching_cell(const Mesh &mesh, const Cell &c, F &&f)
+    {
+      const int64_t N = int64_t(1) << c.level;
+      for (int dz = -1; dz <= 1; ++dz)
+        for (int dy = -1; dy <= 1; ++dy)
+          for (int dx = -1; dx <= 1; ++dx)
+            {
+              if (dx == 0 && dy == 0 && dz == 0)
+                continue;
+              const int64_t n[3] = {int64_t(c.x) + dx, int64_t(c.y) + dy, int64_t(c.z) + dz};
+              if (n[0] < 0 || n[1] < 0 || n[2] < 0 || n[0] >= N || n[1] >= N || n[2] >= N)
+                continue;
+              int           rel = 0;
+              const int64_t j   = mesh.locate(c.level, uint32_t(n[0]), uint32_t(n[1]), uint32_t(n[2]), rel);
+              if (j >= 0)
+                {
+                  f(j); // same-level or coarser neighbour
+                  continue;
+                }
+              // finer neighbours (one level, 2:1 balance): the children of the region on the side facing c
+              const int d[3] = {dx, dy, dz};
+              for (int ch = 0; ch < 8; ++ch)
+                {
+                  bool faces = true;
+                  for (int a = 0; a < 3; ++a)
+                    {
+                      const int bit = (ch >> a) & 1;
+                      if ((d[a] == 1 && bit != 0) || (d[a] == -1 && bit != 1))
+                        faces = false;
+                    }
+                  if (!faces)
+                    continue;
+                  const int64_t k = mesh.leaf(c.level + 1, uint32_t(2 * n[0] + (ch & 1)), uint32_t(2 * n[1] + ((ch >> 1) & 1)),
+                                              uint32_t(2 * n[2] + ((ch >> 2) & 1)));
+                  if (k >= 0)
+                    f(k);
+                }
+            }
+    }
+  } // namespace
+
+  HierarchyStatistics hierarchy_statistics(const std::vector<const Mesh *> &meshes, const std::vector<std::vector<int64_t>> &cell_begin,
+                                           int n_ranks)
+  {
+    HierarchyStatistics st;
+    const size_t        nl = meshes.size();
+    st.levels.resize(nl);
+    if (cell_begin.size() != nl)
+      throw std::runtime_error("hierarchy_statistics: one partition per mesh required");
+    // workload (mg_tools.h:9-36, 277-300)
+    int64_t sum_all = 0, sum_max = 0;
+    for (size_t l = 0; l < nl; ++l)
+      {
+        auto &L       = st.levels[l];
+        L.n_cells_min = INT64_MAX;
+        for (int r = 0; r < n_ranks; ++r)
+          {
+            const int64_t n = cell_begin[l][r + 1] - cell_begin[l][r];
+            L.n_cells_min   = std::min(L.n_cells_min, n);
+            L.n_cells_max   = std::max(L.n_cells_max, n);
+            L.n_cells_sum += n;
+          }
+        sum_all += L.n_cells_sum;
+        sum_max += L.n_cells_max;
+        st.mem_total += double(meshes[l]->cells.size()) * (sizeof(Cell) + 16.0); // leaves + their hash index entries
+      }
+    st.workload_path_max = double(sum_max);
+    st.workload_eff      = sum_max > 0 ? (double(sum_all) / n_ranks) / double(sum_max) : 1.0;
+    // vertical communication: for every cell of level l with children on level l+1, is the child on the same rank
+    int64_t v_local = 0, v_remote = 0;
+    for (size_t l = 0; l + 1 < nl; ++l)
+      {
+        const Mesh &coarse = *meshes[l], &fine = *meshes[l + 1];
+        auto       &L      = st.levels[l + 1];
+        const int   fine_max = fine.max_level();
+        for (int64_t i = 0; i < (int64_t)coarse.cells.size(); ++i)
+          {
+            const Cell &c = coarse.cells[i];
+            if (c.level == fine_max)
+              continue;
+            const int r = owner_of(cell_begin[l], i);
+            for (int ch = 0; ch < 8; ++ch)
+              {
+                const int64_t k = fine.leaf(c.level + 1, 2 * c.x + (ch & 1), 2 * c.y + ((ch >> 1) & 1), 2 * c.z + ((ch >> 2) & 1));
+                if (k < 0)
+                  continue;
+                (owner_of(cell_begin[l + 1], k) == r ? L.vertical_local : L.vertical_remote) += 1;
+              }
+          }
+        v_local += L.vertical_local;
+        v_remote += L.vertical_remote;
+      }
+    st.vertical_eff = (v_local + v_remote) > 0 ? double(v_local) / double(v_local + v_remote) : 1.0;
+    // horizontal communication: owned cells and ghost cells (cells of other ranks touching an owned cell)
+    int64_t h_local = 0, h_remote = 0;
+    for (size_t l = 0; l < nl; ++l)
+      {
+        const Mesh &m = *meshes[l];
+        auto       &L = st.levels[l];
+        L.horizontal_local = (int64_t)m.cells.size();
+        if (n_ranks > 1)
+          for (int64_t j = 0; j < (int64_t)m.cells.size(); ++j)
+            {
+              // cell j is a ghost of every other rank that owns one of its neighbours
+              const int own = owner_of(cell_begin[l], j);
+              int       seen[32];
+              int       n_seen = 0;
+              for_each_touching_cell(m, m.cells[j], [&](int64_t k) {
+                const int q = owner_of(cell_begin[l], k);
+                if (q == own)
+                  return;
+                for (int s = 0; s < n_seen; ++s)
+                  if (seen[s] == q)
+                    return;
+                if (n_seen < 32)
+                  seen[n_seen++] = q;
+              });
+              L.horizontal_remote += n_seen;
+            }
+        h_local += L.horizontal_local;
+        h_remote += L.horizontal_remote;
+      }
+    st.horizontal_eff = (h_local + h_remote) > 0 ? double(h_local + h_remote / 2) / double(h_local + h_remote) : 1.0;
+    return st;
   }
 } // namespace mgb

@@ -53,3 +53,25 @@ namespace mgb
     std::vector<std::vector<int64_t>> sequence(const std::vector<Mesh> &meshes, int n_ranks, int64_t floor_min_cells) const;
   };
 } // namespace mgb
+
+namespace mgb
+{
+  // MGTools::print_multigrid_statistics (include/mg_tools.h:267-513): workload, vertical and horizontal communication
+  // efficiency of a partitioned hierarchy.  The partition is replicated knowledge here (Morton ranges), so the numbers
+  // need no communication.
+  struct HierarchyStatistics
+  {
+    double workload_eff = 1, workload_path_max = 0, vertical_eff = 1, horizontal_eff = 1, mem_total = 0;
+    struct Level
+    {
+      int64_t n_cells_min = 0, n_cells_max = 0, n_cells_sum = 0;
+      int64_t vertical_local = 0, vertical_remote = 0;     // children of the cells of the level below, summed over ranks
+      int64_t horizontal_local = 0, horizontal_remote = 0; // owned / ghost cells, summed over ranks
+    };
+    std::vector<Level> levels;
+  };
+  // meshes: coarse -> fine.  Global coarsening: the coarsening sequence (mg_tools.h:64-81, 117-191, 214-233); local
+  // smoothing: the level meshes of one refinement tree (mg_tools.h:39-62, 83-114, 193-212).
+  HierarchyStatistics hierarchy_statistics(const std::vector<const Mesh *> &meshes, const std::vector<std::vector<int64_t>> &cell_begin,
+                                           int n_ranks);
+} // namespace mgb

@@ -737,6 +737,16 @@ namespace mgb
         return transfer.transfers.at(l - transfer.min_level).get();
       }
       const DoFMap     &fine_dofmap() const override { return *fine_dofs; }
+      size_t statistics_levels() const override { return local_smoothing ? meshes.size() - 1 : meshes.size(); }
+      HierarchyStatistics statistics() const override
+      {
+        // global coarsening: the coarsening sequence; local smoothing: the level meshes (not the active mesh)
+        const size_t              n = local_smoothing ? meshes.size() - 1 : meshes.size();
+        std::vector<const Mesh *> ms;
+        for (size_t i = 0; i < n; ++i)
+          ms.push_back(&meshes[i]);
+        return hierarchy_statistics(ms, std::vector<std::vector<int64_t>>(mesh_begin.begin(), mesh_begin.begin() + n), n_ranks);
+      }
       OperatorT<double> &fine_operator() override { return *fine_op; }
       DVec<double>     &rhs() override { return rhs_; }
       DVec<double>     &solution() override { return solution_; }

@@ -1,6 +1,7 @@
 // JSON-driven problem setup and solve: the equivalent of run<3,1,double,LevelNumber>() +
 // solve_with_global_coarsening / solve_with_local_smoothing + mg_solve of multigrid_throughput.cc.
 #pragma once
+#include "partition.h"
 #include "solver.h"
 
 #include <map>
@@ -83,6 +84,9 @@ namespace mgb
     virtual void           vcycle(DVec<double> &dst, const DVec<double> &src) = 0;
     virtual Result         solve_once(bool with_timers)     = 0;
     virtual Result         run(unsigned n_repetitions)      = 0;
+    // MGTools::print_multigrid_statistics of the partitioned hierarchy (ref :1659, :1866)
+    virtual HierarchyStatistics statistics() const          = 0;
+    virtual size_t         statistics_levels() const        = 0; // meshes the statistics cover
     RunParameters          prm;
   };
 

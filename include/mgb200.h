@@ -277,6 +277,21 @@ typedef struct
   int64_t  coarse_iterations; /* total coarse-grid CG iterations of the reported solve */
 } mgb_result;
 
+/* MGTools::print_multigrid_statistics (include/mg_tools.h:267-513), the columns the reference appends with Verbosity=true
+ * (multigrid_throughput.cc:1657-1665, 1863-1872).  mem_total counts the stand-in octree, not deal.II's triangulations. */
+typedef struct
+{
+  double  workload_eff, workload_path_max, vertical_eff, horizontal_eff, mem_total;
+  int32_t verbose; /* mgb_problem_statistics: the Verbosity key of the input (the reference adds the columns only then) */
+} mgb_statistics;
+/* per level (coarse -> fine), 7 values: n_cells_min, n_cells_max, n_cells_sum, vertical local / remote children,
+ * horizontal owned / ghost cells (sums over ranks) */
+#define MGB_STATISTICS_LEVEL_VALUES 7
+/* meshes: a coarsening sequence (global coarsening) or the level meshes of one tree (local smoothing), coarse -> fine;
+ * cell_begin: n_meshes*(n_ranks+1) Morton offsets (mgb_partition_sequence / mgb_partition_first_child) */
+int  mgb_hierarchy_statistics(const mgb_mesh *const *meshes, int n_meshes, int n_ranks, const int64_t *cell_begin, mgb_statistics *out,
+                              int64_t *per_level /* n_meshes*MGB_STATISTICS_LEVEL_VALUES or NULL */);
+
 int  mgb_problem_create(const char *json_text, int n_ranks, int rank, mgb_problem **out);
 void mgb_problem_destroy(mgb_problem *p);
 int  mgb_problem_n_levels(const mgb_problem *p);
@@ -301,6 +316,9 @@ int  mgb_problem_solve_once(mgb_problem *p, int with_stage_timers, mgb_result *r
 int  mgb_problem_solve_host(mgb_problem *p, const double *rhs_host, double *solution_host, mgb_result *result);
 /* the reference's protocol: 1 warm-up + n_repetitions timed solves, best one reported (:1140-1283) */
 int  mgb_problem_run(mgb_problem *p, int n_repetitions, mgb_result *result);
+/* statistics of the problem's partitioned hierarchy; per_level sized mgb_problem_n_meshes()*MGB_STATISTICS_LEVEL_VALUES or NULL */
+int  mgb_problem_n_meshes(const mgb_problem *p);
+int  mgb_problem_statistics(const mgb_problem *p, mgb_statistics *out, int64_t *per_level);
 
 #ifdef __cplusplus
 }

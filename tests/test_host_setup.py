@@ -486,3 +486,73 @@ def test_partitioned_ls_transfer_maps_are_consistent(geometry, L, p, n_ranks, fi
     cbs = [mg.first_child_boundaries(lm, mesh, act_begin) if first_child else None for lm in lms]
     for l in range(1, len(lms)):
         _check_partitioned_transfer(lms[l], p, lms[l - 1], p, cbs[l], cbs[l - 1], n_ranks, ls=True)
+
+
+def _boxes(mesh):
+    c = mesh.cells().astype(np.int64)
+    lmax = int(c[:, 0].max())
+    lo = c[:, 1:] << (lmax - c[:, 0])[:, None]
+    return lo, lo + (1 << (lmax - c[:, 0]))[:, None], lmax
+
+
+def _brute_statistics(meshes, cbs, n_ranks):
+    """independent restatement of include/mg_tools.h:9-36, 117-191, 214-233, 267-470 with O(n^2) neighbour tests"""
+    owners = [np.searchsorted(np.asarray(cb)[1:], np.arange(m.n_cells), side="right") for m, cb in zip(meshes, cbs)]
+    counts = np.array([np.bincount(o, minlength=n_ranks) for o in owners])
+    out = {"workload_path_max": counts.max(axis=1).sum(), "workload_eff": counts.sum() / n_ranks / counts.max(axis=1).sum()}
+    v_local = v_remote = 0
+    for k in range(len(meshes) - 1):
+        cc, fc = meshes[k].cells().astype(np.int64), meshes[k + 1].cells().astype(np.int64)
+        parent = {tuple(c.tolist()): i for i, c in enumerate(cc)}
+        for j, c in enumerate(fc):
+            i = parent.get((c[0] - 1, c[1] >> 1, c[2] >> 1, c[3] >> 1)) if c[0] > 0 else None
+            if i is not None:
+                if owners[k][i] == owners[k + 1][j]:
+                    v_local += 1
+                else:
+                    v_remote += 1
+    out["vertical_eff"] = v_local / (v_local + v_remote) if v_local + v_remote else 1.0
+    h_local = h_remote = 0
+    for m, o in zip(meshes, owners):
+        lo, hi, _ = _boxes(m)
+        touch = np.all((lo[:, None, :] <= hi[None, :, :]) & (lo[None, :, :] <= hi[:, None, :]), axis=2)
+        h_local += m.n_cells
+        for r in range(n_ranks):
+            mine = o == r
+            h_remote += int(np.count_nonzero(touch[mine].any(axis=0) & ~mine)) if mine.any() else 0
+    out["horizontal_eff"] = (h_local + h_remote // 2) / (h_local + h_remote)
+    out["h_remote"], out["v_remote"] = h_remote, v_remote
+    return out
+
+
+@pytest.mark.parametrize("policy", ["DefaultPolicy", "FirstChildPolicy", "CellWeightPolicy-2.0"])
+@pytest.mark.parametrize("n_ranks", [1, 3, 8])
+@pytest.mark.parametrize("geometry,L", [("quadrant", 3), ("circle", 4)])
+def test_hierarchy_statistics_global_coarsening(geometry, L, n_ranks, policy):
+    """MGTools::print_multigrid_statistics on a coarsening sequence against a brute-force restatement"""
+    seq = mesh_sequence(geometry, L)
+    cbs = mg.partition_sequence(policy, seq, n_ranks)
+    st, ref_ = mg.hierarchy_statistics(seq, cbs, n_ranks), _brute_statistics(seq, cbs, n_ranks)
+    for k in ("workload_eff", "workload_path_max", "vertical_eff", "horizontal_eff"):
+        assert st[k] == pytest.approx(ref_[k], rel=1e-14), k
+    assert sum(l["horizontal_remote"] for l in st["levels"]) == ref_["h_remote"]
+    assert sum(l["vertical_remote"] for l in st["levels"]) == ref_["v_remote"]
+    assert [l["n_cells_sum"] for l in st["levels"]] == [m.n_cells for m in seq]
+    if n_ranks == 1:
+        assert st["workload_eff"] == st["vertical_eff"] == st["horizontal_eff"] == 1.0
+    if policy == "FirstChildPolicy" and n_ranks > 1:
+        # a coarse cell lives with its first child: at least one child of every refined cell is local
+        assert st["vertical_eff"] >= 1.0 / 8.0
+
+
+@pytest.mark.parametrize("n_ranks", [2, 5])
+def test_hierarchy_statistics_local_smoothing(n_ranks):
+    """the same for the level meshes of local smoothing with deal.II's level ownership"""
+    mesh = mg.Mesh("quadrant", 4)
+    act = mg.partition_sequence("DefaultPolicy", [mesh], n_ranks)[0]
+    lms = [mesh.level_mesh(l) for l in range(mesh.n_global_levels)]
+    cbs = [mg.first_child_boundaries(lm, mesh, act) for lm in lms]
+    st, ref_ = mg.hierarchy_statistics(lms, cbs, n_ranks), _brute_statistics(lms, cbs, n_ranks)
+    for k in ("workload_eff", "workload_path_max", "vertical_eff", "horizontal_eff"):
+        assert st[k] == pytest.approx(ref_[k], rel=1e-14), k
+    assert st["workload_eff"] < 1.0   # local smoothing: the refined region's owners carry the fine levels alone
