@@ -169,6 +169,7 @@ SIGNATURES = {
     "mgb_operator_vmult_interface_down": (C.c_int, [P, P, P]),
     "mgb_operator_vmult_interface_up": (C.c_int, [P, P, P]),
     "mgb_operator_compute_inverse_diagonal": (C.c_int, [P, P]),
+    "mgb_operator_set_cell_vertices": (C.c_int, [P, c_f64p, C.c_int64]),
     "mgb_chebyshev_create": (C.c_int, [P, C.c_int, C.c_double, C.c_uint, PP]),
     "mgb_chebyshev_destroy": (None, [P]),
     "mgb_chebyshev_vmult": (C.c_int, [P, P, P]),

@@ -530,6 +530,14 @@ class Operator:
     def compute_inverse_diagonal(self, diag):
         _check(self._lib.mgb_operator_compute_inverse_diagonal(self._h, diag._h))
 
+    def set_cell_vertices(self, xyz):
+        """general (non-Cartesian) cells: (n_cells, 8, 3) vertex coordinates, vertices lexicographic with x fastest, trilinear
+        geometry (MappingQ1); every later cell loop evaluates the metric at the Gauss points from them"""
+        a = np.ascontiguousarray(xyz, dtype=np.float64)
+        if a.ndim != 3 or a.shape[1:] != (8, 3):
+            raise ValueError("xyz must have shape (n_cells, 8, 3)")
+        _check(self._lib.mgb_operator_set_cell_vertices(self._h, a.ctypes.data_as(_lib.c_f64p), a.shape[0]))
+
     def __del__(self):
         if getattr(self, "_h", None) and not self._borrowed:
             self._lib.mgb_operator_destroy(self._h)

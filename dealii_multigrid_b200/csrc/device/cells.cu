@@ -1,6 +1,7 @@
 // Translation unit of all cell-wise kernels (they share the constant-memory 1-D matrices).
 #include "../host/fe1d.h"
 #include "operator.cuh"
+#include "operator_q1.cuh"
 #include "transfer.cuh"
 
 #include <mutex>
@@ -40,6 +41,18 @@ namespace mgb
             hf.lam2[i * MAXN + j] = (float)(fe.lambda[i] + fe.lambda[j]);
           }
       }
+    FEConstQ hq{};
+    for (int q = 0; q < fe.n; ++q)
+      {
+        hq.xq[q] = fe.xq[q];
+        hq.wq[q] = fe.wq[q];
+        for (int i = 0; i < fe.n; ++i)
+          {
+            hq.Bq[q * MAXN + i] = fe.Bq[q * fe.n + i];
+            hq.Dq[q * MAXN + i] = fe.Dq[q * fe.n + i];
+          }
+      }
+    MGB_CUDA(cudaMemcpyToSymbol(c_feq, &hq, sizeof(FEConstQ), sizeof(FEConstQ) * degree));
     MGB_CUDA(cudaMemcpyToSymbol(c_fe, &h, sizeof(FEConst), sizeof(FEConst) * degree));
     MGB_CUDA(cudaMemcpyToSymbol(c_fef, &hf, sizeof(FEConstF), sizeof(FEConstF) * degree));
     done[degree] = true;
@@ -60,10 +73,20 @@ namespace mgb
   template <typename T>
   void cell_laplace_apply(const CellData &cd, const T *src, T *dst, const uint32_t *cell_list, long long n_list, cudaStream_t s)
   {
+    if (cd.vertices)
+      {
+        DISPATCH_DEGREE(cd.degree, (launch_q1<P, T, 0>(cd, src, dst, cell_list, n_list, s)));
+        return;
+      }
     DISPATCH_DEGREE(cd.degree, (launch_apply<P, T>(cd, src, dst, cell_list, n_list, s)));
   }
   template <typename T> void cell_laplace_diagonal(const CellData &cd, T *diag, cudaStream_t s)
   {
+    if (cd.vertices)
+      {
+        DISPATCH_DEGREE(cd.degree, (launch_q1<P, T, 1>(cd, (const T *)nullptr, diag, nullptr, 0, s)));
+        return;
+      }
     DISPATCH_DEGREE(cd.degree, (launch_diagonal<P, T>(cd, diag, s)));
   }
   template <typename T> void transfer_prolongate_add(const TransferData &td, T *dst_fine, const T *src_coarse, cudaStream_t s)

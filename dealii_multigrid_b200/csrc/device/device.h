@@ -90,6 +90,10 @@ namespace mgb
     const uint8_t  *level      = nullptr; // n_cells refinement levels; h = root_length / 2^level
     double          root_length = 2.0;
     int             any_hanging = 0;
+    // general geometry (MappingQ1): n_cells*8*3 vertex coordinates, vertices lexicographic (x fastest); null = the cells
+    // are axis-aligned cubes of side root_length / 2^level
+    const double   *vertices    = nullptr;
+    double          scale       = 1.0; // general geometry: dst += scale * A src (the Cartesian kernel folds it into root_length)
   };
   // dst += A_cells src   (scatter-add with FP atomics); cell_list (optional) restricts to a subset of cells
   template <typename T>

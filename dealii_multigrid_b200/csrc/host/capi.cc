@@ -870,6 +870,20 @@ int mgb_operator_compute_inverse_diagonal(const mgb_operator *op, mgb_vector *di
   });
 }
 
+int mgb_operator_set_cell_vertices(mgb_operator *op, const double *xyz, int64_t n_cells)
+{
+  return guarded([&] {
+    const long long have = op->type == MGB_DOUBLE ? op->pd->cell_data().n_cells : op->pf->cell_data().n_cells;
+    if (n_cells != have)
+      throw std::runtime_error("mgb_operator_set_cell_vertices: the operator has " + std::to_string(have) + " cells, got " +
+                               std::to_string((long long)n_cells));
+    if (op->type == MGB_DOUBLE)
+      op->pd->set_cell_vertices(xyz);
+    else
+      op->pf->set_cell_vertices(xyz);
+  });
+}
+
 // ---- Chebyshev
 int mgb_chebyshev_create(const mgb_operator *op, int degree, double smoothing_range, unsigned eig_its, mgb_chebyshev **out)
 {

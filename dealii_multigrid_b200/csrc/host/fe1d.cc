@@ -123,8 +123,15 @@ namespace mgb
     , n(degree_ + 1)
   {
     nodes = gauss_lobatto_nodes(n);
-    std::vector<double> xq, wq;
     gauss_rule(n, xq, wq);
+    Bq.assign(n * n, 0.0);
+    Dq.assign(n * n, 0.0);
+    for (int q = 0; q < n; ++q)
+      for (int i = 0; i < n; ++i)
+        {
+          Bq[q * n + i] = lagrange_value(nodes, i, xq[q]);
+          Dq[q * n + i] = lagrange_derivative(xq, i, xq[q]);
+        }
     M.assign(n * n, 0.0);
     K.assign(n * n, 0.0);
     for (int i = 0; i < n; ++i)

@@ -31,6 +31,10 @@ namespace mgb
     std::vector<double> M, K;        // n*n row-major
     std::vector<double> S[2];        // n*n row-major, S[c][i*n+j] = l_j(c/2 + x_i/2)
     std::vector<double> Ph;          // (2p+1)*n row-major
+    // general (non-Cartesian) cells: evaluation at the Gauss points in collocation form
+    std::vector<double> xq, wq;      // Gauss(n) points / weights on [0,1]
+    std::vector<double> Bq;          // n*n, Bq[q*n+i] = l_i(x_q): nodal values -> values at the Gauss points
+    std::vector<double> Dq;          // n*n, Dq[q*n+r] = derivative at x_q of the r-th Lagrange polynomial ON the Gauss points
     // fast diagonalisation of the pencil (K, M):  K = Tm^T diag(lambda) Tm,  M = Tm^T Tm, so that
     //   A_e = h (Tm x Tm x Tm)^T diag(lambda_i + lambda_j + lambda_k) (Tm x Tm x Tm)
     // Rows of Tm are the modes; the first (n+1)/2 rows are symmetric in the node index, the remaining

@@ -5,6 +5,7 @@
 #include "comm.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 
 namespace mgb
@@ -318,6 +319,7 @@ namespace mgb
     Context &c  = ctx();
     CellData cd = cd_;
     cd.root_length *= alpha; // the cell matrices are linear in h = root_length / 2^level
+    cd.scale = alpha;
     const bool overlap = !edge_only && !c.prof_enabled && boundary_cells_.n > 0 && interior_cells_.n > 0 && c.overlap_ready();
     if (overlap)
       {
@@ -359,6 +361,17 @@ namespace mgb
       }
     dst.compress_add();
     src.zero_out_ghost_values();
+  }
+
+  template <typename T> void OperatorT<T>::set_cell_vertices(const double *xyz)
+  {
+    if (!xyz)
+      throw std::runtime_error("Operator::set_cell_vertices: null pointer");
+    for (size_t i = 0; i < size_t(cd_.n_cells) * 24; ++i)
+      if (!std::isfinite(xyz[i]))
+        throw std::runtime_error("Operator::set_cell_vertices: non-finite coordinate");
+    vertices_.upload(xyz, size_t(cd_.n_cells) * 24);
+    cd_.vertices = vertices_.ptr;
   }
 
   template <typename T> void OperatorT<T>::vmult(DVec<T> &dst, const DVec<T> &src) const

@@ -396,6 +396,9 @@ namespace mgb
     void      residual_interface_down(DVec<T> &dst, const DVec<T> &b, const DVec<T> &src) const;
     void      vmult_interface_up(DVec<T> &dst, const DVec<T> &src) const;   // :203-226
     void      compute_inverse_diagonal(DVec<T> &diag) const;                // :228-242
+    // general (non-Cartesian) geometry: 8 vertices per cell (lexicographic, x fastest), trilinear map (MappingQ1); the
+    // cell loops then run the quadrature-point kernel (device/operator_q1.cuh) instead of the Cartesian one
+    void      set_cell_vertices(const double *xyz /* n_cells*8*3 */);
     const std::shared_ptr<DevicePartitioner> &partitioner() const { return part_; }
     int       degree() const { return cd_.degree; }
     const CellData &cell_data() const { return cd_; }
@@ -408,6 +411,7 @@ namespace mgb
     DeviceBuffer<uint32_t>             etab_, ctab_;
     DeviceBuffer<uint16_t>             mask_;
     DeviceBuffer<uint8_t>              level_;
+    DeviceBuffer<double>               vertices_;
     DeviceBuffer<uint32_t>             constrained_, edge_, edge_cells_;
     // several ranks: cells that read ghost entries (boundary) and the others (interior), for overlapping the exchange
     DeviceBuffer<uint32_t>             boundary_cells_, interior_cells_;

@@ -250,6 +250,11 @@ int  mgb_operator_tvmult(const mgb_operator *op, mgb_vector *dst, const mgb_vect
 int  mgb_operator_vmult_interface_down(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
 int  mgb_operator_vmult_interface_up(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
 int  mgb_operator_compute_inverse_diagonal(const mgb_operator *op, mgb_vector *diag);
+/* General (non-Cartesian) cells -- what MatrixFree does for a mapping that is not Cartesian (include/operator.h:37-42 asks
+ * for update_gradients; the reference's own meshes are all axis-aligned cubes): 8 vertices per cell, lexicographic with x
+ * fastest, trilinear geometry (MappingQ1).  All subsequent cell loops (vmult, interface operators, diagonal) evaluate
+ * the metric terms at the Gauss points from these vertices.  Call before compute_inverse_diagonal / smoother setup. */
+int  mgb_operator_set_cell_vertices(mgb_operator *op, const double *xyz /* n_cells*8*3 */, int64_t n_cells /* checked */);
 
 /* ---- Chebyshev smoother ---------------------------------------------------------------------------- */
 int  mgb_chebyshev_create(const mgb_operator *op, int degree, double smoothing_range, unsigned eig_cg_n_iterations,

@@ -158,6 +158,71 @@ def element_matrix_reference(fe):
     return dx.T @ (W[:, None] * dx) + dy.T @ (W[:, None] * dy) + dz.T @ (W[:, None] * dz)
 
 
+def cell_vertices(maps, deformation=None):
+    """(n_cells, 8, 3) vertex coordinates of the cells (vertices lexicographic, x fastest), optionally moved by
+    deformation(xyz) -> xyz (applied to the vertices; the geometry inside a cell stays trilinear, MappingQ1)"""
+    corner = np.array([[(v >> d) & 1 for d in range(3)] for v in range(8)], dtype=float)
+    origin = -1.0 + maps.h[:, None] * maps.cell_xyz
+    xyz = origin[:, None, :] + maps.h[:, None, None] * corner[None, :, :]
+    return xyz if deformation is None else deformation(xyz.reshape(-1, 3)).reshape(-1, 8, 3)
+
+
+def element_matrices_mapped(fe, vertices):
+    """dense Laplace element matrices (n_cells, n^3, n^3) of trilinearly mapped hexahedra by Gauss quadrature:
+    A_ij = sum_q w_q det J_q (J_q^-T grad phi_i) . (J_q^-T grad phi_j) -- what FEEvaluation computes with a general
+    MatrixFree mapping (include/operator.h:450-493), written with dense reference-gradient matrices instead of sweeps"""
+    B, G, w = fe.B, fe.G, fe.wq
+    n = fe.n
+    xq = fe.xq
+    W = np.einsum("a,b,c->abc", w, w, w).ravel()                                   # quadrature point (c,b,a), a fastest
+    d = [np.einsum("ck,bj,ai->cbakji", *m).reshape(n ** 3, n ** 3) for m in ((B, B, G), (B, G, B), (G, B, B))]
+    Q = np.stack(np.meshgrid(xq, xq, xq, indexing="ij"), axis=-1).transpose(2, 1, 0, 3).reshape(n ** 3, 3)
+    # derivatives of the 8 trilinear vertex functions at the quadrature points: (nq, 8, 3)
+    dN = np.zeros((n ** 3, 8, 3))
+    for v in range(8):
+        c = [(v >> a) & 1 for a in range(3)]
+        val = [Q[:, a] if c[a] else 1.0 - Q[:, a] for a in range(3)]
+        der = [1.0 if c[a] else -1.0 for a in range(3)]
+        dN[:, v, 0] = der[0] * val[1] * val[2]
+        dN[:, v, 1] = val[0] * der[1] * val[2]
+        dN[:, v, 2] = val[0] * val[1] * der[2]
+    vertices = np.asarray(vertices, dtype=float)
+    out = np.zeros((len(vertices), n ** 3, n ** 3))
+    for c, X in enumerate(vertices):
+        J = np.einsum("vc,qvd->qcd", X, dN)                                         # J[q, c, d] = d x_c / d xi_d
+        Jinv = np.linalg.inv(J)
+        det = np.linalg.det(J)
+        if np.any(det <= 0):
+            raise ValueError("inverted cell")
+        M = np.einsum("q,qdc,qec->qde", W * det, Jinv, Jinv)                        # w det J^-1 J^-T
+        for a in range(3):
+            for b in range(3):
+                out[c] += d[a].T @ (M[:, a, b][:, None] * d[b])
+    return out
+
+
+def assemble_matrix_mapped(maps, vertices, identity_rows=True):
+    """scipy CSR of the constrained operator on mapped cells (cf. assemble_matrix)"""
+    Ae = element_matrices_mapped(maps.fe, vertices)
+    n3 = maps.fe.n ** 3
+    for m in np.unique(maps.mask):
+        if (m >> 3) != 0:
+            C = maps.C(m)
+            sel = maps.mask == m
+            Ae[sel] = C.T[None] @ Ae[sel] @ C[None]
+    keep = ~maps.eval_flag
+    blk = Ae * (keep[:, :, None] & keep[:, None, :])
+    rows = np.repeat(maps.eval_idx, n3, axis=1).ravel()
+    cols = np.tile(maps.eval_idx, (1, n3)).ravel()
+    A = sp.coo_matrix((blk.ravel(), (rows, cols)), shape=(maps.n_dofs, maps.n_dofs)).tocsr()
+    if identity_rows:
+        dd = np.zeros(maps.n_dofs)
+        dd[maps.constrained] = 1.0
+        A = A + sp.diags(dd)
+    A.eliminate_zeros()
+    return A
+
+
 def assemble_matrix(maps, identity_rows=True):
     """scipy CSR of the constrained operator: sum_e C_e^T (h A_ref) C_e on unconstrained DoFs (+ identity
     rows on constrained DoFs as Operator::vmult adds them, include/operator.h:170-172)"""
@@ -266,6 +331,29 @@ class Operator:
             contrib = mp.h[c][:, None] * np.diag(Ae)[None, :]
             np.add.at(diag, idx[~flag], contrib[~flag])
         diag[self.edge] = 0.0
+        return np.where(np.abs(diag) > 1.0e-10, 1.0 / np.where(diag == 0, 1.0, diag), 1.0)
+
+
+class MappedOperator:
+    """the same operator on trilinearly mapped cells (general MatrixFree mapping), from the assembled matrix"""
+
+    def __init__(self, maps, vertices):
+        self.maps = maps
+        self.A0 = assemble_matrix_mapped(maps, vertices, identity_rows=False)
+        d = np.zeros(maps.n_dofs)
+        d[maps.constrained] = 1.0
+        self.A = (self.A0 + sp.diags(d)).tocsr()
+
+    def m(self):
+        return self.maps.n_dofs
+
+    def vmult(self, x):
+        return self.A @ x
+
+    Tvmult = vmult_interface_down = vmult
+
+    def compute_inverse_diagonal(self):
+        diag = self.A0.diagonal()
         return np.where(np.abs(diag) > 1.0e-10, 1.0 / np.where(diag == 0, 1.0, diag), 1.0)
 
 

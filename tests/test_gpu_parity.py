@@ -381,3 +381,53 @@ def test_cuda_graph_replay_local_smoothing(gpu, mg_type):
             mg.synchronize()
     finally:
         mg.set_stream(0)
+
+
+# ----------------------------------------------------------------------------------------------- general geometry (MappingQ1)
+Q1_CASES = [("quadrant", 3, 1, "affine", "double"), ("quadrant", 3, 2, "affine", "double"), ("quadrant", 3, 4, "affine", "double"),
+            ("annulus", 5, 3, "affine", "double"), ("hypercube", 3, 2, "smooth", "double"), ("hypercube", 2, 4, "smooth", "double"),
+            ("hypercube", 1, 5, "smooth", "double"), ("hypercube", 1, 6, "smooth", "double"), ("hypercube", 2, 3, "cube", "double"),
+            ("quadrant", 3, 2, "affine", "float")]
+
+
+@pytest.mark.parametrize("geometry,L,p,deformation,number", Q1_CASES)
+def test_general_geometry_operator(gpu, geometry, L, p, deformation, number):
+    """non-Cartesian cells (8 vertices per cell, trilinear map): vmult, interface operator, inverse diagonal and the
+    Chebyshev smoother built on them against the assembled-matrix oracle; undeformed vertices reproduce the Cartesian kernel"""
+    from util import affine_map, smooth_map
+    mg = gpu
+    d = mg.DoFMap(mg.Mesh(geometry, L), p)
+    maps = ref.LevelMaps.from_dofmap(d)
+    verts = ref.cell_vertices(maps, {"affine": affine_map, "smooth": smooth_map, "cube": None}[deformation])
+    oracle = ref.MappedOperator(maps, verts)
+    ntype, tol = (mg.DOUBLE, PARITY_RTOL) if number == "double" else (mg.FLOAT, 2e-5)
+    op = mg.Operator(d, ntype)
+    op.set_cell_vertices(verts)
+    with pytest.raises(RuntimeError):
+        op.set_cell_vertices(verts[:-1])                                           # wrong cell count is refused
+    src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+    x = seeded(maps.n_dofs)
+    src.from_numpy(x)
+    op.vmult(dst, src)
+    y = dst.to_numpy()
+    assert rel_l2(y, oracle.vmult(x)) < tol
+    np.testing.assert_array_equal(y[maps.constrained], src.to_numpy()[maps.constrained])
+    op.vmult_interface_down(dst, src)
+    assert rel_l2(dst.to_numpy(), oracle.vmult(x)) < tol
+    diag = op.initialize_dof_vector()
+    op.compute_inverse_diagonal(diag)
+    assert rel_l2(diag.to_numpy(), oracle.compute_inverse_diagonal()) < tol
+    if deformation == "cube":                                                      # same operator as the Cartesian kernel
+        plain = mg.Operator(d, ntype)
+        plain.vmult(dst, src)
+        assert rel_l2(dst.to_numpy(), y) < tol
+    if number == "double":
+        ocheb = ref.PreconditionChebyshev(oracle, 3, 20.0, 20)
+        cheb = mg.PreconditionChebyshev(op, 3, 20.0, 20)
+        ocheb.estimate_eigenvalues()
+        assert abs(cheb.eigenvalues()[1] - ocheb.lmax) < 1e-9 * ocheb.lmax
+        b = seeded(maps.n_dofs, 7)
+        rhs = op.initialize_dof_vector()
+        rhs.from_numpy(b)
+        cheb.vmult(dst, rhs)
+        assert rel_l2(dst.to_numpy(), ocheb.vmult(b)) < 1e-10

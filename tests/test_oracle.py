@@ -188,3 +188,47 @@ def test_c_restatement_matches_numpy_oracle(L, p):
     xs, its, res, _ = M.solve(rhs)
     xr, itr, ctl = H.solve(rhs.copy())
     assert its == itr and rel_l2(xs, xr) < 1e-11 and abs(res - ctl.last_value) < 1e-10 * ctl.initial_value
+
+
+# ------------------------------------------------------------------------------------ general geometry (MappingQ1) oracle
+@pytest.mark.parametrize("p", [1, 2, 3])
+def test_mapped_element_matrix_pins(p):
+    """undeformed cells give h * A_ref; an affine map x = A xi + b gives the closed form with G = det(A) A^-1 A^-T;
+    a linear function has zero residual and the energy of u = c.x is |c|^2 * volume"""
+    from util import AFFINE_A, affine_map
+    maps = ref.LevelMaps.from_dofmap(mg.DoFMap(mg.Mesh("quadrant", 3), p))
+    fe = maps.fe
+    A_ref = ref.element_matrix_reference(fe)
+    cube = ref.element_matrices_mapped(fe, ref.cell_vertices(maps)[:5])
+    for c in range(5):
+        np.testing.assert_allclose(cube[c], maps.h[c] * A_ref, rtol=0, atol=1e-12 * np.abs(A_ref).max())
+    # closed form for the affine map: reference gradients contracted with h det(A) (A^-1 A^-T)
+    n = fe.n
+    d = [np.einsum("ck,bj,ai->cbakji", *m).reshape(n ** 3, n ** 3) for m in ((fe.B, fe.B, fe.G), (fe.B, fe.G, fe.B), (fe.G, fe.B, fe.B))]
+    W = np.einsum("a,b,c->abc", fe.wq, fe.wq, fe.wq).ravel()
+    Ainv = np.linalg.inv(AFFINE_A)
+    Gm = np.linalg.det(AFFINE_A) * Ainv @ Ainv.T
+    closed = sum(Gm[a, b] * d[a].T @ (W[:, None] * d[b]) for a in range(3) for b in range(3))
+    verts = ref.cell_vertices(maps, affine_map)
+    aff = ref.element_matrices_mapped(fe, verts[:5])
+    for c in range(5):
+        np.testing.assert_allclose(aff[c], maps.h[c] * closed, rtol=0, atol=1e-12 * np.abs(closed).max())
+    # whole mesh with hanging nodes: symmetric; linear functions are in the kernel on unconstrained rows; energy = volume
+    A = ref.assemble_matrix_mapped(maps, verts, identity_rows=False)
+    assert abs(A - A.T).max() < 1e-12
+    xyz = affine_map(maps.dof_coordinates())
+    cvec = np.array([0.7, -1.3, 0.4])
+    u = xyz @ cvec
+    free = np.ones(maps.n_dofs, bool)
+    free[maps.constrained] = False
+    # (the assembled matrix eliminates Dirichlet columns, so test the energy with the un-eliminated operator instead)
+    maps_free = ref.LevelMaps(maps.degree, maps.eval_table & ref.INDEX_MASK, maps.own_table & ref.INDEX_MASK, maps.mask, maps.cell_level,
+                              maps.cell_xyz, np.zeros(0, np.int64), maps.n_dofs)
+    Afull = ref.assemble_matrix_mapped(maps_free, verts, identity_rows=False)
+    hanging = np.setdiff1d(maps.constrained, np.nonzero(np.any(np.abs(np.abs(maps.dof_coordinates()) - 1.0) < 1e-12, axis=1))[0])
+    u[hanging] = 0.0                                     # hanging DoFs are slaves: their values come from the constraints
+    volume = 8.0 * abs(np.linalg.det(AFFINE_A))
+    assert u @ (Afull @ u) == pytest.approx(cvec @ cvec * volume, rel=1e-12)
+    r = Afull @ u
+    interior = free.copy()
+    assert np.abs(r[interior]).max() < 1e-11 * np.abs(u).max()

@@ -125,3 +125,19 @@ def params(geometry="hypercube", n_ref=3, degree=2, mg_type="HMG-global", coarse
             "Paraview": False, "Verbosity": False, "PartitionerName": "DefaultPolicy", "MinLevel": "0", "MinNCells": "0",
             "CoarseGridSolverType": coarse, "SmootherDegree": smoother_degree, "CoarseSolverNCycles": 1,
             "RelativeTolerance": reltol, "MGNumberType": number, "SimulationType": simulation}
+
+
+# ------------------------------------------------------------------------------------ general (non-Cartesian) geometry
+AFFINE_A = np.array([[1.10, 0.25, -0.10], [0.05, 0.90, 0.30], [-0.20, 0.15, 1.20]])
+
+
+def affine_map(xyz):
+    """shear + stretch + shift: keeps hanging nodes conforming (midpoints map to midpoints)"""
+    return xyz @ AFFINE_A.T + np.array([0.3, -0.2, 0.1])
+
+
+def smooth_map(xyz):
+    """smooth non-affine deformation of [-1,1]^3 (vertices only; trilinear inside the cells) for meshes without hanging nodes"""
+    x, y, z = xyz[:, 0], xyz[:, 1], xyz[:, 2]
+    return np.stack([x + 0.08 * np.sin(np.pi * y) * np.cos(0.5 * np.pi * z), y + 0.06 * np.sin(np.pi * z) * x,
+                     z + 0.07 * np.cos(np.pi * x) * np.sin(0.5 * np.pi * y)], axis=1)
