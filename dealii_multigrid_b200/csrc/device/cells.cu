@@ -53,6 +53,37 @@ namespace mgb
           }
       }
     MGB_CUDA(cudaMemcpyToSymbol(c_feq, &hq, sizeof(FEConstQ), sizeof(FEConstQ) * degree));
+    // even-odd tables of B, G = (d/dx of the nodal basis at the Gauss points) and their transposes (k_laplace_q1_slab)
+    {
+      const int           n = fe.n;
+      std::vector<double> A[4] = {std::vector<double>(n * n), std::vector<double>(n * n), std::vector<double>(n * n),
+                                  std::vector<double>(n * n)};
+      for (int q = 0; q < n; ++q)
+        for (int i = 0; i < n; ++i)
+          {
+            A[0][q * n + i] = fe.Bq[q * n + i];
+            A[1][q * n + i] = lagrange_derivative(fe.nodes, i, fe.xq[q]);
+            A[2][i * n + q] = A[0][q * n + i];
+            A[3][i * n + q] = A[1][q * n + i];
+          }
+      static FEConstQEO he; // 3 KB: keep it off the stack
+      he = FEConstQEO{};
+      for (int mat = 0; mat < 4; ++mat)
+        for (int q = 0; q < (n + 1) / 2; ++q)
+          {
+            for (int l = 0; l < n / 2; ++l)
+              {
+                const double a = A[mat][q * n + l], b = A[mat][q * n + n - 1 - l];
+                he.m[mat][q * MAXN + l]         = 0.5 * (a + b);
+                he.m[mat][q * MAXN + n - 1 - l] = 0.5 * (a - b);
+              }
+            if (n % 2 == 1)
+              he.m[mat][q * MAXN + n / 2] = A[mat][q * n + n / 2];
+            for (int l = 0; l < n; ++l)
+              he.mf[mat][q * MAXN + l] = (float)he.m[mat][q * MAXN + l];
+          }
+      MGB_CUDA(cudaMemcpyToSymbol(c_feqeo, &he, sizeof(FEConstQEO), sizeof(FEConstQEO) * degree));
+    }
     MGB_CUDA(cudaMemcpyToSymbol(c_fe, &h, sizeof(FEConst), sizeof(FEConst) * degree));
     MGB_CUDA(cudaMemcpyToSymbol(c_fef, &hf, sizeof(FEConstF), sizeof(FEConstF) * degree));
     done[degree] = true;
@@ -75,6 +106,17 @@ namespace mgb
   {
     if (cd.vertices)
       {
+        if (cd.degree <= 4 && q1_use_slab())
+          {
+            switch (cd.degree)
+              {
+                case 1: launch_q1_slab<1, T>(cd, src, dst, cell_list, n_list, s); break;
+                case 2: launch_q1_slab<2, T>(cd, src, dst, cell_list, n_list, s); break;
+                case 3: launch_q1_slab<3, T>(cd, src, dst, cell_list, n_list, s); break;
+                default: launch_q1_slab<4, T>(cd, src, dst, cell_list, n_list, s); break;
+              }
+            return;
+          }
         DISPATCH_DEGREE(cd.degree, (launch_q1<P, T, 0>(cd, src, dst, cell_list, n_list, s)));
         return;
       }
