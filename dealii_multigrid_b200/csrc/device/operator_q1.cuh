@@ -277,8 +277,22 @@ namespace mgb
   // gather, the two z sweeps (B_z u and G_z u into two shared arrays), their transposes and the scatter.  Slab layout
   // (lane <-> plane k of a cell, n^2 values in registers): the x/y sweeps and the metric.  The Jacobian at a point
   // comes from the 8 coefficient vectors of the trilinear map (Moebius transform of the 8 vertices, once per cell in
-  // shared memory): 15 FMA per point instead of 8 x 15.  Degrees 1..4 (three n^2 register planes per thread); higher
-  // degrees and the diagonal use k_laplace_q1 above.
+  // shared memory): 15 FMA per point instead of 8 x 15.  The metric is applied in a loop that is rolled over the
+  // y index with the three gradient planes in shared memory (each thread only touches its own plane): the fully
+  // unrolled register form has 6952 SASS instructions per batch and stalls on instruction fetch (ncu: no_instruction
+  // 4 of 10 cycles per issue, profiles/r1s_ncu_q1_slab_L6.txt); the warps of a block also walk through the batches
+  // in lockstep so that they share the fetched lines.  1/det by two Newton steps on the FP32 reciprocal.
+  // Measured (hypercube L=6 p=4 FP64, smooth deformation): 2.15 ms for k_laplace_q1, 0.97 ms register form,
+  // 0.50 ms this form (profiles/r1t_time_vmult_q1_variants.txt).  Degrees 1..4; higher degrees and the diagonal use
+  // k_laplace_q1 above.
+  // Build-time variants (measured in profiles/r1t_time_vmult_q1_variants.txt): the defaults are the rolled metric loop
+  // through shared memory and block-lockstep batches; -DMGB_Q1_REG_METRIC / -DMGB_Q1_NO_LOCKSTEP restore the first form.
+#if !defined(MGB_Q1_REG_METRIC) && !defined(MGB_Q1_SMEM_METRIC)
+#define MGB_Q1_SMEM_METRIC
+#endif
+#if !defined(MGB_Q1_NO_LOCKSTEP) && !defined(MGB_Q1_LOCKSTEP)
+#define MGB_Q1_LOCKSTEP
+#endif
   struct FEConstQEO
   {
     // even-odd tables of 0: B, 1: G, 2: B^T, 3: G^T.  For A with A[n-1-q][n-1-l] = sigma A[q][l] (sigma = +1 for B, -1 for G),
@@ -368,7 +382,12 @@ namespace mgb
     static constexpr int    CS = SlabLayout<n, sizeof(T)>::CS;
     static constexpr size_t u_bytes    = (size_t(CW * CS) * sizeof(T) + 15) / 16 * 16;
     static constexpr size_t tab_bytes  = 2 * size_t(CW) * CTAB_STRIDE * 4;
-    static constexpr size_t warp_bytes = 2 * u_bytes + tab_bytes + size_t(CW) * 24 * sizeof(double);
+#ifdef MGB_Q1_SMEM_METRIC
+    static constexpr size_t g_bytes    = size_t(n * n) * 32 * sizeof(T); // gy of the slab phase, [n^2][lane]
+#else
+    static constexpr size_t g_bytes    = 0;
+#endif
+    static constexpr size_t warp_bytes = 2 * u_bytes + tab_bytes + size_t(CW) * 24 * sizeof(double) + g_bytes;
   };
 
   template <int P, typename T>
@@ -388,12 +407,21 @@ namespace mgb
     T             *u2    = reinterpret_cast<T *>(wbase + SM::u_bytes);                         // [CW*CS]  G_z u   / v2
     uint32_t      *tbuf  = reinterpret_cast<uint32_t *>(wbase + 2 * SM::u_bytes);              // [2][CW][32]
     double        *cf    = reinterpret_cast<double *>(wbase + 2 * SM::u_bytes + SM::tab_bytes); // [CW][8][3]
+#ifdef MGB_Q1_SMEM_METRIC
+    T *u3 = reinterpret_cast<T *>(wbase + 2 * SM::u_bytes + SM::tab_bytes + size_t(CW) * 24 * sizeof(double)) + lane; // [n^2][32]
+#endif
 
     const long long n_batches = (n_work + CW - 1) / CW;
     const long long stride    = (long long)gridDim.x * W;
     long long       b         = (long long)blockIdx.x * W + warp;
+#ifdef MGB_Q1_LOCKSTEP
+    // the warps of a block walk through the (fully unrolled, > 100 KB) loop body together, so that they share the
+    // instruction-cache lines: same trip count for all warps, one barrier per iteration
+    const long long n_it = (n_batches - (long long)blockIdx.x * W + stride - 1) / stride;
+#else
     if (b >= n_batches)
       return;
+#endif
 
     // per-lane description of the columns of each round (as in k_laplace_apply):
     // cell (5 bits) | entity base tx+3ty (4) | offset inside the entity (5) | z stride inside the entity (5) | smem address (13)
@@ -432,9 +460,17 @@ namespace mgb
     issue_tables(b, tbuf);
     const int    cl = lane / n, t = lane - cl * n; // slab layout: plane t of cell cl
     const double zeta = c_feq[P].xq[t < n ? t : 0];
+#ifdef MGB_Q1_LOCKSTEP
+    for (int it = 0; it < (int)n_it; b += stride, ++it)
+      {
+        __syncthreads();
+        if (b >= n_batches)
+          continue;
+#else
     int          it = 0;
     for (; b < n_batches; b += stride, ++it)
       {
+#endif
         uint32_t       *tb    = tbuf + (it & 1) * (CW * CTAB_STRIDE);
         const long long first = b * CW;
         const int       ncw   = (int)min((long long)CW, n_work - first);
@@ -559,6 +595,79 @@ namespace mgb
                 eo_sweep<P, T, n, 0>(ga + i); // gx = B_y G_x
                 eo_sweep<P, T, n, 1>(gb + i); // gy = G_y B_x
               }
+#ifdef MGB_Q1_SMEM_METRIC
+#pragma unroll
+            for (int r = 0; r < n2; ++r)
+              {
+                p1[r]      = ga[r];
+                u3[r * 32] = gb[r];
+              }
+            // metric at the n^2 points of the plane
+            const double *c  = cf + cl * 24;
+            const double  wz = c_feq[P].wq[t];
+            double        A0[3], A1[3], B0[3];
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+              {
+                A0[d] = c[1 * 3 + d] + c[5 * 3 + d] * zeta; // d x_d / d xi   = A0 + A1 eta
+                A1[d] = c[3 * 3 + d] + c[7 * 3 + d] * zeta;
+                B0[d] = c[2 * 3 + d] + c[6 * 3 + d] * zeta; // d x_d / d eta  = B0 + A1 xi
+              }
+#pragma unroll 1
+            for (int j = 0; j < n; ++j) // rolled: the gradients of the plane live in shared memory
+              {
+                const double eta = c_feq[P].xq[j];
+                double       J0[3], E0[3], F0[3];
+#pragma unroll
+                for (int d = 0; d < 3; ++d)
+                  {
+                    J0[d] = A0[d] + A1[d] * eta;
+                    E0[d] = c[4 * 3 + d] + c[6 * 3 + d] * eta; // d x_d / d zeta = E0 + F0 xi
+                    F0[d] = c[5 * 3 + d] + c[7 * 3 + d] * eta;
+                  }
+#pragma unroll
+                for (int i = 0; i < n; ++i)
+                  {
+                    const double xi = c_feq[P].xq[i];
+                    double       J1[3], J2[3];
+#pragma unroll
+                    for (int d = 0; d < 3; ++d)
+                      {
+                        J1[d] = B0[d] + A1[d] * xi;
+                        J2[d] = E0[d] + F0[d] * xi;
+                      }
+                    // J[c][0] = J0[c], J[c][1] = J1[c], J[c][2] = J2[c]; cofactors C[c][d]
+                    const double C00 = J1[1] * J2[2] - J2[1] * J1[2], C01 = J2[1] * J0[2] - J0[1] * J2[2],
+                                 C02 = J0[1] * J1[2] - J1[1] * J0[2];
+                    const double C10 = J2[0] * J1[2] - J1[0] * J2[2], C11 = J0[0] * J2[2] - J2[0] * J0[2],
+                                 C12 = J1[0] * J0[2] - J0[0] * J1[2];
+                    const double C20 = J1[0] * J2[1] - J2[0] * J1[1], C21 = J2[0] * J0[1] - J0[0] * J2[1],
+                                 C22 = J0[0] * J1[1] - J1[0] * J0[1];
+                    const double det = J0[0] * C00 + J1[0] * C01 + J2[0] * C02;
+#ifndef MGB_Q1_EXACT_DIV
+                    double rdet = double(1.0f / float(det)); // two Newton steps: 6e-8 -> 4e-15 -> 1e-29 relative
+                    rdet        = rdet * (2.0 - det * rdet);
+                    rdet        = rdet * (2.0 - det * rdet);
+                    const double s = c_feq[P].wq[i] * c_feq[P].wq[j] * wz * rdet;
+#else
+                    const double s = c_feq[P].wq[i] * c_feq[P].wq[j] * wz / det;
+#endif
+                    const int    r   = j * n + i;
+                    const double g0 = double(p1[r]), g1 = double(u3[r * 32]), g2 = double(p2[r]);
+                    const double p0 = C00 * g0 + C01 * g1 + C02 * g2, p1v = C10 * g0 + C11 * g1 + C12 * g2,
+                                 p2v = C20 * g0 + C21 * g1 + C22 * g2;
+                    p1[r] = T(s * (C00 * p0 + C10 * p1v + C20 * p2v));
+                    u3[r * 32] = T(s * (C01 * p0 + C11 * p1v + C21 * p2v));
+                    p2[r] = T(s * (C02 * p0 + C12 * p1v + C22 * p2v));
+                  }
+              }
+#pragma unroll
+            for (int r = 0; r < n2; ++r)
+              {
+                ga[r] = p1[r];
+                gb[r] = u3[r * 32];
+              }
+#else
             // metric at the n^2 points of the plane
             const double *c  = cf + cl * 24;
             const double  wz = c_feq[P].wq[t];
@@ -601,7 +710,7 @@ namespace mgb
                     const double C20 = J1[0] * J2[1] - J2[0] * J1[1], C21 = J2[0] * J0[1] - J0[0] * J2[1],
                                  C22 = J0[0] * J1[1] - J1[0] * J0[1];
                     const double det = J0[0] * C00 + J1[0] * C01 + J2[0] * C02;
-#ifdef MGB_Q1_FAST_RCP
+#ifndef MGB_Q1_EXACT_DIV
                     double rdet = double(1.0f / float(det)); // two Newton steps: 6e-8 -> 4e-15 -> 1e-29 relative
                     rdet        = rdet * (2.0 - det * rdet);
                     rdet        = rdet * (2.0 - det * rdet);
@@ -618,6 +727,7 @@ namespace mgb
                     p2[r] = T(s * (C02 * p0 + C12 * p1v + C22 * p2v));
                   }
               }
+#endif
             // transposed y and x sweeps
 #pragma unroll
             for (int i = 0; i < n; ++i)
