@@ -232,3 +232,75 @@ def test_mapped_element_matrix_pins(p):
     r = Afull @ u
     interior = free.copy()
     assert np.abs(r[interior]).max() < 1e-11 * np.abs(u).max()
+
+
+def _eo_tables(fe):
+    """even-odd tables of B, G, B^T, G^T as csrc/device/cells.cu builds them for k_laplace_q1_slab (FEConstQEO)"""
+    n = fe.n
+    A = [fe.B, fe.G, fe.B.T.copy(), fe.G.T.copy()]
+    m = np.zeros((4, n, n))
+    for mat in range(4):
+        for q in range((n + 1) // 2):
+            for l in range(n // 2):
+                a, b = A[mat][q, l], A[mat][q, n - 1 - l]
+                m[mat, q, l], m[mat, q, n - 1 - l] = 0.5 * (a + b), 0.5 * (a - b)
+            if n % 2 == 1:
+                m[mat, q, n // 2] = A[mat][q, n // 2]
+    return m
+
+
+def _eo_sweep(m, mat, v):
+    """the kernel's eo_sweep: sums/differences of mirrored entries, half-size products, butterfly; sigma = -1 for G"""
+    n = len(v)
+    no, mid, odd, antisym = n // 2, n // 2, n % 2 == 1, (mat & 1) != 0
+    e = [v[l] + v[n - 1 - l] for l in range(no)]
+    o = [v[l] - v[n - 1 - l] for l in range(no)]
+    out = np.array(v, dtype=float)
+    for q in range(no):
+        X = sum(m[mat, q, l] * e[l] for l in range(no)) + (m[mat, q, mid] * v[mid] if odd else 0.0)
+        Y = sum(m[mat, q, n - 1 - l] * o[l] for l in range(no))
+        out[q], out[n - 1 - q] = X + Y, (Y - X if antisym else X - Y)
+    if odd:
+        out[mid] = (sum(m[mat, mid, n - 1 - l] * o[l] for l in range(no)) if antisym else
+                    m[mat, mid, mid] * v[mid] + sum(m[mat, mid, l] * e[l] for l in range(no)))
+    return out
+
+
+@pytest.mark.parametrize("p", [1, 2, 3, 4])
+def test_general_geometry_kernel_formulation(p):
+    """the algebra of k_laplace_q1_slab (operator_q1.cuh), restated step by step in numpy, against the dense mapped-cell
+    oracle: even-odd sweeps with the centro-(anti)symmetric tables, 16-sweep ordering (z in the column layout, x/y per
+    plane), Jacobian from the 8 trilinear coefficient vectors (Moebius transform of the vertices), flux w C^T C g / det"""
+    fe = ref.LevelMaps.from_dofmap(mg.DoFMap(mg.Mesh("hypercube", 1), p)).fe
+    n, xq, wq = fe.n, fe.xq, fe.wq
+    m = _eo_tables(fe)
+    rng = np.random.default_rng(p)
+    for mat, A in enumerate((fe.B, fe.G, fe.B.T, fe.G.T)):                          # every table reproduces its matrix
+        v = rng.standard_normal(n)
+        np.testing.assert_allclose(_eo_sweep(m, mat, v), A @ v, rtol=0, atol=1e-13 * np.abs(A).max() * n)
+    sw = lambda mat, u, axis: np.apply_along_axis(lambda v: _eo_sweep(m, mat, v), axis, u)
+    corner = np.array([[(v >> d) & 1 for d in range(3)] for v in range(8)], dtype=float)
+    X = 0.3 * corner + 0.04 * rng.standard_normal((8, 3)) + np.array([0.2, -0.4, 0.1])
+    c = X.copy()
+    for bit in (1, 2, 4):                                                          # vertices -> coefficients of 1, xi, eta, xi eta, zeta, ...
+        for v in range(8):
+            if v & bit:
+                c[v] -= c[v ^ bit]
+    u = rng.standard_normal((n, n, n))                                             # u[k, j, i]
+    u1, u2 = sw(0, u, 0), sw(1, u, 0)
+    v1, v2 = np.zeros_like(u), np.zeros_like(u)
+    for t in range(n):
+        gx, gy, gz = sw(0, sw(1, u1[t], 1), 0), sw(1, sw(0, u1[t], 1), 0), sw(0, sw(0, u2[t], 1), 0)
+        A0, A1, B0 = c[1] + c[5] * xq[t], c[3] + c[7] * xq[t], c[2] + c[6] * xq[t]
+        for j in range(n):
+            J0, E0, F0 = A0 + A1 * xq[j], c[4] + c[6] * xq[j], c[5] + c[7] * xq[j]
+            for i in range(n):
+                J = np.stack([J0, B0 + A1 * xq[i], E0 + F0 * xq[i]], axis=1)       # J[c][d] = d x_c / d xi_d
+                C = np.linalg.det(J) * np.linalg.inv(J).T                          # cofactors
+                g = np.array([gx[j, i], gy[j, i], gz[j, i]])
+                gx[j, i], gy[j, i], gz[j, i] = wq[i] * wq[j] * wq[t] / np.linalg.det(J) * (C.T @ (C @ g))
+        v1[t] = sw(3, sw(2, gx, 0), 1) + sw(2, sw(3, gy, 0), 1)
+        v2[t] = sw(2, sw(2, gz, 0), 1)
+    y = sw(2, v1, 0) + sw(3, v2, 0)
+    y_ref = ref.element_matrices_mapped(fe, X[None])[0] @ u.ravel()
+    assert rel_l2(y.ravel(), y_ref) < 1e-13

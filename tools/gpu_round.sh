@@ -11,6 +11,11 @@ for spec in "hypercube 6 4 double" "hypercube 7 4 double" "hypercube 7 4 float" 
   set -- $spec
   timeout 300 python tools/time_vmult.py --geometry $1 --nref $2 --degree $3 --number $4 --reps 100 >> $O/${TAG}_time_vmult.txt 2>&1
 done
+# general-geometry kernel (mgb_operator_set_cell_vertices): smoothly deformed cells
+for spec in "6 4 double" "6 3 double" "6 2 double" "6 1 double" "6 4 float" "7 4 double"; do
+  set -- $spec
+  timeout 300 python tools/time_vmult.py --nref $1 --degree $2 --number $3 --deform smooth --reps 20 >> $O/${TAG}_time_vmult_q1.txt 2>&1
+done
 timeout 600 python bench.py --nref 6 > $O/${TAG}_bench_L6.json 2> $O/${TAG}_bench_L6.err; echo "bench L6 rc=$?"
 timeout 900 python bench.py > $O/${TAG}_bench_L7.json 2> $O/${TAG}_bench_L7.err; echo "bench L7 rc=$?"
 timeout 600 python bench.py --number float --no-cpu > $O/${TAG}_bench_L7_float.json 2> $O/${TAG}_bench_L7_float.err; echo "bench L7 float rc=$?"
@@ -24,5 +29,7 @@ timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_la
 # the bench workload itself (L=7): DRAM traffic per launch for roofline.traffic
 timeout 600 ncu --set full --clock-control none -k regex:k_laplace_apply --launch-skip 3 -c 1 -f -o $O/${TAG}_vmult_L7 \
   python tools/time_vmult.py --nref 7 --degree 4 --reps 2 > $O/${TAG}_ncu_full_L7.log 2>&1; echo "ncu full L7 rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_laplace_q1_slab --launch-skip 3 -c 1 -f -o $O/${TAG}_q1_slab_L6 \
+  python tools/time_vmult.py --nref 6 --degree 4 --deform smooth --reps 2 > $O/${TAG}_ncu_q1.log 2>&1; echo "ncu q1 rc=$?"
 for L in 6 7; do timeout 120 python tools/time_transfer.py --nref $L >> $O/${TAG}_time_transfer.txt 2>&1; done
 ls -la $O | tail -20
