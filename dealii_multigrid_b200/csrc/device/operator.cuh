@@ -222,8 +222,14 @@ namespace mgb
     const long long n_batches = (n_work + CW - 1) / CW;
     const long long stride    = (long long)gridDim.x * W;
     long long       b         = (long long)blockIdx.x * W + warp;
+#ifdef MGB_SLAB_LOCKSTEP
+    // experiment (-DMGB_SLAB_LOCKSTEP): the warps of a block walk through the unrolled loop body together and share its
+    // instruction-cache lines (same trip count for all warps, one barrier per batch); see k_laplace_q1_slab
+    const long long n_it = (n_batches - (long long)blockIdx.x * W + stride - 1) / stride;
+#else
     if (b >= n_batches)
       return;
+#endif
 
     // static per-lane description of the columns of each round, packed into one word:
     // cell (5 bits) | entity base tx+3ty (4) | offset inside the entity (5) | z stride inside the entity (5) | smem address (13)
@@ -287,9 +293,17 @@ namespace mgb
 
     const int cl = lane / n, t = lane - cl * n;
     const T   lk = cl < CW ? FDM<P, T>::lam(t) : T(0);
+#ifdef MGB_SLAB_LOCKSTEP
+    for (int it = 0; it < (int)n_it; b += stride, ++it)
+      {
+        __syncthreads();
+        if (b >= n_batches)
+          continue;
+#else
     int       it = 0;
     for (; b < n_batches; b += stride, ++it)
       {
+#endif
         const uint32_t *tb  = tbuf + (it % 3) * (CW * CTAB_STRIDE);
         const int       ncw = (int)min((long long)CW, n_work - b * CW);
         bool            warp_hn = false;
