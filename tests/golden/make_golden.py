@@ -43,7 +43,32 @@ def generate(c):
                 n_iterations=its, final_residual=ctl.last_value, lambda_max=np.array([s.lmax for s in H.smoothers]))
 
 
+# general (non-Cartesian) geometry: operator-level fixtures in tests/golden/mapped/ (vmult and inverse diagonal of the
+# mapped-cell oracle on seeded input; the deformation is applied to the cell vertices, util.affine_map / smooth_map)
+MAPPED_CASES = [("quadrant", 3, 4, "affine"), ("quadrant", 3, 1, "affine"), ("hypercube", 2, 4, "smooth"), ("hypercube", 3, 3, "smooth")]
+
+
+def mapped_case_name(c):
+    return "%s_L%d_p%d_%s" % c
+
+
+def generate_mapped(c):
+    import dealii_multigrid_b200 as mg
+    from oracle import reference as ref
+    from util import affine_map, smooth_map
+    geometry, L, p, deformation = c
+    maps = ref.LevelMaps.from_dofmap(mg.DoFMap(mg.Mesh(geometry, L), p))
+    verts = ref.cell_vertices(maps, {"affine": affine_map, "smooth": smooth_map}[deformation])
+    op = ref.MappedOperator(maps, verts)
+    return dict(n_dofs=maps.n_dofs, vertices=verts, vmult=op.vmult(seeded(maps.n_dofs)), inverse_diagonal=op.compute_inverse_diagonal())
+
+
 if __name__ == "__main__":
+    os.makedirs(os.path.join(HERE, "mapped"), exist_ok=True)
+    for c in MAPPED_CASES:
+        if os.path.exists(os.path.join(HERE, "mapped", mapped_case_name(c) + ".npz")) and "--all" not in sys.argv:
+            continue
+        np.savez_compressed(os.path.join(HERE, "mapped", mapped_case_name(c) + ".npz"), **generate_mapped(c))
     for c in CASES:
         if os.path.exists(os.path.join(HERE, case_name(c) + ".npz")) and "--all" not in sys.argv:
             continue  # existing fixtures stay frozen; pass --all to regenerate everything
