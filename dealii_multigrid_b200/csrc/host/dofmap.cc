@@ -185,29 +185,37 @@ namespace mgb
     dm.cell_begin = cell_begin[rank];
     dm.n_cells    = cell_begin[rank + 1] - cell_begin[rank];
 
-    // pass 1: global numbering, Morton first touch
+    // pass 1: global numbering, Morton first touch; the bases of the local cells' own entities are kept (g_own) so that
+    // pass 2 does not look them up again
     FlatMap ent;
     ent.reserve(size_t(nc) * (degree > 1 ? 9 : 2) + 64);
     std::vector<int64_t> dof_begin(n_ranks + 1, 0);
+    std::vector<int64_t> g_eval(size_t(dm.n_cells) * 27), g_own(size_t(dm.n_cells) * 27, -1);
     int64_t              next = 0;
     {
-      int r = 0;
+      int           r       = 0;
+      const int64_t l_begin = cell_begin[rank], l_end = cell_begin[rank + 1];
       for (int64_t i = 0; i < nc; ++i)
         {
           while (r < n_ranks && cell_begin[r] == i)
             dof_begin[r++] = next;
-          const Cell &c = mesh.cells[i];
+          const Cell &c     = mesh.cells[i];
+          int64_t    *local = (i >= l_begin && i < l_end) ? &g_own[size_t(i - l_begin) * 27] : nullptr;
           for (int k = 0; k < 27; ++k)
             {
               const int e = ENTITY_ORDER[k];
               if (esize[e] == 0)
                 continue;
-              const uint64_t key = K(c.level, c.x, c.y, c.z, e);
-              if (ent.find(key) < 0)
+              const uint64_t key  = K(c.level, c.x, c.y, c.z, e);
+              int64_t        base = ent.find(key);
+              if (base < 0)
                 {
+                  base = next;
                   ent.insert(key, next);
                   next += esize[e];
                 }
+              if (local)
+                local[e] = base;
             }
         }
       while (r <= n_ranks)
@@ -230,7 +238,6 @@ namespace mgb
       bool    operator<(const Ent &o) const { return base < o.base; }
       bool    operator==(const Ent &o) const { return base == o.base; }
     };
-    std::vector<int64_t>          g_eval(size_t(dm.n_cells) * 27), g_own(size_t(dm.n_cells) * 27);
     std::vector<uint8_t>          f_eval(size_t(dm.n_cells) * 27), f_own(size_t(dm.n_cells) * 27);
     std::vector<Ent>              ghosts, constrained_ents;
     std::vector<std::vector<Ent>> imports(n_ranks);
@@ -240,12 +247,38 @@ namespace mgb
 
     const int64_t pass_begin = n_ranks == 1 ? cell_begin[rank] : 0;
     const int64_t pass_end   = n_ranks == 1 ? cell_begin[rank + 1] : nc;
-    int           q          = 0;
+    // closed bounding box of the local cells on the doubled lattice of the finest level: a cell of another rank can only
+    // touch an entity we own (directly or, with hanging nodes, through its parent's entities) if its PARENT's closed box
+    // meets this one
+    uint64_t box_lo[3] = {~uint64_t(0), ~uint64_t(0), ~uint64_t(0)}, box_hi[3] = {0, 0, 0};
+    for (int64_t i = cell_begin[rank]; i < cell_begin[rank + 1]; ++i)
+      {
+        const Cell    &c    = mesh.cells[i];
+        const uint64_t U    = uint64_t(1) << (dm.mesh_max_level - c.level);
+        const uint64_t x[3] = {c.x, c.y, c.z};
+        for (int d = 0; d < 3; ++d)
+          {
+            box_lo[d] = std::min(box_lo[d], 2 * x[d] * U);
+            box_hi[d] = std::max(box_hi[d], (2 * x[d] + 2) * U);
+          }
+      }
+    const auto may_touch_local = [&](const Cell &c) {
+      const int      shift = c.level > 0 ? 1 : 0; // parent's box (the cell itself on level 0)
+      const uint64_t U     = uint64_t(1) << (dm.mesh_max_level - c.level + shift);
+      const uint64_t x[3]  = {c.x >> shift, c.y >> shift, c.z >> shift};
+      for (int d = 0; d < 3; ++d)
+        if ((2 * x[d] + 2) * U < box_lo[d] || 2 * x[d] * U > box_hi[d])
+          return false;
+      return true;
+    };
+    int q = 0;
     for (int64_t i = pass_begin; i < pass_end; ++i)
       {
         while (cell_begin[q + 1] <= i)
           ++q;
         const Cell &c = mesh.cells[i];
+        if (q != rank && (dm.n_cells == 0 || !may_touch_local(c)))
+          continue;
         uint64_t    own[27], eval[27];
         uint16_t    mask;
         analyse_cell(mesh, K, c, own, eval, mask);
@@ -267,7 +300,7 @@ namespace mgb
                     f_eval[l * 27 + e] = f_own[l * 27 + e] = 0;
                     continue;
                   }
-                const int64_t bo = ent.find(own[e]);
+                const int64_t bo = g_own[l * 27 + e]; // from pass 1
                 const int64_t be = (eval[e] == own[e]) ? bo : ent.find(eval[e]);
                 if (bo < 0 || be < 0)
                   throw std::runtime_error("DoFMap: entity lookup failed (mesh not 2:1 balanced?)");

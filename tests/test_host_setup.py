@@ -211,6 +211,10 @@ def test_partitioned_dofmaps_are_consistent(geometry, L, p, n_ranks, policy):
             j = list(pb["ghost_ranks"]).index(a.rank)
             recv = pb["ghost_global"][pb["ghost_offsets"][j]:pb["ghost_offsets"][j + 1]]
             np.testing.assert_array_equal(send, recv)
+    # ... and every ghost range has its import on the owner's side (no exchange partner is missed)
+    for b in parts:
+        for a_rank in b.partitioner()["ghost_ranks"]:
+            assert b.rank in list(parts[a_rank].partitioner()["import_ranks"])
 
 
 @pytest.mark.parametrize("p", [1, 2, 3, 4, 5, 6])
