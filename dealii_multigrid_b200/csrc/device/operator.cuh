@@ -204,6 +204,13 @@ namespace mgb
     static size_t           block_bytes(int warps) { return warps * warp_bytes_aligned; }
   };
 
+  // MGB_SLAB_ABLATE (timing experiments with tools/build_variants.sh only -- the results are wrong by construction):
+  //   1: no scatter (the atomic adds are predicated off by a value test that never holds)
+  //   2: no gather (the column values are made up from the indices, no loads from src)
+  //   3: no arithmetic and no shared-memory transposes (gathered values are scattered back directly)
+#ifndef MGB_SLAB_ABLATE
+#define MGB_SLAB_ABLATE 0
+#endif
   template <int P, typename T>
   __global__ void __launch_bounds__(SlabCfg<P>::W * 32, SlabCfg<P>::MIN_BLOCKS)
     k_laplace_apply(const uint32_t *__restrict__ ctab, const int any_hanging, const double root_length, const long long n_work,
@@ -278,8 +285,12 @@ namespace mgb
             if (col_cl(r) < ncw)
               {
                 const uint32_t idx = column_index(tb, r, k);
+#if MGB_SLAB_ABLATE == 2
+                pre[r][k] = T(idx & 1023u) * T(1e-3);
+#else
                 if (!(idx & D_FLAG_BIT))
                   pre[r][k] = __ldg(src + idx);
+#endif
               }
           }
     };
@@ -332,6 +343,14 @@ namespace mgb
             __syncwarp();
           }
         // z sweep in the column layout, then to shared memory
+#if MGB_SLAB_ABLATE == 3
+        T keep[NR][n];
+#pragma unroll
+        for (int r = 0; r < NR; ++r)
+#pragma unroll
+          for (int k = 0; k < n; ++k)
+            keep[r][k] = pre[r][k];
+#else
 #pragma unroll
         for (int r = 0; r < NR; ++r)
           if (col_cl(r) < ncw)
@@ -341,13 +360,14 @@ namespace mgb
               for (int k = 0; k < n; ++k)
                 u[col_sm(r) + k * PS] = pre[r][k];
             }
+#endif
         // tables(b+stride) have landed (issued one iteration ago): start the gather of the next batch
         cp_async_wait_all();
         __syncwarp();
         issue_gather(b + stride, tbuf + ((it + 1) % 3) * (CW * CTAB_STRIDE));
         issue_tables(b + 2 * stride, tbuf + ((it + 2) % 3) * (CW * CTAB_STRIDE));
 
-        if (cl < ncw)
+        if (MGB_SLAB_ABLATE != 3 && cl < ncw)
           {
             T  reg[n2];
             T *pl = u + cl * CS + t * PS; // plane k = t (z mode t): reg[j*n+i]
@@ -400,18 +420,28 @@ namespace mgb
           if (col_cl(r) < ncw)
             {
               T res[n];
+#if MGB_SLAB_ABLATE == 3
+#pragma unroll
+              for (int k = 0; k < n; ++k)
+                res[k] = keep[r][k];
+#else
 #pragma unroll
               for (int k = 0; k < n; ++k)
                 res[k] = u[col_sm(r) + k * PS];
               if (!warp_hn)
                 fdm_backward<P, T, 1>(res);
+#endif
               const unsigned level = (tb[col_cl(r) * CTAB_STRIDE + 27] >> 16) & 0xffu;
               const T        h     = T(root_length * __hiloint2double((1023 - (int)level) << 20, 0));
 #pragma unroll
               for (int k = 0; k < n; ++k)
                 {
                   const uint32_t idx = column_index(tb, r, k);
+#if MGB_SLAB_ABLATE == 1
+                  if (h * res[k] == T(-1.2345e300)) // never: keeps the arithmetic alive without the atomics
+#else
                   if (!(idx & D_FLAG_BIT))
+#endif
                     atomic_add(dst + idx, h * res[k]);
                 }
             }
