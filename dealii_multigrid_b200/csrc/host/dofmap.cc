@@ -612,12 +612,45 @@ namespace mgb
     // pass 2: all coarse cells: valences of the needed entities and what the other ranks import from us
     std::vector<std::vector<Ent>> imports(R);
     {
+      // A coarse cell contributes only if its fine patch touches an entity of our own patches (inside the closed bounding
+      // box of our coarse cells) or an entity we own (inside the closed bounding box of our fine cells): skip the others.
+      struct Box
+      {
+        uint64_t lo[3] = {~uint64_t(0), ~uint64_t(0), ~uint64_t(0)}, hi[3] = {0, 0, 0};
+        bool     empty = true;
+        void     add(const Cell &c, int Lmax)
+        {
+          const uint64_t U = uint64_t(1) << (Lmax - c.level), x[3] = {c.x, c.y, c.z};
+          for (int d = 0; d < 3; ++d)
+            {
+              lo[d] = std::min(lo[d], 2 * x[d] * U);
+              hi[d] = std::max(hi[d], (2 * x[d] + 2) * U);
+            }
+          empty = false;
+        }
+        bool meets(const Cell &c, int Lmax) const
+        {
+          if (empty)
+            return false;
+          const uint64_t U = uint64_t(1) << (Lmax - c.level), x[3] = {c.x, c.y, c.z};
+          for (int d = 0; d < 3; ++d)
+            if ((2 * x[d] + 2) * U < lo[d] || 2 * x[d] * U > hi[d])
+              return false;
+          return true;
+        }
+      } box_coarse, box_fine;
+      for (int64_t c = cb; c < ce; ++c)
+        box_coarse.add(mesh_coarse.cells[c], df.mesh_max_level);
+      for (int64_t f = df.rank_cell_begin[me]; f < df.rank_cell_begin[me + 1]; ++f)
+        box_fine.add(mesh_fine.cells[f], df.mesh_max_level);
       int              q = 0;
       std::vector<Ent> patch;
       for (int64_t c = 0; c < ncc; ++c)
         {
           while (dc.rank_cell_begin[q + 1] <= c)
             ++q;
+          if (!box_coarse.meets(mesh_coarse.cells[c], df.mesh_max_level) && !box_fine.meets(mesh_coarse.cells[c], df.mesh_max_level))
+            continue;
           patch.clear();
           for (int ch = 0; ch < nch[c]; ++ch)
             {
