@@ -304,3 +304,33 @@ def test_general_geometry_kernel_formulation(p):
     y = sw(2, v1, 0) + sw(3, v2, 0)
     y_ref = ref.element_matrices_mapped(fe, X[None])[0] @ u.ravel()
     assert rel_l2(y.ravel(), y_ref) < 1e-13
+
+
+@pytest.mark.parametrize("p,degree", [(2, 2), (3, 3), (4, 3)])
+def test_mapped_operator_energy_of_polynomials(p, degree):
+    """mathematical pin of the mapped-cell oracle beyond linear functions: on the affinely mapped quadrant mesh (hanging
+    nodes) a polynomial of degree <= p lies in the FE space, so u^T A u must equal the integral of |grad u|^2 over the
+    parallelepiped, computed here independently by tensor Gauss quadrature in reference coordinates"""
+    from util import AFFINE_A, affine_map
+    maps = ref.LevelMaps.from_dofmap(mg.DoFMap(mg.Mesh("quadrant", 3), p))
+    verts = ref.cell_vertices(maps, affine_map)
+    free = ref.LevelMaps(maps.degree, maps.eval_table & ref.INDEX_MASK, maps.own_table & ref.INDEX_MASK, maps.mask, maps.cell_level,
+                         maps.cell_xyz, np.zeros(0, np.int64), maps.n_dofs)
+    A = ref.assemble_matrix_mapped(free, verts, identity_rows=False)
+    if degree == 2:
+        u = lambda x, y, z: x * x + y * z - 0.5 * z * z + 0.3 * x
+        grad = lambda x, y, z: np.stack([2 * x + 0.3, z, y - z], axis=-1)
+    else:
+        u = lambda x, y, z: x ** 3 - 3 * x * y * y + 0.2 * y * z * z + z
+        grad = lambda x, y, z: np.stack([3 * x * x - 3 * y * y, -6 * x * y + 0.2 * z * z, 0.4 * y * z + 1.0], axis=-1)
+    xyz = affine_map(maps.dof_coordinates())
+    uh = u(xyz[:, 0], xyz[:, 1], xyz[:, 2])
+    boundary = np.nonzero(np.any(np.abs(np.abs(maps.dof_coordinates()) - 1.0) < 1e-12, axis=1))[0]
+    uh[np.setdiff1d(maps.constrained, boundary)] = 0.0                               # hanging DoFs are slaves of the constraints
+    g, w = np.polynomial.legendre.leggauss(6)                                       # exact up to degree 11 per direction
+    X = np.stack(np.meshgrid(g, g, g, indexing="ij"), axis=-1).reshape(-1, 3)
+    W = np.einsum("a,b,c->abc", w, w, w).ravel()
+    P = affine_map(X)
+    G = grad(P[:, 0], P[:, 1], P[:, 2])
+    exact = abs(np.linalg.det(AFFINE_A)) * np.sum(W * np.einsum("qd,qd->q", G, G))
+    assert uh @ (A @ uh) == pytest.approx(exact, rel=1e-11)
