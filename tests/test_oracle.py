@@ -334,3 +334,32 @@ def test_mapped_operator_energy_of_polynomials(p, degree):
     G = grad(P[:, 0], P[:, 1], P[:, 2])
     exact = abs(np.linalg.det(AFFINE_A)) * np.sum(W * np.einsum("qd,qd->q", G, G))
     assert uh @ (A @ uh) == pytest.approx(exact, rel=1e-11)
+
+
+@pytest.mark.parametrize("L,p,rtol", [(2, 4, 2e-6), (2, 6, 5e-7), (3, 3, 5e-7)])
+def test_known_answer_centre_value_of_the_constant_load_problem(L, p, rtol):
+    """known-answer pin of operator + right-hand side + Dirichlet constraints (SimulationType=Constant: -Laplace u = 1,
+    u = 0 on the boundary of [-1,1]^3, multigrid_throughput.cc:2286-2312): u(0) = 4 * 0.0562128..., the classical
+    Fourier-series value for the unit cube sum_{l,m,n odd} 64 (-1)^((l+m+n-3)/2) / (pi^5 l m n (l^2+m^2+n^2))"""
+    k = np.arange(1, 400, 2)
+    s = (-1.0) ** ((k - 1) // 2)
+    l, m, n = np.meshgrid(k, k, k, indexing="ij", sparse=True)
+    sl, sm, sn = np.meshgrid(s, s, s, indexing="ij", sparse=True)
+    exact = 4.0 * 64.0 / np.pi ** 5 * np.sum(sl * sm * sn / (l * m * n * (l * l + m * m + n * n)))
+    assert exact == pytest.approx(4 * 0.0562128, rel=2e-6)
+    maps = ref.LevelMaps.from_dofmap(mg.DoFMap(mg.Mesh("hypercube", L), p))
+    u = spla.spsolve(ref.assemble_matrix(maps).tocsc(), ref.assemble_rhs_constant(maps))
+    centre = np.argmin(np.abs(maps.dof_coordinates()).sum(axis=1))
+    assert np.abs(maps.dof_coordinates()[centre]).max() == 0.0
+    assert u[centre] == pytest.approx(exact, rel=rtol)
+
+
+def test_known_answer_through_the_multigrid_cg_solve():
+    """the same known answer through the whole oracle pipeline of multigrid_throughput (V-cycle-preconditioned CG with
+    Chebyshev(3), coarse CG, relative tolerance 1e-4): 4 iterations, centre value within 2e-5 of the series value"""
+    from util import make_oracle
+    H = make_oracle("hypercube", 3, 3, "HMG-global", 3, "cg")
+    x, its, _ = H.solve(ref.assemble_rhs_constant(H.fine_maps).copy())
+    centre = np.argmin(np.abs(H.fine_maps.dof_coordinates()).sum(axis=1))
+    assert its == 4
+    assert x[centre] == pytest.approx(4 * 0.0562128268, rel=2e-5)
