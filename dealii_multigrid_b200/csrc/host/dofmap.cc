@@ -201,6 +201,13 @@ namespace mgb
             dof_begin[r++] = next;
           const Cell &c     = mesh.cells[i];
           int64_t    *local = (i >= l_begin && i < l_end) ? &g_own[size_t(i - l_begin) * 27] : nullptr;
+          if (i + 1 < nc) // the next cell's slots arrive while this cell is numbered
+            {
+              const Cell &cn = mesh.cells[i + 1];
+              for (int e = 0; e < 27; ++e)
+                if (esize[e] != 0)
+                  ent.prefetch(K(cn.level, cn.x, cn.y, cn.z, e));
+            }
           for (int k = 0; k < 27; ++k)
             {
               const int e = ENTITY_ORDER[k];

@@ -19,8 +19,7 @@ namespace mgb
 
   void FlatMap::clear()
   {
-    keys_.clear();
-    vals_.clear();
+    slots_.clear();
     n_    = 0;
     mask_ = 0;
   }
@@ -28,47 +27,43 @@ namespace mgb
   void FlatMap::reserve(size_t n)
   {
     size_t cap = 16;
-    while (cap < 2 * n + 2)
+    while (cap < n + n / 2 + 2) // load factor <= 2/3 (linear probing, 16-byte slots)
       cap <<= 1;
-    if (cap <= keys_.size())
+    if (cap <= slots_.size())
       return;
-    std::vector<uint64_t> ok;
-    std::vector<int64_t>  ov;
-    ok.swap(keys_);
-    ov.swap(vals_);
-    keys_.assign(cap, ~uint64_t(0));
-    vals_.assign(cap, -1);
+    std::vector<Slot> old;
+    old.swap(slots_);
+    slots_.assign(cap, Slot{~uint64_t(0), -1});
     mask_ = cap - 1;
     n_    = 0;
-    for (size_t i = 0; i < ok.size(); ++i)
-      if (ok[i] != ~uint64_t(0))
-        insert(ok[i], ov[i]);
+    for (const Slot &sl : old)
+      if (sl.key != ~uint64_t(0))
+        insert(sl.key, sl.val);
   }
 
   void FlatMap::grow() { reserve(std::max<size_t>(16, 2 * n_ + 8)); }
 
   void FlatMap::insert(uint64_t key, int64_t value)
   {
-    if (keys_.empty() || 2 * (n_ + 1) > keys_.size())
+    if (slots_.empty() || 3 * (n_ + 1) > 2 * slots_.size())
       grow();
     size_t i = hash(key) & mask_;
-    while (keys_[i] != ~uint64_t(0) && keys_[i] != key)
+    while (slots_[i].key != ~uint64_t(0) && slots_[i].key != key)
       i = (i + 1) & mask_;
-    if (keys_[i] != key)
+    if (slots_[i].key != key)
       ++n_;
-    keys_[i] = key;
-    vals_[i] = value;
+    slots_[i] = Slot{key, value};
   }
 
   int64_t FlatMap::find(uint64_t key) const
   {
-    if (keys_.empty())
+    if (slots_.empty())
       return -1;
     size_t i = hash(key) & mask_;
-    while (keys_[i] != ~uint64_t(0))
+    while (slots_[i].key != ~uint64_t(0))
       {
-        if (keys_[i] == key)
-          return vals_[i];
+        if (slots_[i].key == key)
+          return slots_[i].val;
         i = (i + 1) & mask_;
       }
     return -1;

@@ -23,14 +23,25 @@ namespace mgb
     int64_t find(uint64_t key) const; // -1 if absent
     size_t  size() const { return n_; }
     void    clear();
+    // hint that `key` is looked up or inserted soon: the big tables of the setup are random-access bound, and the 27
+    // entities of a cell can be requested together
+    void prefetch(uint64_t key) const
+    {
+      if (!slots_.empty())
+        __builtin_prefetch(&slots_[hash(key) & mask_]);
+    }
 
   private:
-    static uint64_t      hash(uint64_t k);
-    void                 grow();
-    std::vector<uint64_t> keys_;
-    std::vector<int64_t>  vals_;
-    size_t                n_    = 0;
-    size_t                mask_ = 0;
+    struct Slot // key and value share a cache line
+    {
+      uint64_t key;
+      int64_t  val;
+    };
+    static uint64_t   hash(uint64_t k);
+    void              grow();
+    std::vector<Slot> slots_;
+    size_t            n_    = 0;
+    size_t            mask_ = 0;
   };
 
   struct Cell
