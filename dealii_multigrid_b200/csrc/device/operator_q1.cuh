@@ -603,33 +603,39 @@ namespace mgb
                 u3[r * 32] = gb[r];
               }
             // metric at the n^2 points of the plane
+            // MT: arithmetic type of the metric (FP64; -DMGB_Q1_FLOAT_METRIC: FP32 in the float kernels, an experiment)
+#ifdef MGB_Q1_FLOAT_METRIC
+            using MT = T;
+#else
+            using MT = double;
+#endif
             const double *c  = cf + cl * 24;
-            const double  wz = c_feq[P].wq[t];
-            double        A0[3], A1[3], B0[3];
+            const MT      wz = MT(c_feq[P].wq[t]);
+            MT            A0[3], A1[3], B0[3];
 #pragma unroll
             for (int d = 0; d < 3; ++d)
               {
-                A0[d] = c[1 * 3 + d] + c[5 * 3 + d] * zeta; // d x_d / d xi   = A0 + A1 eta
-                A1[d] = c[3 * 3 + d] + c[7 * 3 + d] * zeta;
-                B0[d] = c[2 * 3 + d] + c[6 * 3 + d] * zeta; // d x_d / d eta  = B0 + A1 xi
+                A0[d] = MT(c[1 * 3 + d]) + MT(c[5 * 3 + d]) * MT(zeta); // d x_d / d xi   = A0 + A1 eta
+                A1[d] = MT(c[3 * 3 + d]) + MT(c[7 * 3 + d]) * MT(zeta);
+                B0[d] = MT(c[2 * 3 + d]) + MT(c[6 * 3 + d]) * MT(zeta); // d x_d / d eta  = B0 + A1 xi
               }
 #pragma unroll 1
             for (int j = 0; j < n; ++j) // rolled: the gradients of the plane live in shared memory
               {
-                const double eta = c_feq[P].xq[j];
-                double       J0[3], E0[3], F0[3];
+                const MT eta = MT(c_feq[P].xq[j]);
+                MT       J0[3], E0[3], F0[3];
 #pragma unroll
                 for (int d = 0; d < 3; ++d)
                   {
                     J0[d] = A0[d] + A1[d] * eta;
-                    E0[d] = c[4 * 3 + d] + c[6 * 3 + d] * eta; // d x_d / d zeta = E0 + F0 xi
-                    F0[d] = c[5 * 3 + d] + c[7 * 3 + d] * eta;
+                    E0[d] = MT(c[4 * 3 + d]) + MT(c[6 * 3 + d]) * eta; // d x_d / d zeta = E0 + F0 xi
+                    F0[d] = MT(c[5 * 3 + d]) + MT(c[7 * 3 + d]) * eta;
                   }
 #pragma unroll
                 for (int i = 0; i < n; ++i)
                   {
-                    const double xi = c_feq[P].xq[i];
-                    double       J1[3], J2[3];
+                    const MT xi = MT(c_feq[P].xq[i]);
+                    MT       J1[3], J2[3];
 #pragma unroll
                     for (int d = 0; d < 3; ++d)
                       {
@@ -637,24 +643,24 @@ namespace mgb
                         J2[d] = E0[d] + F0[d] * xi;
                       }
                     // J[c][0] = J0[c], J[c][1] = J1[c], J[c][2] = J2[c]; cofactors C[c][d]
-                    const double C00 = J1[1] * J2[2] - J2[1] * J1[2], C01 = J2[1] * J0[2] - J0[1] * J2[2],
-                                 C02 = J0[1] * J1[2] - J1[1] * J0[2];
-                    const double C10 = J2[0] * J1[2] - J1[0] * J2[2], C11 = J0[0] * J2[2] - J2[0] * J0[2],
-                                 C12 = J1[0] * J0[2] - J0[0] * J1[2];
-                    const double C20 = J1[0] * J2[1] - J2[0] * J1[1], C21 = J2[0] * J0[1] - J0[0] * J2[1],
-                                 C22 = J0[0] * J1[1] - J1[0] * J0[1];
-                    const double det = J0[0] * C00 + J1[0] * C01 + J2[0] * C02;
+                    const MT C00 = J1[1] * J2[2] - J2[1] * J1[2], C01 = J2[1] * J0[2] - J0[1] * J2[2],
+                             C02 = J0[1] * J1[2] - J1[1] * J0[2];
+                    const MT C10 = J2[0] * J1[2] - J1[0] * J2[2], C11 = J0[0] * J2[2] - J2[0] * J0[2],
+                             C12 = J1[0] * J0[2] - J0[0] * J1[2];
+                    const MT C20 = J1[0] * J2[1] - J2[0] * J1[1], C21 = J2[0] * J0[1] - J0[0] * J2[1],
+                             C22 = J0[0] * J1[1] - J1[0] * J0[1];
+                    const MT det = J0[0] * C00 + J1[0] * C01 + J2[0] * C02;
 #ifndef MGB_Q1_EXACT_DIV
-                    double rdet = double(1.0f / float(det)); // two Newton steps: 6e-8 -> 4e-15 -> 1e-29 relative
-                    rdet        = rdet * (2.0 - det * rdet);
-                    rdet        = rdet * (2.0 - det * rdet);
-                    const double s = c_feq[P].wq[i] * c_feq[P].wq[j] * wz * rdet;
+                    MT rdet = MT(1.0f / float(det));     // two Newton steps: 6e-8 -> 4e-15 -> 1e-29 relative
+                    rdet        = rdet * (MT(2) - det * rdet);
+                    rdet        = rdet * (MT(2) - det * rdet);
+                    const MT s = MT(c_feq[P].wq[i] * c_feq[P].wq[j]) * wz * rdet;
 #else
-                    const double s = c_feq[P].wq[i] * c_feq[P].wq[j] * wz / det;
+                    const MT s = MT(c_feq[P].wq[i] * c_feq[P].wq[j]) * wz / det;
 #endif
                     const int    r   = j * n + i;
-                    const double g0 = double(p1[r]), g1 = double(u3[r * 32]), g2 = double(p2[r]);
-                    const double p0 = C00 * g0 + C01 * g1 + C02 * g2, p1v = C10 * g0 + C11 * g1 + C12 * g2,
+                    const MT g0 = MT(p1[r]), g1 = MT(u3[r * 32]), g2 = MT(p2[r]);
+                    const MT p0 = C00 * g0 + C01 * g1 + C02 * g2, p1v = C10 * g0 + C11 * g1 + C12 * g2,
                                  p2v = C20 * g0 + C21 * g1 + C22 * g2;
                     p1[r] = T(s * (C00 * p0 + C10 * p1v + C20 * p2v));
                     u3[r * 32] = T(s * (C01 * p0 + C11 * p1v + C21 * p2v));

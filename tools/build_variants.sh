@@ -2,8 +2,8 @@
 # build_variants.sh "tag:flags" ... -- build kernel variants of libmgb200.so HERE (nvcc cross-compiles, in parallel), one per
 # argument, into variants/libmgb200_<tag>.so (git-ignored, travels to the GPU box with gpurun).  flags are extra nvcc
 # options, typically the -D switches of the cell kernels:
-#   -DMGB_SLAB_W=<warps per block> -DMGB_SLAB_MINB=<blocks per SM> -DMGB_SLAB_LOCKSTEP            (operator.cuh)
-#   -DMGB_Q1_W= -DMGB_Q1_MINB= -DMGB_Q1_NO_LOCKSTEP -DMGB_Q1_REG_METRIC -DMGB_Q1_EXACT_DIV         (operator_q1.cuh)
+#   -DMGB_SLAB_W=<warps per block> -DMGB_SLAB_MINB=<blocks per SM> -DMGB_SLAB_LOCKSTEP -DMGB_SLAB_ABLATE=1|2|3   (operator.cuh)
+#   -DMGB_Q1_W= -DMGB_Q1_MINB= -DMGB_Q1_NO_LOCKSTEP -DMGB_Q1_REG_METRIC -DMGB_Q1_EXACT_DIV -DMGB_Q1_FLOAT_METRIC   (operator_q1.cuh)
 # Then, in ONE gpurun call:  tools/time_variants.sh <tag> ... [-- time_vmult.py options]
 # example: tools/build_variants.sh "lock:-DMGB_SLAB_LOCKSTEP" "w8:-DMGB_SLAB_W=8 -DMGB_SLAB_MINB=1"
 set -e

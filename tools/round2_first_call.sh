@@ -4,7 +4,7 @@
 #   here, before the call:   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o tools/bench_bulk tools/bench_bulk.cu
 #                            nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o tools/bench_bulk_cells tools/bench_bulk_cells.cu
 #                            python tools/span_table.py --nref 6        (writes tools/spans_L6_p4.bin, 63 MB)
-#                            tools/build_variants.sh "lock:-DMGB_SLAB_LOCKSTEP" "q1minb3:-DMGB_Q1_MINB=3" "q1nolock:-DMGB_Q1_NO_LOCKSTEP" \
+#                            tools/build_variants.sh "lock:-DMGB_SLAB_LOCKSTEP" "q1minb3:-DMGB_Q1_MINB=3" "q1nolock:-DMGB_Q1_NO_LOCKSTEP" "q1fm:-DMGB_Q1_FLOAT_METRIC" \
 #                                "abl1:-DMGB_SLAB_ABLATE=1" "abl2:-DMGB_SLAB_ABLATE=2" "abl3:-DMGB_SLAB_ABLATE=3"
 #   gpurun --timeout 400 -- tools/round2_first_call.sh
 # 1. short bulk copies / f64 bulk reduce-add per SM (does the TMA path carry a cell's ~10+10 spans?)
@@ -22,6 +22,9 @@ for p in 4 3; do
   tools/time_variants.sh q1minb3 q1nolock -- --nref 6 --degree $p --deform smooth --reps 20 > $O/r2a_variants_q1_p$p.log 2>&1
   mv $O/variants_time.txt $O/r2a_variants_q1_p${p}_time.txt
 done
+# 3b. float kernels with the metric in FP32 (parity tolerance of the float test: 2e-5)
+tools/time_variants.sh q1fm -- --nref 6 --degree 4 --number float --deform smooth --reps 20 > $O/r2a_variants_q1_float.log 2>&1
+mv $O/variants_time.txt $O/r2a_variants_q1_float_time.txt
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:k_laplace_q1_slab --launch-skip 3 -c 1 -f -o $O/r2a_q1_slab_L6 \
   python tools/time_vmult.py --nref 6 --degree 4 --deform smooth --reps 2 > $O/r2a_ncu_q1.log 2>&1; echo "ncu rc=$?"
 tail -n 30 $O/r2a_bench_bulk.txt $O/r2a_bench_bulk_cells.txt $O/r2a_variants_vmult_time.txt $O/r2a_ablation_time.txt $O/r2a_variants_q1_p4_time.txt
