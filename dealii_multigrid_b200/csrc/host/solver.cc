@@ -281,6 +281,16 @@ namespace mgb
         }
       ctab_.upload(rec.data(), rec.size());
     }
+    if (any_hanging && std::getenv("MGB_SPLIT_HANGING") && std::string(std::getenv("MGB_SPLIT_HANGING")) == "1")
+      {
+        // experiment: two launches per cell loop, the cells without hanging-node constraints on the kernel's fast path
+        // (a warp takes the shared-memory detour as soon as ONE of its cells has a constrained face or edge)
+        std::vector<uint32_t> plain, hanging;
+        for (long long c = 0; c < s.n_cells; ++c)
+          ((s.mask[c] >> 3) ? hanging : plain).push_back(uint32_t(c));
+        plain_cells_.upload(plain.data(), plain.size());
+        hanging_cells_.upload(hanging.data(), hanging.size());
+      }
     cd_.ctab        = ctab_.ptr;
     cd_.degree      = s.degree;
     cd_.n_cells     = s.n_cells;
@@ -356,7 +366,15 @@ namespace mgb
     else
       {
         c.prof_begin(cd_.n_cells);
-        cell_laplace_apply<T>(cd, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
+        if (plain_cells_.n > 0 && hanging_cells_.n > 0)
+          {
+            CellData cp    = cd;
+            cp.any_hanging = 0;
+            cell_laplace_apply<T>(cp, src.data, dst.data, plain_cells_.ptr, (long long)plain_cells_.n, c.stream), ++c.launches;
+            cell_laplace_apply<T>(cd, src.data, dst.data, hanging_cells_.ptr, (long long)hanging_cells_.n, c.stream), ++c.launches;
+          }
+        else
+          cell_laplace_apply<T>(cd, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
         c.prof_end(cd_.n_cells);
       }
     dst.compress_add();

@@ -415,6 +415,7 @@ namespace mgb
     DeviceBuffer<uint32_t>             constrained_, edge_, edge_cells_;
     // several ranks: cells that read ghost entries (boundary) and the others (interior), for overlapping the exchange
     DeviceBuffer<uint32_t>             boundary_cells_, interior_cells_;
+    DeviceBuffer<uint32_t>             plain_cells_, hanging_cells_; // MGB_SPLIT_HANGING=1: cells without / with hanging-node constraints
     mutable DeviceBuffer<T>            edge_src_vals_;
     mutable DVec<T>                    src_copy_;
     bool                               has_edge_global_ = false;

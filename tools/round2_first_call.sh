@@ -22,6 +22,12 @@ for p in 4 3; do
   tools/time_variants.sh q1minb3 q1nolock -- --nref 6 --degree $p --deform smooth --reps 20 > $O/r2a_variants_q1_p$p.log 2>&1
   mv $O/variants_time.txt $O/r2a_variants_q1_p${p}_time.txt
 done
+# 2c. locally refined mesh: cells with hanging-node constraints in a launch of their own (MGB_SPLIT_HANGING=1)
+for v in 0 1; do
+  echo "MGB_SPLIT_HANGING=$v" >> $O/r2a_split_hanging.txt
+  MGB_SPLIT_HANGING=$v timeout 120 python tools/time_vmult.py --geometry quadrant --nref 7 --degree 4 --reps 50 >> $O/r2a_split_hanging.txt 2>&1
+done
+MGB_SPLIT_HANGING=1 timeout 300 python -m pytest tests -m gpu -q -x > $O/r2a_split_hanging_pytest.log 2>&1; echo "split-hanging pytest rc=$? $(tail -1 $O/r2a_split_hanging_pytest.log)"
 # 3b. float kernels with the metric in FP32 (parity tolerance of the float test: 2e-5)
 tools/time_variants.sh q1fm -- --nref 6 --degree 4 --number float --deform smooth --reps 20 > $O/r2a_variants_q1_float.log 2>&1
 mv $O/variants_time.txt $O/r2a_variants_q1_float_time.txt
