@@ -1,12 +1,12 @@
 #!/bin/bash
 # round2_first_call.sh -- the measurements queued at the end of round 1 (no GPU minutes were left), to be run as the FIRST
-# gpurun call of the next round (about 4 minutes of box time):
+# gpurun call of the next round (about 7 minutes of box time):
 #   here, before the call:   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o tools/bench_bulk tools/bench_bulk.cu
 #                            nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o tools/bench_bulk_cells tools/bench_bulk_cells.cu
 #                            python tools/span_table.py --nref 6        (writes tools/spans_L6_p4.bin, 63 MB)
 #                            tools/build_variants.sh "lock:-DMGB_SLAB_LOCKSTEP" "q1minb3:-DMGB_Q1_MINB=3" "q1nolock:-DMGB_Q1_NO_LOCKSTEP" "q1fm:-DMGB_Q1_FLOAT_METRIC" \
 #                                "abl1:-DMGB_SLAB_ABLATE=1" "abl2:-DMGB_SLAB_ABLATE=2" "abl3:-DMGB_SLAB_ABLATE=3"
-#   gpurun --timeout 400 -- tools/round2_first_call.sh
+#   gpurun --timeout 700 -- tools/round2_first_call.sh
 # 1. short bulk copies / f64 bulk reduce-add per SM (does the TMA path carry a cell's ~10+10 spans?)
 # 2. block-lockstep variant of the Cartesian vmult kernel against the default (L=7 p=4), with the operator parity tests
 # 3. general-geometry kernel: MIN_BLOCKS=3 and no-lockstep variants at p=3 and p=4, and an ncu capture of the default
