@@ -84,3 +84,60 @@ def test_two_rank_ghost_exchange_over_gloo(geometry, L, p):
     assert sum(r[2] for r in res.values()) > 0 and any(r[3] > 0 for r in res.values())  # somebody has ghosts
     for err, dot_err, _, _ in res.values():
         assert err < 1e-13 and dot_err < 1e-13
+
+
+def _transfer_worker(rank, world, port, geometry, L, p, out):
+    """the two-level transfer's internal ghosted fine vector (MGTwoLevelTransfer keeps its own partitioner: a rank's coarse
+    cells may have children owned by the other rank): ghost update and compress(add) over gloo with the transfer map's tables"""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import dealii_multigrid_b200 as mg
+    from util import mesh_sequence, seeded
+    seq = mesh_sequence(geometry, L)
+    mf, mc = seq[-1], seq[-2]
+    df, dc = mg.DoFMap(mf, p, world, rank), mg.DoFMap(mc, p, world, rank)
+    tm = mg.TransferMap(mf, df, mc, dc)
+    P = tm.partitioner()
+    n_owned, n_ghost = P["n_owned"], P["n_ghost"]
+    x_global = seeded(df.n_dofs_global)
+    x = np.zeros(n_owned + n_ghost)
+    x[:n_owned] = x_global[P["owned_begin"]:P["owned_begin"] + n_owned]
+    io, go = P["import_offsets"].astype(int), P["ghost_offsets"].astype(int)
+    send = [x[P["import_indices"][io[i]:io[i + 1]]] for i in range(len(P["import_ranks"]))]
+    got = _exchange(P, send, [go[j + 1] - go[j] for j in range(len(P["ghost_ranks"]))], P["import_ranks"], P["ghost_ranks"])
+    for j, g in enumerate(got):
+        x[n_owned + go[j]:n_owned + go[j + 1]] = g
+    ghost_ok = np.array_equal(x[n_owned:], x_global[P["ghost_global"]])
+    # compress(add): every rank adds 1 to each entry its coarse cells' patches touch (owned or ghost); after the exchange an
+    # owned entry holds the number of ranks touching it, and the global sum equals the sum of the ranks' touched counts
+    touched = np.zeros(n_owned + n_ghost)
+    own = tm.fine_own()
+    esize = np.array([(p - 1) ** ((e % 3 == 1) + ((e // 3) % 3 == 1) + (e // 9 == 1)) for e in range(27)])
+    for e in range(27):
+        for k in range(esize[e]):
+            touched[(own[:, e] & mg.INDEX_MASK) + k] = 1.0
+    n_touched = float(touched.sum())
+    send = [touched[n_owned + go[j]:n_owned + go[j + 1]] for j in range(len(P["ghost_ranks"]))]
+    got = _exchange(P, send, [io[i + 1] - io[i] for i in range(len(P["import_ranks"]))], P["ghost_ranks"], P["import_ranks"])
+    y = touched[:n_owned].copy()
+    for i, g in enumerate(got):
+        np.add.at(y, P["import_indices"][io[i]:io[i + 1]], g)
+    t = torch.tensor([float(y.sum()), n_touched], dtype=torch.float64)
+    dist.all_reduce(t)
+    out[rank] = (bool(ghost_ok), float(t[0]), float(t[1]), float(y.max()), int(n_ghost))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("geometry,L,p", [("hypercube", 2, 2), ("quadrant", 4, 2)])
+def test_two_rank_transfer_partitioner_over_gloo(geometry, L, p):
+    world = 2
+    with mp.Manager() as m:
+        out = m.dict()
+        mp.spawn(_transfer_worker, args=(world, _free_port(), geometry, L, p, out), nprocs=world, join=True)
+        res = dict(out)
+    assert set(res) == {0, 1}
+    assert any(r[4] > 0 for r in res.values())                        # the transfer really needs fine values of the other rank
+    for ghost_ok, total, touched, ymax, _ in res.values():
+        assert ghost_ok and total == touched and ymax <= world
