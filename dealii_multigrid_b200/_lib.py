@@ -130,6 +130,7 @@ SIGNATURES = {
     "mgb_problem_statistics": (C.c_int, [P, C.POINTER(Statistics), C.POINTER(C.c_int64)]),
     "mgb_dofmap_view_get": (C.c_int, [P, C.POINTER(DofmapView)]),
     "mgb_dofmap_expand": (C.c_int, [P, C.c_int, c_u32p]),
+    "mgb_dofmap_chunk_plan_check": (C.c_int, [P, C.c_int, C.POINTER(C.c_double)]),
     "mgb_dofmap_destroy": (None, [P]),
     "mgb_transfer_map_create": (C.c_int, [P, P, P, P, PP]),
     "mgb_transfer_map_create_ls": (C.c_int, [P, P, P, P, PP]),

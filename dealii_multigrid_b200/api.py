@@ -277,6 +277,15 @@ class DoFMap:
         _check(self._lib.mgb_dofmap_expand(self._h, 0 if which == "eval" else 1, out.ctypes.data_as(_lib.c_u32p)))
         return out
 
+    def chunk_plan_check(self, value_bytes=8):
+        """host-only check of the cell loop's chunk plan (host/chunks.h): dict with the deviation of the CPU walk through
+        the plan from the direct scatter-add and the plan's statistics"""
+        st = (C.c_double * 11)()
+        _check(self._lib.mgb_dofmap_chunk_plan_check(self._h, value_bytes, st))
+        keys = ("max_err", "n_chunks", "n_compute_tables", "n_pull_tables", "table_words", "foreign_low", "foreign_late",
+                "foreign_ghost", "side_entries", "max_slots", "build_seconds")
+        return dict(zip(keys, [float(x) for x in st]))
+
     def __del__(self):
         if getattr(self, "_h", None) and not self._borrowed:
             self._lib.mgb_dofmap_destroy(self._h)

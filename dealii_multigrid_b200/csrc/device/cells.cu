@@ -2,6 +2,7 @@
 #include "../host/fe1d.h"
 #include "operator.cuh"
 #include "operator_q1.cuh"
+#include "chunk.cuh"
 #include "transfer.cuh"
 
 #include <mutex>
@@ -122,6 +123,53 @@ namespace mgb
       }
     DISPATCH_DEGREE(cd.degree, (launch_apply<P, T>(cd, src, dst, cell_list, n_list, s)));
   }
+  template <typename T>
+  void cell_laplace_chunked(const CellData &cd, const ChunkDevice &ch, const T *x, T *out, const FusedEpilogue<T> &ep, cudaStream_t s)
+  {
+    if (cd.vertices)
+      throw std::runtime_error("cell_laplace_chunked: Cartesian cells only");
+    ChunkArgs<T> a;
+    a.n_chunks    = ch.n_chunks;
+    a.desc        = ch.desc;
+    a.pool        = ch.pool;
+    a.deps        = ch.deps;
+    a.ghost_idx   = ch.ghost_idx;
+    a.side        = static_cast<T *>(ch.side);
+    a.flags       = ch.flags;
+    a.state       = ch.state;
+    a.root_length = cd.root_length;
+    a.src         = x;
+    a.out         = out;
+    a.mode        = ep.mode;
+    a.b           = ep.b;
+    a.dinv        = ep.dinv;
+    a.xold        = ep.xold;
+    a.f1          = ep.f1;
+    a.f2          = ep.f2;
+    DISPATCH_DEGREE(cd.degree, (launch_chunks<P, T>(a, s)));
+  }
+  namespace
+  {
+    template <typename T>
+    __global__ void k_idx_fused_identity(T *out, const T *x, const int mode, const T *dinv, const T f2, const uint32_t *idx, uint32_t n)
+    {
+      const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+      if (i < n)
+        {
+          const uint32_t g = idx[i];
+          const T        coef = mode == 0 ? T(1) : (mode == 1 ? T(-1) : -f2 * dinv[g]);
+          out[g] += coef * x[g];
+        }
+    }
+  } // namespace
+  template <typename T>
+  void idx_fused_identity(T *out, const T *x, const FusedEpilogue<T> &ep, const uint32_t *idx, uint32_t n, cudaStream_t s)
+  {
+    if (n == 0)
+      return;
+    k_idx_fused_identity<T><<<(n + 255) / 256, 256, 0, s>>>(out, x, ep.mode, ep.dinv, ep.f2, idx, n);
+    MGB_CUDA(cudaGetLastError());
+  }
   template <typename T> void cell_laplace_diagonal(const CellData &cd, T *diag, cudaStream_t s)
   {
     if (cd.vertices)
@@ -142,6 +190,10 @@ namespace mgb
 
   template void cell_laplace_apply<double>(const CellData &, const double *, double *, const uint32_t *, long long, cudaStream_t);
   template void cell_laplace_apply<float>(const CellData &, const float *, float *, const uint32_t *, long long, cudaStream_t);
+  template void cell_laplace_chunked<double>(const CellData &, const ChunkDevice &, const double *, double *, const FusedEpilogue<double> &, cudaStream_t);
+  template void cell_laplace_chunked<float>(const CellData &, const ChunkDevice &, const float *, float *, const FusedEpilogue<float> &, cudaStream_t);
+  template void idx_fused_identity<double>(double *, const double *, const FusedEpilogue<double> &, const uint32_t *, uint32_t, cudaStream_t);
+  template void idx_fused_identity<float>(float *, const float *, const FusedEpilogue<float> &, const uint32_t *, uint32_t, cudaStream_t);
   template void cell_laplace_diagonal<double>(const CellData &, double *, cudaStream_t);
   template void cell_laplace_diagonal<float>(const CellData &, float *, cudaStream_t);
   template void transfer_prolongate_add<double>(const TransferData &, double *, const double *, cudaStream_t);

@@ -99,6 +99,31 @@ namespace mgb
   template <typename T>
   void cell_laplace_apply(const CellData &cd, const T *src, T *dst, const uint32_t *cell_list, long long n_list,
                           cudaStream_t s);
+  // Chunked cell loop (device/chunk.cuh, plan: host/chunks.h): out = E(A src) on the owned range with plain stores, E the
+  // epilogue below; contributions to ghost entries are added atomically to the ghost tail of out (must be zero on entry).
+  struct ChunkDevice
+  {
+    uint32_t        n_chunks  = 0;
+    const uint32_t *desc      = nullptr, *pool = nullptr, *deps = nullptr, *ghost_idx = nullptr;
+    void           *side      = nullptr; // side buffer (value type of the operator)
+    uint32_t       *flags     = nullptr; // 2 * n_chunks
+    uint32_t       *state     = nullptr; // 4 words: ticket, epoch, finished blocks
+  };
+  // mode 0: out = A x;  1: out = b - A x;  2: out = (1+f1) x + f2 dinv (b - A x);  3: out = (1+f1) x - f1 xold + f2 dinv (b - A x)
+  // (the Chebyshev updates of cheb_update with t = A x); out may alias xold, never x
+  template <typename T> struct FusedEpilogue
+  {
+    int      mode = 0;
+    const T *b = nullptr, *dinv = nullptr, *xold = nullptr;
+    T        f1 = T(0), f2 = T(0);
+  };
+  template <typename T>
+  void cell_laplace_chunked(const CellData &cd, const ChunkDevice &ch, const T *x, T *out, const FusedEpilogue<T> &ep, cudaStream_t s);
+  // out[idx[i]] += coef(idx[i]) * x[idx[i]]: the identity rows of the constrained DoFs after a fused cell loop (coef as the
+  // epilogue applies it to A x: 1, -1, -f2 dinv)
+  template <typename T>
+  void idx_fused_identity(T *out, const T *x, const FusedEpilogue<T> &ep, const uint32_t *idx, uint32_t n, cudaStream_t s);
+
   // diag += diag(C^T A_e C) cell-wise (MatrixFreeTools::compute_diagonal)
   template <typename T> void cell_laplace_diagonal(const CellData &cd, T *diag, cudaStream_t s);
 

@@ -1,10 +1,12 @@
 // extern "C" boundary (include/mgb200.h): plain pointers and sizes in, opaque handles out.
 #include "mgb200.h"
 
+#include "chunks.h"
 #include "comm.h"
 #include "partition.h"
 #include "problem.h"
 
+#include <chrono>
 #include <cstring>
 #include <map>
 
@@ -440,6 +442,26 @@ int mgb_dofmap_expand(const mgb_dofmap *h, int which, uint32_t *out)
     std::vector<uint32_t> tmp;
     h->d->expand(which == 0 ? h->d->eval_table : h->d->own_table, tmp);
     std::memcpy(out, tmp.data(), tmp.size() * sizeof(uint32_t));
+  });
+}
+int mgb_dofmap_chunk_plan_check(const mgb_dofmap *h, int value_bytes, double *stats)
+{
+  return guarded([&] {
+    const DoFMap   &d    = *h->d;
+    const auto      t0   = std::chrono::steady_clock::now();
+    const ChunkPlan plan = build_chunk_plan(d.degree, d.n_cells, d.eval_table.data(), d.mask.data(), d.cell_level.data(), d.part.n_owned,
+                                            d.part.n_ghost, value_bytes, d.cell_begin);
+    stats[10] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    stats[0] = check_chunk_plan(plan, d.n_cells, d.eval_table.data(), d.part.n_owned, d.part.n_ghost);
+    stats[1] = plan.n_chunks;
+    stats[2] = plan.n_compute_blobs;
+    stats[3] = plan.n_pull_blobs;
+    stats[4] = double(plan.pool.size());
+    stats[5] = double(plan.n_foreign_low);
+    stats[6] = double(plan.n_foreign_late);
+    stats[7] = double(plan.n_foreign_ghost);
+    stats[8] = double(plan.side_size);
+    stats[9] = plan.max_slots;
   });
 }
 void mgb_dofmap_destroy(mgb_dofmap *d) { delete d; }

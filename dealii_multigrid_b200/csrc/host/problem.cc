@@ -365,6 +365,7 @@ namespace mgb
       s.n_constrained = (uint32_t)dm.constrained.size();
       s.n_dofs_global = dm.part.n_global;
       s.partitioner   = &dm.part;
+      s.first_cell_global = dm.cell_begin;
       return s;
     }
 

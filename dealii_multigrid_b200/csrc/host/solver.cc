@@ -2,6 +2,7 @@
 
 #include <cstdlib>
 
+#include "chunks.h"
 #include "comm.h"
 
 #include <algorithm>
@@ -291,6 +292,47 @@ namespace mgb
         plain_cells_.upload(plain.data(), plain.size());
         hanging_cells_.upload(hanging.data(), hanging.size());
       }
+    {
+      // chunk plan of the cell loop (device/chunk.cuh); MGB_CHUNKED=0 keeps the atomic cell kernel
+      const char *e = std::getenv("MGB_CHUNKED");
+      if (!(e && e[0] == '0') && s.n_cells > 0)
+        try
+          {
+            const ChunkPlan plan = build_chunk_plan(s.degree, s.n_cells, s.entity_table, s.mask, s.cell_level, s.partitioner ? s.partitioner->n_owned : 0u,
+                                                    s.partitioner ? s.partitioner->n_ghost : 0u, (int)sizeof(T), s.first_cell_global);
+            bool deps_fit = true;
+            for (uint32_t k = 0; k < plan.n_chunks && deps_fit; ++k)
+              {
+                const uint32_t *cb = &plan.pool[plan.desc[size_t(k) * CHUNK_DESC_WORDS + CD_BLOB]];
+                const uint32_t *pb = &plan.pool[plan.desc[size_t(k) * CHUNK_DESC_WORDS + CD_PULL_BLOB]];
+                deps_fit = cb[CB_N_DEP_LOW] + cb[CB_N_DEP_LATE] <= 96u && pb[PB_N_DEPS] <= 96u;
+              }
+            if (deps_fit && plan.n_chunks > 0)
+              {
+                ch_desc_.upload(plan.desc.data(), plan.desc.size());
+                ch_pool_.upload(plan.pool.data(), plan.pool.size());
+                ch_deps_.upload(plan.deps.data(), plan.deps.size());
+                ch_ghost_.upload(plan.ghost_idx.data(), plan.ghost_idx.size());
+                ch_side_.alloc(size_t(plan.side_size) + 2);
+                std::vector<uint32_t> zeros(size_t(plan.n_chunks) * 2 + 4, 0u);
+                ch_flags_.upload(zeros.data(), size_t(plan.n_chunks) * 2);
+                ch_state_.upload(zeros.data(), 4);
+                chd_.n_chunks  = plan.n_chunks;
+                chd_.desc      = ch_desc_.ptr;
+                chd_.pool      = ch_pool_.ptr;
+                chd_.deps      = ch_deps_.ptr;
+                chd_.ghost_idx = ch_ghost_.ptr;
+                chd_.side      = ch_side_.ptr;
+                chd_.flags     = ch_flags_.ptr;
+                chd_.state     = ch_state_.ptr;
+                chunked_       = true;
+              }
+          }
+        catch (const std::runtime_error &)
+          {
+            chunked_ = false; // meshes the planner cannot chunk stay on the atomic kernel
+          }
+    }
     cd_.ctab        = ctab_.ptr;
     cd_.degree      = s.degree;
     cd_.n_cells     = s.n_cells;
@@ -355,6 +397,20 @@ namespace mgb
         src.zero_out_ghost_values();
         return;
       }
+    if (zero_dst && !edge_only && alpha == 1.0 && chunk_path_ok(dst.data, src.data))
+      {
+        // chunked cell loop: every owned entry of dst is written once (no zeroing, no atomics); only the contributions to
+        // ghost entries are added atomically to the (zeroed) ghost tail
+        src.update_ghost_values();
+        if (dst.n_ghost)
+          dst.zero_out_ghost_values();
+        c.prof_begin(cd_.n_cells);
+        cell_laplace_chunked<T>(cd, chd_, src.data, dst.data, FusedEpilogue<T>(), c.stream), ++c.launches;
+        c.prof_end(cd_.n_cells);
+        dst.compress_add();
+        src.zero_out_ghost_values();
+        return;
+      }
     src.update_ghost_values();
     if (zero_dst)
       dst.zero();
@@ -379,6 +435,28 @@ namespace mgb
       }
     dst.compress_add();
     src.zero_out_ghost_values();
+  }
+
+  template <typename T> bool OperatorT<T>::chunk_path_ok(const T *out, const T *x) const
+  {
+    return chunked_ && !cd_.vertices && out != x && (reinterpret_cast<uintptr_t>(x) & 15u) == 0;
+  }
+
+  template <typename T> bool OperatorT<T>::fused_available(const DVec<T> &out, const DVec<T> &x) const
+  {
+    return chunk_path_ok(out.data, x.data) && edge_.n == 0 && part_->trivial();
+  }
+
+  template <typename T> void OperatorT<T>::vmult_fused(DVec<T> &out, const DVec<T> &x, const FusedEpilogue<T> &ep) const
+  {
+    if (!fused_available(out, x))
+      throw std::runtime_error("Operator::vmult_fused: not available for this operator");
+    Context &c = ctx();
+    c.prof_begin(cd_.n_cells);
+    cell_laplace_chunked<T>(cd_, chd_, x.data, out.data, ep, c.stream), ++c.launches;
+    c.prof_end(cd_.n_cells);
+    if (constrained_.n)
+      idx_fused_identity<T>(out.data, x.data, ep, constrained_.ptr, (uint32_t)constrained_.n, c.stream), ++c.launches;
   }
 
   template <typename T> void OperatorT<T>::set_cell_vertices(const double *xyz)
@@ -425,6 +503,14 @@ namespace mgb
   template <typename T> void OperatorT<T>::residual_interface_down(DVec<T> &dst, const DVec<T> &b, const DVec<T> &src) const
   {
     Context &c = ctx();
+    if (fused_available(dst, src) && dst.data != b.data)
+      {
+        FusedEpilogue<T> ep;
+        ep.mode = 1;
+        ep.b    = b.data;
+        vmult_fused(dst, src, ep); // dst = b - A src in the cell loop's own pass, identity rows included
+        return;
+      }
     dst.copy_from(b);
     cell_loop(dst, src, false, false, -1.0);
     if (constrained_.n)
@@ -468,6 +554,8 @@ namespace mgb
     , smoothing_range_(smoothing_range)
     , eig_its_(eig_its)
   {
+    const char *e = std::getenv("MGB_FUSE_CHEB");
+    fuse_         = !(e && e[0] == '0');
     op_.compute_inverse_diagonal(dinv_);
   }
 
@@ -542,6 +630,50 @@ namespace mgb
     DVec<T>   *x = &dst, *xo = &solution_old_;
     bool       have_old = false;
     double     rhok = delta_ / theta_, sigma = theta_ / delta_;
+    if (n_updates >= 2 && fuse_ && (temp1_.n_owned != dst.n_owned || temp1_.n_ghost != dst.n_ghost))
+      temp1_.reinit_like(dst);
+    if (n_updates >= 2 && fuse_ && op_.fused_available(solution_old_, dst) && op_.fused_available(dst, solution_old_) &&
+        op_.fused_available(dst, temp1_))
+      {
+        // The vector update runs in the cell loop's own pass (north_star: "the smoother's vector updates fused with
+        // vmult"; deal.II: cell_loop post hook).  An update may overwrite x_old but not x, and the last one has to land
+        // in dst, so the iterates rotate through dst, solution_old_ and (odd counts only) temp1_:
+        //   even: dst -> old -> dst -> ...        odd: dst -> old -> temp -> dst -> old -> dst ...
+        temp1_.part = dst.part;
+        for (int u = 0; u < n_updates; ++u)
+          {
+            double f1, f2;
+            if (!zero_guess && u == 0)
+              {
+                f1 = 0.0;
+                f2 = 1.0 / theta_;
+              }
+            else
+              {
+                const double rhokp = 1.0 / (2.0 * sigma - rhok);
+                f1   = rhokp * rhok;
+                f2   = 2.0 * rhokp / delta_;
+                rhok = rhokp;
+              }
+            DVec<T> *out;
+            if (n_updates % 2 == 1 && u <= 1)
+              out = u == 0 ? &solution_old_ : &temp1_;
+            else
+              out = ((n_updates - 1 - u) % 2 == 0) ? &dst : &solution_old_;
+            FusedEpilogue<T> ep;
+            ep.mode = have_old ? 3 : 2;
+            ep.b    = rhs.data;
+            ep.dinv = dinv_.data;
+            ep.xold = have_old ? xo->data : nullptr;
+            ep.f1   = T(f1);
+            ep.f2   = T(f2);
+            op_.vmult_fused(*out, *x, ep);
+            xo       = x;
+            x        = out;
+            have_old = true;
+          }
+        return;
+      }
     for (int u = 0; u < n_updates; ++u)
       {
         op_.vmult(temp1_, *x);

@@ -380,6 +380,7 @@ namespace mgb
     uint32_t              n_edge_cells = 0;
     long long             n_dofs_global = 0;
     const Partitioner    *partitioner = nullptr;
+    long long             first_cell_global = 0; // position of cell 0 in the global Morton order (aligns the chunk plan)
   };
 
   template <typename T> class OperatorT
@@ -399,6 +400,12 @@ namespace mgb
     // general (non-Cartesian) geometry: 8 vertices per cell (lexicographic, x fastest), trilinear map (MappingQ1); the
     // cell loops then run the quadrature-point kernel (device/operator_q1.cuh) instead of the Cartesian one
     void      set_cell_vertices(const double *xyz /* n_cells*8*3 */);
+    // Fused cell loop (device/chunk.cuh): out = E(A x), E = FusedEpilogue (residual or Chebyshev update), identity rows of
+    // the constrained DoFs included.  Available for Cartesian cells without refinement-edge DoFs on vectors without ghost
+    // exchange; otherwise the caller runs vmult followed by the separate vector update.  out must not alias x.
+    bool      fused_available(const DVec<T> &out, const DVec<T> &x) const;
+    void      vmult_fused(DVec<T> &out, const DVec<T> &x, const FusedEpilogue<T> &ep) const;
+    bool      chunked() const { return chunked_; }
     const std::shared_ptr<DevicePartitioner> &partitioner() const { return part_; }
     int       degree() const { return cd_.degree; }
     const CellData &cell_data() const { return cd_; }
@@ -418,6 +425,12 @@ namespace mgb
     DeviceBuffer<uint32_t>             plain_cells_, hanging_cells_; // MGB_SPLIT_HANGING=1: cells without / with hanging-node constraints
     mutable DeviceBuffer<T>            edge_src_vals_;
     mutable DVec<T>                    src_copy_;
+    // chunk plan of the cell loop (host/chunks.h) on the device
+    bool                               chunked_ = false;
+    ChunkDevice                        chd_;
+    DeviceBuffer<uint32_t>             ch_desc_, ch_pool_, ch_deps_, ch_ghost_, ch_flags_, ch_state_;
+    DeviceBuffer<T>                    ch_side_;
+    bool chunk_path_ok(const T *out, const T *x) const;
     bool                               has_edge_global_ = false;
     long long                          n_dofs_global_   = 0;
     std::shared_ptr<DevicePartitioner> part_;
@@ -447,6 +460,7 @@ namespace mgb
     double              smoothing_range_;
     unsigned            eig_its_;
     bool                eig_done_ = false;
+    bool                fuse_     = true; // vector updates inside the cell loop (MGB_FUSE_CHEB=0: separate pass)
     double              lambda_max_ = 0, lambda_min_est_ = 0, theta_ = 1, delta_ = 1;
     DVec<T>             dinv_, solution_old_, temp1_, temp2_;
     CGWork<T>           cgw_;

@@ -136,6 +136,12 @@ int  mgb_dofmap_view_get(const mgb_dofmap *d, mgb_dofmap_view *view);
 /* expand an entity table to the lexicographic (p+1)^3 index map per cell (flag kept in bit 31) */
 int  mgb_dofmap_expand(const mgb_dofmap *d, int which /*0 eval, 1 own*/, uint32_t *out /* n_cells*(p+1)^3 */);
 void mgb_dofmap_destroy(mgb_dofmap *d);
+/* Host-only diagnostic of the chunk plan the operators build over a DoF map (cell loop of device/chunk.cuh): builds the
+ * plan for values of value_bytes (8 or 4) and walks through it on the CPU in the kernel's order with a diagonal stand-in
+ * for the cell matrices.  stats[0] = largest relative deviation from the direct scatter-add (>= 1e300: structural defect),
+ * [1] chunks, [2] distinct compute tables, [3] distinct pull tables, [4] table words, [5..7] foreign DoF slots owned by a
+ * lower chunk / by a higher chunk (late) / by another rank, [8] side-buffer entries, [9] largest DoF window, [10] seconds spent building the plan */
+int  mgb_dofmap_chunk_plan_check(const mgb_dofmap *d, int value_bytes, double *stats /* 11 */);
 
 typedef struct
 {
