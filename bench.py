@@ -103,15 +103,30 @@ def measured_peaks():
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm (oracle)
-def cpu_solve_sample(n_ref, degree, steps, warmup):
-    """time the threaded C restatement of the reference's CPU algorithm (oracle/mgcpu.c) on a bounded sample of the workload:
-    the same solver on a smaller hypercube, on as many host threads as speed the operator up (autotuned)"""
+def cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown CPU"
+
+
+def cpu_solve_sample(n_ref, degree, steps, warmup, keep=False):
+    """time the threaded C restatement of the reference's CPU algorithm (oracle/mgcpu.c, built on this machine with
+    -march=native when a compiler is present) on the hypercube workload of NRefGlobal = n_ref, on as many host threads as
+    speed the operator up (autotuned up to all hardware threads the process may use)"""
     import dealii_multigrid_b200 as mg  # host-side map generator only (no GPU call)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from util import mesh_sequence
     from oracle import reference as ref
+    from oracle import cpu_solver
     from oracle.cpu_solver import CpuMultigrid
 
+    t0 = time.perf_counter()
+    build = cpu_solver.build_native()
     meshes = mesh_sequence("hypercube", n_ref)
     dofmaps = [mg.DoFMap(m, degree) for m in meshes]
     tmaps = [None] + [mg.TransferMap(meshes[l], dofmaps[l], meshes[l - 1], dofmaps[l - 1]) for l in range(1, len(meshes))]
@@ -119,32 +134,77 @@ def cpu_solve_sample(n_ref, degree, steps, warmup):
     threads = M.autotune_threads()
     b = ref.assemble_rhs_constant(M.maps[-1])
     n = M.maps[-1].n_dofs
-    best, its = 1e300, 0
-    for i in range(warmup + steps):
+    setup_s = time.perf_counter() - t0
+    times, its, i = [], 0, 0
+    while i < warmup + steps:
         t0 = time.perf_counter()
         _, its, _, _ = M.solve(b)
         dt = time.perf_counter() - t0
         if i >= warmup:
-            best = min(best, dt)
-    return {"n_dofs": n, "n_iterations": its, "seconds": best, "value": n * its / best, "cores": threads}
+            times.append(dt)
+        elif dt > 40.0:
+            steps = 1  # a slow host: one timed solve keeps the whole run within a few minutes
+        i += 1
+    best = min(times)
+    r = {"n_dofs": n, "n_iterations": its, "seconds": best, "seconds_all": times, "value": n * its / best, "cores": threads,
+         "setup_s": setup_s, "build": build, "cpu": cpu_model(), "steps_run": len(times),
+         "hw_threads": len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)}
+    return (r, M, b) if keep else r
 
 
 def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (deal.II itself cannot be built here, so its
+    threaded C restatement oracle/mgcpu.c) on the SAME workload as the GPU arm, on the host cores.  A solve of the 135M-DoF
+    problem takes tens of seconds on the host, so the run is bounded to at most 1 warm-up + 2 timed solves; the line
+    reports the counts that were actually run."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n_ref = args.cpu_nref
-    steps = min(max(1, args.steps), 5)  # bounded: a solve of the 17M-DoF sample takes seconds on the host cores
-    r = cpu_solve_sample(n_ref, args.degree, steps, min(args.warmup, 1))
-    sample = f"{workload_name(n_ref, args.degree, 'double')}: best of {steps} solves, threaded C restatement oracle/mgcpu.c on {r['cores']} thread(s) (deal.II itself cannot be built here)"
-    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": r["seconds"] * 1e3, "higher_is_better": True, "scaling": "strong",
+    n_ref = args.nref if args.cpu_nref is None else args.cpu_nref
+    steps, warmup = min(max(1, args.steps), 2), min(max(0, args.warmup), 1)
+    r = cpu_solve_sample(n_ref, args.degree, steps, warmup)
+    steps = r["steps_run"]
+    sample = (f"{workload_name(n_ref, args.degree, 'double')}: best of {steps} solve(s) after {warmup} warm-up, threaded C restatement "
+              f"oracle/mgcpu.c ({r['build']}) on {r['cores']} of {r['hw_threads']} hardware threads, {r['cpu']}; setup {r['setup_s']:.0f} s; "
+              "a port, not the deal.II binary (which cannot be built here)")
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warmup, "requested_steps": args.steps, "requested_warmup": args.warmup,
+            "ms_per_step": r["seconds"] * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args.nref, args.degree, args.number), "sample": sample},
+            "config": {"workload": workload_name(n_ref, args.degree, "double"), "sample": sample,
+                       "same_workload_as_gpu_arm": n_ref == args.nref and args.number == "double"},
             "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "n_iterations": r["n_iterations"]}
     print(json.dumps(line))
+
+
+def parity_check(mg, M, b_cpu, n_ref, degree, number):
+    """bench-scale parity inside the driver-run artefact: the GPU path against the host restatement on the SAME mesh
+    (NRefGlobal = n_ref): one vmult and one V-cycle of a seeded vector, and the CG iteration counts"""
+    import numpy as np
+    prob = mg.Problem(workload_params(n_ref, degree, number))
+    fine = prob.n_levels - 1
+    op = prob.fine_operator()
+    n = M.maps[-1].n_dofs
+    x = np.random.default_rng(7).uniform(-1.0, 1.0, n)
+    src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+    src.from_numpy(x)
+    op.vmult(dst, src)
+    y_cpu = M.vmult(len(M.maps) - 1, x)
+    e_vmult = float(np.linalg.norm(dst.to_numpy() - y_cpu) / np.linalg.norm(y_cpu))
+    r = x.copy()
+    r[M.maps[-1].constrained] = 0.0
+    src.from_numpy(r)
+    prob.vcycle(dst, src)
+    z_cpu = M.vcycle(r)
+    e_vcycle = float(np.linalg.norm(dst.to_numpy() - z_cpu) / np.linalg.norm(z_cpu))
+    its_gpu = prob.solve_once()["n_iterations"]
+    _, its_cpu, _, _ = M.solve(b_cpu)
+    tol_v, tol_c = (1e-12, 1e-11) if number == "double" else (None, 1e-3)
+    ok = its_gpu == its_cpu and e_vcycle < tol_c and (tol_v is None or e_vmult < tol_v)
+    return {"nref": n_ref, "n_dofs": int(n), "level": fine, "vmult_rel_l2": e_vmult, "vcycle_rel_l2": e_vcycle, "its_gpu": int(its_gpu),
+            "its_cpu": int(its_cpu), "tolerance": {"vmult": tol_v, "vcycle": tol_c}, "ok": bool(ok)}
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
@@ -242,17 +302,22 @@ def run_ours(args):
     peak, peak_src = measured_peaks()
     k_avg_s = (k_ms / max(k_launches, 1)) * 1e-3
     k_avg_s = max_over_ranks(k_avg_s)
-    alg_bytes = 16.0 * n_owned
+    value_bytes = 8 if args.number == "double" else 4  # the finest level runs in MGNumberType inside the V-cycle
+    alg_bytes = 2.0 * value_bytes * n_owned
     achieved = alg_bytes / k_avg_s / 1e9 if k_launches else 0.0
     n1 = args.degree + 1
     flops_ref = n_cells_local * (24.0 * n1 ** 4 + 9.0 * n1 ** 3)   # F_alg of the 12-sweep reference kernel
     if rank != 0:
         return
-    cpu = None
+    cpu = parity = None
     if world == 1 and not args.no_cpu:
-        c = cpu_solve_sample(args.cpu_nref, args.degree, 2, 1)
+        cpu_nref = 6 if args.cpu_nref is None else args.cpu_nref
+        c, M, b_cpu = cpu_solve_sample(cpu_nref, args.degree, 2, 1, keep=True)
         cpu = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
-               "sample": f"{workload_name(args.cpu_nref, args.degree, 'double')}: best of 2 solves after 1 warm-up ({c['seconds']:.1f} s each), threaded C restatement oracle/mgcpu.c on {c['cores']} thread(s)"}
+               "sample": f"{workload_name(cpu_nref, args.degree, 'double')} (a bounded sample: the GPU arm runs NRefGlobal={args.nref}; "
+                         f"`--impl reference` times the full workload): best of 2 solves after 1 warm-up ({c['seconds']:.1f} s each), "
+                         f"threaded C restatement oracle/mgcpu.c ({c['build']}) on {c['cores']} of {c['hw_threads']} hardware threads, {c['cpu']}"}
+        parity = parity_check(mg, M, b_cpu, cpu_nref, args.degree, args.number)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -263,16 +328,18 @@ def run_ours(args):
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 8 * n_owned, "d2h_bytes_per_step": 8 * n_owned,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
-        "roofline": {"kernel": f"k_laplace_apply<{args.degree},double> (finest level)", "bound": "hbm", "achieved": achieved, "peak": peak,
+        "roofline": {"kernel": f"k_laplace_apply<{args.degree},{args.number}> (finest level" + ("" if args.number == "double" else "; the outer CG's double-precision launches on the same mesh are timed with it, bytes counted for the float ones") + ")", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.nref, args.degree, args.number, world),
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "launches_timed": k_launches, "avg_launch_ms": k_avg_s * 1e3,
                      "share_of_step": k_ms / ms_prof, "timed_in": "second pass of the same K solves with per-launch CUDA events "
                      "(eager launches, %.3f ms/step)" % (ms_prof / args.steps), "gdofs_per_s": n_owned / k_avg_s / 1e9,
                      "fp64_tflops_reference_flop_count": flops_ref / k_avg_s / 1e12},
-        "cpu_baseline": cpu, "clocks": clocks,
+        "cpu_baseline": cpu, "parity_check": parity, "clocks": clocks,
     }
     print(json.dumps(line))
+    if parity is not None and not parity["ok"]:
+        raise SystemExit("bench.py: parity_check failed: %s" % json.dumps(parity))
     if world > 1:
         dist.destroy_process_group()
 
@@ -286,7 +353,8 @@ def main():
     ap.add_argument("--nref", type=int, default=7, help="NRefGlobal of the GPU workload (7: 513^3 = 135 005 697 DoFs)")
     ap.add_argument("--degree", type=int, default=4)
     ap.add_argument("--number", default="double", choices=["double", "float"], help="MGNumberType")
-    ap.add_argument("--cpu-nref", type=int, default=6, help="NRefGlobal of the bounded CPU sample (6: 257^3 = 16 974 593 DoFs)")
+    ap.add_argument("--cpu-nref", type=int, default=None,
+                    help="NRefGlobal of the CPU runs (default: 6 = 257^3 DoFs for the cpu_baseline sample of the GPU arm, --nref for --impl reference)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

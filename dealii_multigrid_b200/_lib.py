@@ -130,6 +130,7 @@ SIGNATURES = {
     "mgb_problem_statistics": (C.c_int, [P, C.POINTER(Statistics), C.POINTER(C.c_int64)]),
     "mgb_dofmap_view_get": (C.c_int, [P, C.POINTER(DofmapView)]),
     "mgb_dofmap_expand": (C.c_int, [P, C.c_int, c_u32p]),
+    "mgb_assemble_rhs": (C.c_int, [P, P, C.c_char_p, C.POINTER(C.c_double)]),
     "mgb_dofmap_chunk_plan_check": (C.c_int, [P, C.c_int, C.POINTER(C.c_double)]),
     "mgb_dofmap_destroy": (None, [P]),
     "mgb_transfer_map_create": (C.c_int, [P, P, P, P, PP]),
@@ -167,6 +168,8 @@ SIGNATURES = {
     "mgb_operator_initialize_dof_vector": (C.c_int, [P, PP]),
     "mgb_operator_vmult": (C.c_int, [P, P, P]),
     "mgb_operator_tvmult": (C.c_int, [P, P, P]),
+    "mgb_operator_fused_available": (C.c_int, [P]),
+    "mgb_operator_vmult_fused": (C.c_int, [P, P, P, C.c_int, P, P, P, C.c_double, C.c_double]),
     "mgb_operator_vmult_interface_down": (C.c_int, [P, P, P]),
     "mgb_operator_vmult_interface_up": (C.c_int, [P, P, P]),
     "mgb_operator_compute_inverse_diagonal": (C.c_int, [P, P]),

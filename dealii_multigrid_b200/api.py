@@ -277,6 +277,12 @@ class DoFMap:
         _check(self._lib.mgb_dofmap_expand(self._h, 0 if which == "eval" else 1, out.ctypes.data_as(_lib.c_u32p)))
         return out
 
+    def assemble_rhs(self, mesh, simulation_type="Constant"):
+        """Operator::rhs on the host (n_owned + n_ghost entries, ghost contributions not compressed)"""
+        out = np.zeros(self.n_owned + self.n_ghost)
+        _check(self._lib.mgb_assemble_rhs(mesh._h, self._h, simulation_type.encode(), out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
     def chunk_plan_check(self, value_bytes=8):
         """host-only check of the cell loop's chunk plan (host/chunks.h): dict with the deviation of the CPU walk through
         the plan from the direct scatter-add and the plan's statistics"""
@@ -538,6 +544,15 @@ class Operator:
 
     def compute_inverse_diagonal(self, diag):
         _check(self._lib.mgb_operator_compute_inverse_diagonal(self._h, diag._h))
+
+    def fused_available(self):
+        """True if the operator runs the chunked cell loop (created with MGB_CHUNKED=1) and can fuse vector updates"""
+        return bool(self._lib.mgb_operator_fused_available(self._h))
+
+    def vmult_fused(self, out, x, mode, b=None, dinv=None, xold=None, f1=0.0, f2=0.0):
+        """cell loop with the vector update in the same pass: mode 0 out = A x, 1 out = b - A x, 2 / 3 the Chebyshev updates"""
+        h = lambda v: v._h if v is not None else None
+        _check(self._lib.mgb_operator_vmult_fused(self._h, out._h, x._h, mode, h(b), h(dinv), h(xold), f1, f2))
 
     def set_cell_vertices(self, xyz):
         """general (non-Cartesian) cells: (n_cells, 8, 3) vertex coordinates, vertices lexicographic with x fastest, trilinear

@@ -133,11 +133,10 @@ namespace mgb
   };
 
   // warp-level version of hanging_node_sweeps for the padded slab layout; `u` = the warp's cells, tb = their 32-word records (word 27 = mask | level << 16)
-  template <int P, typename T, bool TRANSPOSE>
+  template <int P, typename T, bool TRANSPOSE, int PS = SlabLayout<P + 1, sizeof(T)>::PS, int CS = SlabLayout<P + 1, sizeof(T)>::CS>
   __device__ __forceinline__ void hanging_node_sweeps_slab(T *u, const uint32_t *tb, const int ncw, const int lane)
   {
     constexpr int n = P + 1, n2 = n * n;
-    constexpr int PS = SlabLayout<n, sizeof(T)>::PS, CS = SlabLayout<n, sizeof(T)>::CS;
 #pragma unroll 1
     for (int dd = 0; dd < 3; ++dd)
       {

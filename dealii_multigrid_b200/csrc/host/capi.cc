@@ -141,6 +141,30 @@ namespace
   }
 } // namespace
 
+namespace
+{
+  template <typename T>
+  void call_fused(const OperatorT<T> &op, DVec<T> &out, const DVec<T> &x, int mode, const DVec<T> *b, const DVec<T> *dinv, const DVec<T> *xold,
+                  double f1, double f2)
+  {
+    if (mode < 0 || mode > 3)
+      throw std::runtime_error("mgb_operator_vmult_fused: mode must be 0..3");
+    if ((mode >= 1 && !b) || (mode >= 2 && !dinv) || (mode == 3 && !xold))
+      throw std::runtime_error("mgb_operator_vmult_fused: a vector this mode reads is NULL");
+    if (!op.fused_available(out, x))
+      throw std::runtime_error("mgb_operator_vmult_fused: not available (create the operator with MGB_CHUNKED=1; Cartesian cells, no "
+                               "refinement-edge DoFs, one rank, out != x)");
+    FusedEpilogue<T> ep;
+    ep.mode = mode;
+    ep.b    = b ? b->data : nullptr;
+    ep.dinv = dinv ? dinv->data : nullptr;
+    ep.xold = xold ? xold->data : nullptr;
+    ep.f1   = T(f1);
+    ep.f2   = T(f2);
+    op.vmult_fused(out, x, ep);
+  }
+} // namespace
+
 extern "C" {
 
 const char *mgb_last_error(void) { return g_error.c_str(); }
@@ -442,6 +466,14 @@ int mgb_dofmap_expand(const mgb_dofmap *h, int which, uint32_t *out)
     std::vector<uint32_t> tmp;
     h->d->expand(which == 0 ? h->d->eval_table : h->d->own_table, tmp);
     std::memcpy(out, tmp.data(), tmp.size() * sizeof(uint32_t));
+  });
+}
+int mgb_assemble_rhs(const mgb_mesh *m, const mgb_dofmap *h, const char *simulation_type, double *rhs_local)
+{
+  return guarded([&] {
+    std::vector<double> b;
+    assemble_rhs(m->m, *h->d, simulation_type ? simulation_type : "Constant", b);
+    std::memcpy(rhs_local, b.data(), b.size() * sizeof(double));
   });
 }
 int mgb_dofmap_chunk_plan_check(const mgb_dofmap *h, int value_bytes, double *stats)
@@ -881,6 +913,29 @@ int mgb_operator_vmult(const mgb_operator *op, mgb_vector *dst, const mgb_vector
 int mgb_operator_tvmult(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src) { OP_CALL(Tvmult); }
 int mgb_operator_vmult_interface_down(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src) { OP_CALL(vmult_interface_down); }
 int mgb_operator_vmult_interface_up(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src) { OP_CALL(vmult_interface_up); }
+int mgb_operator_fused_available(const mgb_operator *op)
+{
+  // vectors of the operator's own layout (16-byte aligned allocations, distinct out / x)
+  return (op->type == MGB_DOUBLE ? op->pd->chunked() && op->pd->partitioner()->trivial() && !op->pd->has_edge_dofs() :
+                                   op->pf->chunked() && op->pf->partitioner()->trivial() && !op->pf->has_edge_dofs()) ?
+           1 :
+           0;
+}
+int mgb_operator_vmult_fused(const mgb_operator *op, mgb_vector *out, const mgb_vector *x, int mode, const mgb_vector *b,
+                             const mgb_vector *dinv, const mgb_vector *xold, double f1, double f2)
+{
+  return guarded([&] {
+    require_same_type(op->type, out->type);
+    require_same_type(op->type, x->type);
+    for (const mgb_vector *v : {b, dinv, xold})
+      if (v)
+        require_same_type(op->type, v->type);
+    if (op->type == MGB_DOUBLE)
+      call_fused<double>(*op->pd, *out->pd, *x->pd, mode, b ? b->pd : nullptr, dinv ? dinv->pd : nullptr, xold ? xold->pd : nullptr, f1, f2);
+    else
+      call_fused<float>(*op->pf, *out->pf, *x->pf, mode, b ? b->pf : nullptr, dinv ? dinv->pf : nullptr, xold ? xold->pf : nullptr, f1, f2);
+  });
+}
 int mgb_operator_compute_inverse_diagonal(const mgb_operator *op, mgb_vector *diag)
 {
   return guarded([&] {

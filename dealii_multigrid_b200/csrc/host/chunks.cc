@@ -14,29 +14,36 @@ namespace mgb
   // Chunk sizes are powers of two (whole octets of the Morton order) and chunk boundaries sit at multiples of the size in
   // the GLOBAL cell order: on a uniform mesh every chunk is then the same box (or one of two half boxes), sees its
   // neighbours in the same relative position, and all chunks of one kind share one table.
+#ifndef MGB_CHUNK_NC4
+#define MGB_CHUNK_NC4 32
+#endif
+#ifndef MGB_CHUNK_CAP4
+#define MGB_CHUNK_CAP4 (MGB_CHUNK_NC4 == 32 ? 2880 : 1536)
+#endif
   int chunk_cells(int p)
   {
-    static const int nc[7] = {0, 256, 64, 64, 32, 32, 16};
+    static const int nc[7] = {0, 256, 64, 64, MGB_CHUNK_NC4, 32, 16};
     return nc[p];
   }
   int chunk_warps(int p)
   {
-    static const int w[7] = {0, 8, 7, 8, 6, 7, 4};
+    static const int w[7] = {0, 8, 7, 8, (MGB_CHUNK_NC4 + 5) / 6, 7, 4};
     return w[p];
   }
   int chunk_slot_capacity(int p)
   {
-    static const int cap[7] = {0, 2112, 1792, 3072, 2880, 5632, 5632};
+    static const int cap[7] = {0, 2112, 1792, 3072, MGB_CHUNK_CAP4, 5632, 5632};
     return cap[p];
   }
 
-  void slab_layout(int n, int bytes, int &ps, int &cs)
+  void chunk_layout(int n, int bytes, int &ps, int &cs)
   {
-    // must equal SlabLayout<N, BYTES> of device/cell_common.cuh (static_asserts in device/chunk.cuh)
-    static const int t8[8][2] = {{0, 0}, {0, 0}, {5, 10}, {19, 57}, {17, 68}, {37, 185}, {37, 222}, {55, 385}};
+    // must equal ChunkLayout<N, BYTES> of device/chunk.cuh (checked by its launcher): SlabLayout of device/cell_common.cuh
+    // except for n = 5 doubles, where the tighter (27, 135) keeps three blocks resident per SM
+    static const int t8[8][2] = {{0, 0}, {0, 0}, {5, 10}, {19, 57}, {17, 68}, {27, 135}, {37, 222}, {55, 385}};
     static const int t4[8][2] = {{0, 0}, {0, 0}, {5, 10}, {26, 105}, {17, 68}, {27, 153}, {37, 222}, {50, 369}};
     if (n < 2 || n > 7 || (bytes != 4 && bytes != 8))
-      throw std::runtime_error("slab_layout: unsupported size");
+      throw std::runtime_error("chunk_layout: unsupported size");
     ps = (bytes == 8 ? t8 : t4)[n][0];
     cs = (bytes == 8 ? t8 : t4)[n][1];
   }
@@ -139,7 +146,7 @@ namespace mgb
       return plan;
     const int n = p + 1;
     int       PS, CS;
-    slab_layout(n, value_bytes, PS, CS);
+    chunk_layout(n, value_bytes, PS, CS);
     const int NC = chunk_cells(p), CAP = chunk_slot_capacity(p);
     if (NC * CS >= 65536)
       throw std::runtime_error("chunk plan: cell storage positions exceed 16 bits");
@@ -356,8 +363,9 @@ namespace mgb
                   blob[at + (f.slot - n_own) + j] = (ord << 16) | (f.idx + j - owned_begin[o]);
               }
         }
-        uint32_t blob_off = 0;
-        uint64_t key_hash = 1469598103934665603ull;
+        uint32_t     blob_off = 0;
+        const size_t key_size = blob.size();
+        uint64_t     key_hash = 1469598103934665603ull;
         for (uint32_t w : blob)
           {
             key_hash ^= w;
@@ -371,9 +379,9 @@ namespace mgb
               {
                 // the cached blob starts with the same header/records/sources up to the two offsets not known yet
                 const uint32_t *q = &plan.pool[off];
-                bool            same = off + blob.size() <= plan.pool.size();
-                for (size_t w = 0; same && w < blob.size(); ++w)
-                  same = (w == CB_OFF_ENT_HDR || w == CB_OFF_ENT) ? true : q[w] == blob[w];
+                bool            same = off + key_size <= plan.pool.size();
+                for (size_t w = 0; same && w < key_size; ++w)
+                  same = (w == CB_N_ROUNDS || w == CB_OFF_MERGE || w == CB_OFF_SLOTPOS || w == CB_TOTAL_WORDS) ? true : q[w] == blob[w];
                 if (same)
                   {
                     blob_off = off;
@@ -417,13 +425,45 @@ namespace mgb
                 throw std::runtime_error("chunk plan: more than 255 cell contributions to one DoF");
             if (ent_off[n_slots] >= (1u << 24))
               throw std::runtime_error("chunk plan: contribution list too long");
-            blob[CB_OFF_ENT_HDR] = uint32_t(blob.size());
-            for (uint32_t s = 0; s < n_slots; ++s)
-              blob.push_back((ent_off[s] << 8) | ent_cnt[s]);
-            blob[CB_OFF_ENT] = uint32_t(blob.size());
-            for (size_t q = 0; q < ent_list.size(); q += 2)
-              blob.push_back(uint32_t(ent_list[q]) | (uint32_t(ent_list[q + 1]) << 16));
-            blob_off = blobs.add(blob);
+            // merge rounds: the copies p[0..m) of a DoF are summed as a binary tree, round r adds p[i + 2^r] to p[i] for
+            // i = 0, 2^(r+1), ...; the sum ends up in p[0] (fixed order: reproducible)
+            {
+              uint32_t max_cnt = 1;
+              for (uint32_t s = 0; s < n_slots; ++s)
+                max_cnt = std::max(max_cnt, ent_cnt[s]);
+              uint32_t n_rounds = 0;
+              while ((1u << n_rounds) < max_cnt)
+                ++n_rounds;
+              std::vector<std::vector<uint32_t>> pairs(n_rounds);
+              for (uint32_t s = 0; s < n_slots; ++s)
+                for (uint32_t r = 0; (1u << r) < ent_cnt[s]; ++r)
+                  for (uint32_t i = 0; i + (1u << r) < ent_cnt[s]; i += 2u << r)
+                    pairs[r].push_back(uint32_t(ent_list[ent_off[s] + i]) | (uint32_t(ent_list[ent_off[s] + i + (1u << r)]) << 16));
+              while (blob.size() % 4)
+                blob.push_back(0u); // the epilogue tables [CB_OFF_MERGE, CB_TOTAL_WORDS) are fetched with one bulk copy
+              blob[CB_N_ROUNDS]  = n_rounds;
+              blob[CB_OFF_MERGE] = uint32_t(blob.size());
+              uint32_t at = n_rounds + 1;
+              for (uint32_t r = 0; r < n_rounds; ++r)
+                {
+                  blob.push_back(at);
+                  at += uint32_t(pairs[r].size());
+                }
+              blob.push_back(at);
+              for (uint32_t r = 0; r < n_rounds; ++r)
+                blob.insert(blob.end(), pairs[r].begin(), pairs[r].end());
+              blob[CB_OFF_SLOTPOS] = uint32_t(blob.size());
+              for (uint32_t s = 0; s < n_slots; s += 2)
+                {
+                  const uint32_t p0 = ent_cnt[s] ? ent_list[ent_off[s]] : 0xffffu;
+                  const uint32_t p1 = (s + 1 < n_slots && ent_cnt[s + 1]) ? ent_list[ent_off[s + 1]] : 0xffffu;
+                  blob.push_back(p0 | (p1 << 16));
+                }
+            }
+            while (blob.size() % 4)
+              blob.push_back(0u);
+            blob[CB_TOTAL_WORDS] = uint32_t(blob.size());
+            blob_off             = blobs.add(blob);
             key_cache[key_hash].push_back(blob_off);
           }
 
@@ -484,25 +524,34 @@ namespace mgb
         std::sort(entries.begin(), entries.end(), [](const PullEntry &a, const PullEntry &b) {
           return a.slot != b.slot ? a.slot < b.slot : a.contributor < b.contributor;
         });
-        const uint32_t *cb      = &plan.pool[plan.desc[size_t(k) * CHUNK_DESC_WORDS + CD_BLOB]];
-        const uint32_t *ent_hdr = cb + cb[CB_OFF_ENT_HDR];
-        const uint32_t *ent     = cb + cb[CB_OFF_ENT];
         blob.assign(PB_HEADER_WORDS, 0u);
+        const uint32_t        n_own_k = plan.desc[size_t(k) * CHUNK_DESC_WORDS + CD_N_OWNED];
         std::vector<uint32_t> recw, listw;
+        std::vector<uint16_t> opos(n_own_k + (n_own_k & 1), 0x7fffu);
+        {
+          const uint32_t *cb      = &plan.pool[plan.desc[size_t(k) * CHUNK_DESC_WORDS + CD_BLOB]];
+          const uint32_t *slotpos = cb + cb[CB_OFF_SLOTPOS];
+          for (uint32_t s = 0; s < n_own_k; ++s)
+            {
+              const uint32_t pos = (slotpos[s >> 1] >> ((s & 1) * 16)) & 0xffffu;
+              if (pos != 0xffffu && pos >= 0x7fffu)
+                throw std::runtime_error("chunk plan: cell storage position exceeds 15 bits");
+              opos[s] = uint16_t(pos == 0xffffu ? 0x7fffu : pos);
+            }
+        }
         for (size_t q = 0; q < entries.size();)
           {
             size_t q1 = q;
             while (q1 < entries.size() && entries[q1].slot == entries[q].slot)
               ++q1;
-            const uint32_t hdr = ent_hdr[entries[q].slot];
-            if ((hdr & 255u) == 0)
-              throw std::runtime_error("chunk plan: a DoF receives contributions but none from its own chunk");
-            const uint32_t e0  = hdr >> 8;
-            const uint32_t pos = (ent[e0 >> 1] >> ((e0 & 1) * 16)) & 0xffffu;
-            if (q1 - q >= 65536)
-              throw std::runtime_error("chunk plan: too many contributions");
-            recw.push_back(pos | (uint32_t(q1 - q) << 16));
-            recw.push_back(uint32_t(listw.size()));
+            const uint32_t slot = entries[q].slot;
+            if (slot >= n_own_k)
+              throw std::runtime_error("chunk plan: pull target outside the owned range");
+            opos[slot] |= 0x8000u;
+            if (q1 - q >= 32 || slot >= 8192 || listw.size() >= 16384)
+              throw std::runtime_error("chunk plan: pull record out of range");
+            const uint32_t more_at = uint32_t(listw.size());
+            uint32_t       first   = 0u;
             for (size_t t = q; t < q1; ++t)
               {
                 size_t o = std::find(pull_deps.begin(), pull_deps.end(), entries[t].contributor) - pull_deps.begin();
@@ -510,8 +559,14 @@ namespace mgb
                   pull_deps.push_back(entries[t].contributor);
                 if (o >= 65536 || entries[t].rel >= 65536)
                   throw std::runtime_error("chunk plan: pull entry out of range");
-                listw.push_back((uint32_t(o) << 16) | entries[t].rel);
+                const uint32_t w = (uint32_t(o) << 16) | entries[t].rel;
+                if (t == q)
+                  first = w;
+                else
+                  listw.push_back(w);
               }
+            recw.push_back(slot | (uint32_t(q1 - q) << 13) | (more_at << 18));
+            recw.push_back(first);
             q = q1;
           }
         blob[PB_N_SLOTS]  = uint32_t(recw.size() / 2);
@@ -520,6 +575,12 @@ namespace mgb
         blob.insert(blob.end(), recw.begin(), recw.end());
         blob[PB_OFF_LIST] = uint32_t(blob.size());
         blob.insert(blob.end(), listw.begin(), listw.end());
+        blob[PB_OFF_OPOS] = uint32_t(blob.size());
+        for (size_t q = 0; q < opos.size(); q += 2)
+          blob.push_back(uint32_t(opos[q]) | (uint32_t(opos[q + 1]) << 16));
+        while (blob.size() % 4)
+          blob.push_back(0u);
+        blob[PB_TOTAL_WORDS] = uint32_t(blob.size());
         plan.desc[size_t(k) * CHUNK_DESC_WORDS + CD_PULL_BLOB] = blobs.add(blob);
         pull_deps_off[k] = uint32_t(pull_deps_all.size());
         pull_deps_all.insert(pull_deps_all.end(), pull_deps.begin(), pull_deps.end());
@@ -549,7 +610,7 @@ namespace mgb
   {
     const int p = plan.degree, n = p + 1;
     int       PS, CS;
-    slab_layout(n, plan.value_bytes, PS, CS);
+    chunk_layout(n, plan.value_bytes, PS, CS);
     const size_t        n_local = size_t(n_owned) + n_ghost;
     std::vector<double> src(n_local), ref(n_local, 0.0), out(n_local, 0.0), side(size_t(plan.side_size) + 1, 0.0);
     for (size_t i = 0; i < n_local; ++i)
@@ -588,8 +649,8 @@ namespace mgb
         const uint32_t  nc = cb[CB_N_CELLS], n_own = cb[CB_N_OWNED], n_fp = cb[CB_N_FP], n_fl = cb[CB_N_FL], n_fg = cb[CB_N_FG];
         const uint32_t  n_slots = n_own + n_fp + n_fl + n_fg, ob = d[CD_OWNED_BEGIN];
         const uint32_t *src_deps = &plan.deps[d[CD_SRC_DEPS]];
-        const uint32_t *fsrc = cb + cb[CB_OFF_FSRC], *rec = cb + cb[CB_OFF_CELLREC], *ent_hdr = cb + cb[CB_OFF_ENT_HDR];
-        const uint32_t *entw = cb + cb[CB_OFF_ENT];
+        const uint32_t *fsrc = cb + cb[CB_OFF_FSRC], *rec = cb + cb[CB_OFF_CELLREC], *merge = cb + cb[CB_OFF_MERGE];
+        const uint32_t *slotpos = cb + cb[CB_OFF_SLOTPOS];
         if (n_own != d[CD_N_OWNED] || n_slots + CHUNK_ZERO_SLOTS > uint32_t(chunk_slot_capacity(p)))
           return 2e300;
         xs.assign(n_slots + CHUNK_ZERO_SLOTS, 0.0);
@@ -613,12 +674,21 @@ namespace mgb
                   u_all[size_t(cl) * CS + k * PS + j * n + i] =
                     weight(first_cell[c] + cl, (k * n + j) * n + i) * xs[rec[size_t(cl) * 32 + e] + uint32_t(off)];
                 }
+        for (uint32_t r = 0; r < cb[CB_N_ROUNDS]; ++r)
+          {
+            std::vector<uint8_t> touched(u_all.size(), 0);
+            for (uint32_t q = merge[r]; q < merge[r + 1]; ++q)
+              {
+                const uint32_t dst = merge[q] & 0xffffu, src = merge[q] >> 16;
+                if (touched[dst] || touched[src])
+                  return 7e300; // a position twice in one round: the parallel merge would race
+                touched[dst] = touched[src] = 1;
+                u_all[dst] += u_all[src];
+              }
+          }
         const auto slot_sum = [&](uint32_t s) {
-          const uint32_t cnt = ent_hdr[s] & 255u, off = ent_hdr[s] >> 8;
-          double         v   = 0;
-          for (uint32_t j = 0; j < cnt; ++j)
-            v += u_all[(entw[(off + j) >> 1] >> (((off + j) & 1) * 16)) & 0xffffu];
-          return v;
+          const uint32_t pos = (slotpos[s >> 1] >> ((s & 1) * 16)) & 0xffffu;
+          return pos == 0xffffu ? 0.0 : u_all[pos];
         };
         for (uint32_t t = 0; t < n_fp; ++t)
           side[size_t(d[CD_SIDE_OFF]) + t] = slot_sum(n_own + t);
@@ -630,19 +700,29 @@ namespace mgb
         for (uint32_t t = 0; t < pb[PB_N_DEPS]; ++t)
           if (pull_deps[t] <= uint32_t(c) || !ready[pull_deps[t]])
             return 3e300; // a dependency that was not started before this chunk
+        const uint32_t *oposw = pb + pb[PB_OFF_OPOS];
+        std::vector<double> pulled(n_own, 0.0);
         for (uint32_t q = 0; q < pb[PB_N_SLOTS]; ++q)
           {
-            const uint32_t w0 = prec[2 * q], w1 = prec[2 * q + 1];
+            const uint32_t w0 = prec[2 * q], slot = w0 & 0x1fffu;
             double         v  = 0;
-            for (uint32_t j = 0; j < (w0 >> 16); ++j)
+            for (uint32_t j = 0; j < ((w0 >> 13) & 31u); ++j)
               {
-                const uint32_t e = plist[w1 + j];
+                const uint32_t e = j == 0 ? prec[2 * q + 1] : plist[(w0 >> 18) + j - 1];
                 v += side[size_t(plan.desc[size_t(pull_deps[e >> 16]) * CHUNK_DESC_WORDS + CD_SIDE_OFF]) + (e & 0xffffu)];
               }
-            u_all[w0 & 0xffffu] += v;
+            if (!(((oposw[slot >> 1] >> ((slot & 1) * 16)) & 0x8000u)))
+              return 6e300;
+            pulled[slot] = v;
           }
         for (uint32_t s = 0; s < n_own; ++s)
-          out[ob + s] = slot_sum(s);
+          {
+            const uint32_t w = (oposw[s >> 1] >> ((s & 1) * 16)) & 0xffffu, sp = (slotpos[s >> 1] >> ((s & 1) * 16)) & 0xffffu;
+            if ((w & 0x7fffu) != (sp == 0xffffu ? 0x7fffu : sp) || (!(w & 0x8000u) && pulled[s] != 0.0))
+              return 8e300;
+          }
+        for (uint32_t s = 0; s < n_own; ++s)
+          out[ob + s] = slot_sum(s) + pulled[s];
         stored[c] = 1;
         for (uint32_t t = 0; t < n_fl; ++t)
           {

@@ -53,8 +53,11 @@ namespace mgb
     CB_HANGING,    // any cell of the chunk has a hanging-node constraint
     CB_OFF_CELLREC,
     CB_OFF_FSRC,
-    CB_OFF_ENT_HDR,
-    CB_OFF_ENT,
+    CB_N_ROUNDS,   // merge rounds: copies of one DoF in the cell storage are summed pairwise, as a binary tree
+    CB_OFF_MERGE,  // n_rounds + 1 offsets (relative to this word), then the pairs: destination | source << 16 (positions of
+                   // the cell storage; within one round every position occurs at most once)
+    CB_OFF_SLOTPOS, // per slot the 16-bit position holding its sum after the merge rounds (0xffff: no contribution)
+    CB_TOTAL_WORDS,
     CB_HEADER_WORDS = 16
   };
   // words of the pull blob header
@@ -62,9 +65,13 @@ namespace mgb
   {
     PB_N_SLOTS = 0, // owned slots that receive contributions of other chunks
     PB_N_DEPS,
-    PB_OFF_REC,  // 2 words per slot: (position in the cell storage | count << 16), offset into the entry list
-    PB_OFF_LIST, // entries: dependency ordinal << 16 | position in that chunk's side buffer
-    PB_HEADER_WORDS = 4
+    PB_OFF_REC,  // 2 words per slot: owned slot (13 bits) | count << 13 (5 bits) | offset of the further entries << 18, first
+                 // entry
+    PB_OFF_LIST, // the further entries: dependency ordinal << 16 | position in that chunk's side buffer
+    PB_OFF_OPOS, // per owned slot (16 bit): position of its sum in the cell storage (0x7fff: none) | 0x8000 if other
+                 // chunks contribute
+    PB_TOTAL_WORDS,
+    PB_HEADER_WORDS = 8
   };
 
   struct ChunkPlan
@@ -93,6 +100,6 @@ namespace mgb
   // relative deviation from the direct scatter-add (tests/test_chunk_plan.py); >= 1e300: a structural defect
   double check_chunk_plan(const ChunkPlan &plan, long long n_cells, const uint32_t *etab, uint32_t n_owned, uint32_t n_ghost);
 
-  // shared-memory cell layout of the slab kernels (device/cell_common.cuh SlabLayout): plane and cell stride
-  void slab_layout(int n, int value_bytes, int &plane_stride, int &cell_stride);
+  // shared-memory cell layout of the chunk kernel (device/chunk.cuh ChunkLayout): plane and cell stride
+  void chunk_layout(int n, int value_bytes, int &plane_stride, int &cell_stride);
 } // namespace mgb

@@ -1,5 +1,6 @@
 #include "solver.h"
 
+#include <cstdio>
 #include <cstdlib>
 
 #include "chunks.h"
@@ -293,9 +294,12 @@ namespace mgb
         hanging_cells_.upload(hanging.data(), hanging.size());
       }
     {
-      // chunk plan of the cell loop (device/chunk.cuh); MGB_CHUNKED=0 keeps the atomic cell kernel
+      // chunk plan of the cell loop (device/chunk.cuh): opt-in with MGB_CHUNKED=1.  The chunked loop needs no atomics on
+      // owned entries (bitwise reproducible results), no zeroing of dst, and carries the smoother's vector update in its
+      // epilogue, but measured on B200 (profiles/r2f_*) it is 1.6-1.9x slower than the atomic kernel (latency of the
+      // per-chunk phases), so the atomic kernel stays the default
       const char *e = std::getenv("MGB_CHUNKED");
-      if (!(e && e[0] == '0') && s.n_cells > 0)
+      if (e && e[0] == '1' && s.n_cells > 0)
         try
           {
             const ChunkPlan plan = build_chunk_plan(s.degree, s.n_cells, s.entity_table, s.mask, s.cell_level, s.partitioner ? s.partitioner->n_owned : 0u,
@@ -307,6 +311,11 @@ namespace mgb
                 const uint32_t *pb = &plan.pool[plan.desc[size_t(k) * CHUNK_DESC_WORDS + CD_PULL_BLOB]];
                 deps_fit = cb[CB_N_DEP_LOW] + cb[CB_N_DEP_LATE] <= 96u && pb[PB_N_DEPS] <= 96u;
               }
+            if (const char *v = std::getenv("MGB_CHUNK_VERBOSE"); v && v[0] == '1')
+              std::fprintf(stderr, "mgb200: chunk plan p=%d cells=%lld chunks=%u tables=%u+%u (%zu words) foreign low/late/ghost=%llu/%llu/%llu deps_fit=%d\n",
+                           s.degree, s.n_cells, plan.n_chunks, plan.n_compute_blobs, plan.n_pull_blobs, plan.pool.size(),
+                           (unsigned long long)plan.n_foreign_low, (unsigned long long)plan.n_foreign_late,
+                           (unsigned long long)plan.n_foreign_ghost, int(deps_fit));
             if (deps_fit && plan.n_chunks > 0)
               {
                 ch_desc_.upload(plan.desc.data(), plan.desc.size());
@@ -328,9 +337,11 @@ namespace mgb
                 chunked_       = true;
               }
           }
-        catch (const std::runtime_error &)
+        catch (const std::runtime_error &err)
           {
             chunked_ = false; // meshes the planner cannot chunk stay on the atomic kernel
+            if (const char *v = std::getenv("MGB_CHUNK_VERBOSE"); v && v[0] == '1')
+              std::fprintf(stderr, "mgb200: no chunk plan (%s)\n", err.what());
           }
     }
     cd_.ctab        = ctab_.ptr;

@@ -406,6 +406,7 @@ namespace mgb
     bool      fused_available(const DVec<T> &out, const DVec<T> &x) const;
     void      vmult_fused(DVec<T> &out, const DVec<T> &x, const FusedEpilogue<T> &ep) const;
     bool      chunked() const { return chunked_; }
+    bool      has_edge_dofs() const { return edge_.n != 0; }
     const std::shared_ptr<DevicePartitioner> &partitioner() const { return part_; }
     int       degree() const { return cd_.degree; }
     const CellData &cell_data() const { return cd_; }

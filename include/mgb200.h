@@ -136,6 +136,10 @@ int  mgb_dofmap_view_get(const mgb_dofmap *d, mgb_dofmap_view *view);
 /* expand an entity table to the lexicographic (p+1)^3 index map per cell (flag kept in bit 31) */
 int  mgb_dofmap_expand(const mgb_dofmap *d, int which /*0 eval, 1 own*/, uint32_t *out /* n_cells*(p+1)^3 */);
 void mgb_dofmap_destroy(mgb_dofmap *d);
+/* Operator::rhs on the host (include/operator.h:362-447): simulation_type "Constant" (f = 1, u_D = 0) or "Gaussian"
+ * (GaussianRightHandSide / GaussianSolution of multigrid_throughput.cc:60-127 with the inhomogeneous Dirichlet lift
+ * b -= A_hn x_D); rhs_local holds n_owned + n_ghost entries (ghost contributions are NOT compressed).  Host only. */
+int  mgb_assemble_rhs(const mgb_mesh *m, const mgb_dofmap *d, const char *simulation_type, double *rhs_local);
 /* Host-only diagnostic of the chunk plan the operators build over a DoF map (cell loop of device/chunk.cuh): builds the
  * plan for values of value_bytes (8 or 4) and walks through it on the CPU in the kernel's order with a diagonal stand-in
  * for the cell matrices.  stats[0] = largest relative deviation from the direct scatter-add (>= 1e300: structural defect),
@@ -256,6 +260,15 @@ int  mgb_operator_tvmult(const mgb_operator *op, mgb_vector *dst, const mgb_vect
 int  mgb_operator_vmult_interface_down(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
 int  mgb_operator_vmult_interface_up(const mgb_operator *op, mgb_vector *dst, const mgb_vector *src);
 int  mgb_operator_compute_inverse_diagonal(const mgb_operator *op, mgb_vector *diag);
+/* Cell loop with the vector update in its own pass (what deal.II does with the pre/post hooks of MatrixFree::cell_loop;
+ * north_star: "the smoother's vector updates fused with vmult").  mode 0: out = A x;  1: out = b - A x;
+ * 2: out = (1+f1) x + f2 dinv (b - A x);  3: out = (1+f1) x - f1 xold + f2 dinv (b - A x)   (identity rows of the
+ * constrained DoFs included; b / dinv / xold may be NULL where the mode does not read them; out may alias xold, never x).
+ * Needs the chunked cell loop (environment MGB_CHUNKED=1 when the operator is created): mgb_operator_fused_available
+ * returns 1 if this operator can run it for vectors of its own layout, else the call fails with MGB_ERROR. */
+int  mgb_operator_fused_available(const mgb_operator *op);
+int  mgb_operator_vmult_fused(const mgb_operator *op, mgb_vector *out, const mgb_vector *x, int mode, const mgb_vector *b,
+                              const mgb_vector *dinv, const mgb_vector *xold, double f1, double f2);
 /* General (non-Cartesian) cells -- what MatrixFree does for a mapping that is not Cartesian (include/operator.h:37-42 asks
  * for update_gradients; the reference's own meshes are all axis-aligned cubes): 8 vertices per cell, lexicographic with x
  * fastest, trilinear geometry (MappingQ1).  All subsequent cell loops (vmult, interface operators, diagonal) evaluate

@@ -13,13 +13,31 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 
+_NATIVE = None
+
+
+def build_native():
+    """build the library for THIS machine's CPU (-march=native) when a compiler is present -- the timed host baseline should
+    use the vector width of the box it runs on; returns the description of the build that load() will use"""
+    global _NATIVE
+    if _LIB is not None:
+        return _NATIVE or "-march=x86-64-v3 build"
+    try:
+        subprocess.check_call(["make", "-C", _HERE, "native"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        _NATIVE = "-O3 -march=native build of this machine"
+    except (OSError, subprocess.CalledProcessError):
+        _NATIVE = None
+    return _NATIVE or "-march=x86-64-v3 build"
+
+
 def load():
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = os.path.join(_HERE, "_build", "libmgcpu.so")
+    path = os.path.join(_HERE, "_build", "libmgcpu_native.so" if _NATIVE else "libmgcpu.so")
     if not os.path.exists(path):
         subprocess.check_call(["make", "-C", _HERE])
+        path = os.path.join(_HERE, "_build", "libmgcpu.so")
     lib = C.CDLL(path)
     P = C.c_void_p
     lib.mgcpu_create.restype = P
@@ -80,7 +98,7 @@ class CpuMultigrid:
             fine, coarse, tm = self.maps[l], self.maps[l - 1], tmaps[l]
             first = np.ascontiguousarray(tm.fine_first(), dtype=np.uint32)
             nch = np.ascontiguousarray(tm.n_children(), dtype=np.uint8)
-            w = np.ascontiguousarray(ref.transfer_weights(fine, coarse, first, nch), dtype=np.float64)
+            w = np.ascontiguousarray(ref.transfer_weights_uniform(fine, coarse, first, nch), dtype=np.float64)
             own = np.ascontiguousarray(fine.own_idx, dtype=np.uint32)
             P1 = np.ascontiguousarray(coarse.fe.Ph, dtype=np.float64)
             self._keep += [first, nch, w, own, P1]

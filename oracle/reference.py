@@ -556,6 +556,39 @@ def transfer_weights(fine, coarse, fine_first, n_children):
     return w
 
 
+def transfer_weights_uniform(fine, coarse, fine_first, n_children):
+    """transfer_weights for fine meshes WITHOUT hanging nodes, vectorised (the L=7 host baseline of bench.py needs it): a
+    coarse cell's patch is the cell itself or its 8 children in Morton order (x fastest); node (i,j,k) of child (a,b,c)
+    also belongs to an earlier child of the same patch iff it lies on a low face towards one (a=1,i=0 / b=1,j=0 / c=1,k=0),
+    so counting every (patch, DoF) pair once is a static mask per child.  Checked against transfer_weights in
+    tests/test_oracle.py."""
+    if np.any(fine.mask >> 3):
+        raise ValueError("transfer_weights_uniform: fine mesh has hanging nodes")
+    n = fine.fe.n
+    i, j, k = np.meshgrid(np.arange(n), np.arange(n), np.arange(n), indexing="ij")
+    i, j, k = (a.transpose(2, 1, 0).ravel() for a in (i, j, k))   # lexicographic, x fastest
+    first = np.ones((8, n ** 3), dtype=bool)
+    for ch in range(8):
+        a, b, c = ch & 1, (ch >> 1) & 1, (ch >> 2) & 1
+        first[ch] = ~(((a == 1) & (i == 0)) | ((b == 1) & (j == 0)) | ((c == 1) & (k == 0)))
+    nch = np.asarray(n_children).astype(np.int64)
+    if not np.all((nch == 1) | (nch == 8)):
+        raise ValueError("transfer_weights_uniform: patches of 1 or 8 cells only")
+    parent = np.repeat(np.arange(coarse.n_cells), nch)
+    child = np.arange(fine.n_cells) - np.asarray(fine_first).astype(np.int64)[parent]
+    val = np.zeros(fine.n_dofs)
+    for ch in range(8):
+        cells = np.nonzero((child == ch) & (nch[parent] == 8))[0]
+        if len(cells):
+            val += np.bincount(fine.own_idx[cells][:, first[ch]].ravel(), minlength=fine.n_dofs)
+    single = np.nonzero(nch[parent] == 1)[0]
+    if len(single):
+        val += np.bincount(fine.own_idx[single].ravel(), minlength=fine.n_dofs)
+    w = np.where(val > 0, 1.0 / np.maximum(val, 1), 0.0)
+    w[fine.constrained] = 0.0
+    return w
+
+
 # ----------------------------------------------------------------------------------------- multigrid
 class Multigrid:
     """Multigrid<Vector>::cycle / level_v_step + PreconditionMG::vmult for a global-coarsening hierarchy
@@ -629,6 +662,69 @@ def assemble_rhs_constant(maps):
             r = r @ maps.C(m)
         np.add.at(rhs, maps.eval_idx[c][~maps.eval_flag[c]], r[~maps.eval_flag[c]])
     return rhs
+
+
+GAUSSIAN_CENTER, GAUSSIAN_WIDTH = np.array([-0.5, -0.5, -0.5]), 0.1   # multigrid_throughput.cc:2294-2295
+
+
+def gaussian_solution(x):
+    """GaussianSolution::value (multigrid_throughput.cc:60-89) at points x[..., 3]"""
+    r2 = np.sum((np.asarray(x) - GAUSSIAN_CENTER) ** 2, axis=-1)
+    return np.exp(-r2 / GAUSSIAN_WIDTH ** 2) / (np.sqrt(2.0 * np.pi) * GAUSSIAN_WIDTH) ** 3
+
+
+def gaussian_rhs(x):
+    """GaussianRightHandSide::value (multigrid_throughput.cc:92-127) = -laplace(GaussianSolution)"""
+    r2 = np.sum((np.asarray(x) - GAUSSIAN_CENTER) ** 2, axis=-1)
+    w2 = GAUSSIAN_WIDTH ** 2
+    return (2 * 3 - 4 * r2 / w2) / w2 * np.exp(-r2 / w2) / (np.sqrt(2.0 * np.pi) * GAUSSIAN_WIDTH) ** 3
+
+
+def assemble_rhs_gaussian(maps, return_lift=False):
+    """Operator::rhs for SimulationType=Gaussian (include/operator.h:362-447, multigrid_throughput.cc:2292-2299):
+      b_i = int f phi_i  with QGauss(p+1), constraints resolved in the scatter (:371-413),
+      b  -= A_hn x_D     (:415-446): x_D holds GaussianSolution at the support points of the Dirichlet DoFs
+                         (interpolate_boundary_values, :2309-2310; constraints.distribute), A_hn is the cell loop of a
+                         MatrixFree that knows the hanging-node constraints only -- Dirichlet entries are READ here, and a
+                         hanging node on the boundary is read through its parents' Dirichlet values -- and rows of
+                         constrained DoFs are dropped (constraints.set_zero)."""
+    fe, n = maps.fe, maps.fe.n
+    # quadrature points of every cell, lexicographic with x fastest
+    q1 = fe.xq
+    refq = np.stack(np.meshgrid(q1, q1, q1, indexing="ij"), axis=-1).transpose(2, 1, 0, 3).reshape(n ** 3, 3)
+    origin = -1.0 + maps.h[:, None] * maps.cell_xyz
+    xq = origin[:, None, :] + maps.h[:, None, None] * refq[None, :, :]
+    w3 = np.einsum("k,j,i->kji", fe.wq, fe.wq, fe.wq).ravel()
+    fq = gaussian_rhs(xq) * w3[None, :] * (maps.h ** 3)[:, None]                        # f(x_q) JxW
+    B = fe.B                                                                            # B[q, i] = phi_i(x_q)
+    loc = fq @ np.einsum("ak,bj,ci->abckji", B, B, B).reshape(n ** 3, n ** 3)          # sum_q fq[q] phi_i(x_q), (qz,qy,qx) x (k,j,i)
+    # Dirichlet values at the support points of the flagged entries
+    xd = np.zeros(maps.n_dofs)
+    coords = maps.dof_coordinates()
+    bdofs = boundary_dofs(maps)
+    xd[bdofs] = gaussian_solution(coords[bdofs])
+    A_ref = element_matrix_reference(fe)
+    rhs = np.zeros(maps.n_dofs)
+    lift_total = np.zeros(maps.n_dofs)
+    for m in np.unique(maps.mask):
+        c = np.nonzero(maps.mask == m)[0]
+        idx, flag = maps.eval_idx[c], maps.eval_flag[c]
+        r = loc[c]
+        u = xd[idx]                                                                     # Dirichlet entries are read
+        if m >> 3:
+            u = u @ maps.C(m).T
+        lift = (u @ A_ref.T) * maps.h[c][:, None]
+        if m >> 3:
+            r, lift = r @ maps.C(m), lift @ maps.C(m)
+        np.add.at(rhs, idx[~flag], r[~flag])
+        np.add.at(lift_total, idx[~flag], lift[~flag])
+    rhs -= lift_total
+    return (rhs, xd) if return_lift else rhs
+
+
+def boundary_dofs(maps):
+    """DoFs on the boundary that carry a Dirichlet value: the entries flagged in the evaluation table (bit 31)"""
+    return np.unique(maps.eval_idx[maps.eval_flag])
 
 
 def polynomial_coarsening_sequence_bisect(degree):

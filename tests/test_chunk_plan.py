@@ -9,7 +9,7 @@ from util import mesh_sequence
 
 CASES = [("hypercube", 3, 1), ("hypercube", 3, 2), ("hypercube", 3, 3), ("hypercube", 3, 4), ("hypercube", 2, 5), ("hypercube", 2, 6),
          ("hypercube", 4, 4), ("quadrant", 3, 1), ("quadrant", 3, 2), ("quadrant", 4, 4), ("quadrant", 3, 3), ("annulus", 4, 2),
-         ("annulus", 5, 4), ("quadrant", 3, 6)]
+         ("annulus", 5, 4), ("quadrant", 3, 6), ("quadrant", 6, 4), ("annulus", 6, 4), ("circle", 4, 2)]
 
 
 @pytest.mark.parametrize("geometry,nref,degree", CASES)
