@@ -168,6 +168,19 @@ SIGNATURES = {
     "mgb_operator_initialize_dof_vector": (C.c_int, [P, PP]),
     "mgb_operator_vmult": (C.c_int, [P, P, P]),
     "mgb_operator_tvmult": (C.c_int, [P, P, P]),
+    "mgb_transfer_prolongate": (C.c_int, [P, P, P]),
+    "mgb_level_copy_create": (C.c_int, [P, P, PP]),
+    "mgb_level_copy_destroy": (None, [P]),
+    "mgb_level_copy_to_mg": (C.c_int, [P, P, P]),
+    "mgb_level_copy_from_mg": (C.c_int, [P, P, P]),
+    "mgb_multigrid_create": (C.c_int, [C.c_int, PP, PP, PP, P, C.c_uint, C.c_double, C.c_double, PP]),
+    "mgb_multigrid_destroy": (None, [P]),
+    "mgb_multigrid_set_edge_in": (C.c_int, [P, C.c_int]),
+    "mgb_multigrid_set_level_copies": (C.c_int, [P, PP]),
+    "mgb_multigrid_vcycle": (C.c_int, [P, P, P]),
+    "mgb_multigrid_enable_timers": (C.c_int, [P, C.c_int]),
+    "mgb_multigrid_collect_times": (C.c_int, [P, C.POINTER(C.c_double)]),
+    "mgb_cg_solve": (C.c_int, [P, P, P, P, C.c_uint, C.c_double, C.c_double, C.POINTER(C.c_uint), C.POINTER(C.c_double)]),
     "mgb_operator_fused_available": (C.c_int, [P]),
     "mgb_operator_vmult_fused": (C.c_int, [P, P, P, C.c_int, P, P, P, C.c_double, C.c_double]),
     "mgb_operator_vmult_interface_down": (C.c_int, [P, P, P]),

@@ -333,7 +333,12 @@ class CopyIndices:
         self.distributed = bool(v.distributed)
         self.owned_begin, self.n_owned, self.n_ghost = int(v.owned_begin), int(v.n_owned), int(v.n_ghost)
         self.ghost_global = _arr(v.ghost_global, v.n_ghost, np.int64)
-        lib.mgb_copy_indices_destroy(h)
+        self._lib, self._h = lib, h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.mgb_copy_indices_destroy(self._h)
+        self._h = None
 
 
 class TransferMap:
@@ -619,10 +624,86 @@ class MGTwoLevelTransfer:
     def restrict_and_add(self, dst_coarse, src_fine):
         _check(self._lib.mgb_transfer_restrict_and_add(self._h, dst_coarse._h, src_fine._h))
 
+    def prolongate(self, dst_fine, src_coarse):
+        """MGTwoLevelTransfer::prolongate: dst = P src (no accumulation)"""
+        _check(self._lib.mgb_transfer_prolongate(self._h, dst_fine._h, src_coarse._h))
+
     def __del__(self):
         if getattr(self, "_h", None) and not self._borrowed:
             self._lib.mgb_transfer_destroy(self._h)
         self._h = None
+
+
+class LevelCopy:
+    """device copy of copy_indices[level]: MGLevelGlobalTransfer::copy_to_mg / copy_from_mg for one level"""
+
+    def __init__(self, copy_indices, level_op):
+        self._lib = _lib.load()
+        self._owner = (copy_indices, level_op)
+        h = C.c_void_p()
+        _check(self._lib.mgb_level_copy_create(copy_indices._h, level_op._h, C.byref(h)))
+        self._h = h
+
+    def copy_to_mg(self, dst_level, src_active):
+        _check(self._lib.mgb_level_copy_to_mg(self._h, dst_level._h, src_active._h))
+
+    def copy_from_mg(self, dst_active, src_level):
+        _check(self._lib.mgb_level_copy_from_mg(self._h, dst_active._h, src_level._h))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.mgb_level_copy_destroy(self._h)
+        self._h = None
+
+
+class Multigrid:
+    """Multigrid + PreconditionMG over borrowed level operators, smoothers and two-level transfers (mg_solve,
+    multigrid_throughput.cc:1082-1133).  operators / smoothers / transfers: lists coarse -> fine, entry 0 of smoothers and
+    transfers ignored; coarse_precond: a PreconditionChebyshev on level 0 (cg_with_chebyshev) or None (cg)."""
+
+    N_STAGES = 7
+
+    def __init__(self, operators, smoothers, transfers, coarse_precond=None, coarse_maxiter=10000, coarse_abstol=1e-20,
+                 coarse_reltol=1e-4, edge_in=False, level_copies=None):
+        self._lib = _lib.load()
+        self._owner = (operators, smoothers, transfers, coarse_precond, level_copies)
+        n = len(operators)
+        P = C.c_void_p
+        arr = lambda objs: (P * n)(*[(o._h if o is not None else None) for o in objs])
+        h = P()
+        _check(self._lib.mgb_multigrid_create(n, arr(operators), arr(smoothers), arr(transfers),
+                                              coarse_precond._h if coarse_precond is not None else None, coarse_maxiter,
+                                              coarse_abstol, coarse_reltol, C.byref(h)))
+        self._h, self.n_levels = h, n
+        if edge_in:
+            _check(self._lib.mgb_multigrid_set_edge_in(self._h, 1))
+        if level_copies is not None:
+            _check(self._lib.mgb_multigrid_set_level_copies(self._h, arr(level_copies)))
+
+    def vmult(self, dst, src):
+        """PreconditionMG::vmult"""
+        _check(self._lib.mgb_multigrid_vcycle(self._h, dst._h, src._h))
+
+    def enable_timers(self, on=True):
+        _check(self._lib.mgb_multigrid_enable_timers(self._h, 1 if on else 0))
+
+    def collect_times(self):
+        out = np.zeros((self.n_levels, self.N_STAGES))
+        _check(self._lib.mgb_multigrid_collect_times(self._h, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.mgb_multigrid_destroy(self._h)
+        self._h = None
+
+
+def cg_solve(A, x, b, preconditioner=None, maxiter=10000, abstol=1e-20, reltol=1e-4):
+    """SolverCG(ReductionControl(maxiter, abstol, reltol)).solve(A, x, b, preconditioner) from x = 0; returns (n_iterations, residual)"""
+    its, res = C.c_uint(0), C.c_double(0.0)
+    _check(_lib.load().mgb_cg_solve(A._h, preconditioner._h if preconditioner is not None else None, x._h, b._h, maxiter, abstol, reltol,
+                                    C.byref(its), C.byref(res)))
+    return int(its.value), float(res.value)
 
 
 class Problem:

@@ -1,5 +1,5 @@
 // extern "C" boundary (include/mgb200.h): plain pointers and sizes in, opaque handles out.
-#include "mgb200.h"
+#include "capi_handles.h"
 
 #include "chunks.h"
 #include "comm.h"
@@ -12,84 +12,15 @@
 
 using namespace mgb;
 
-namespace
+namespace mgb
 {
-  thread_local std::string g_error;
-
-  template <class F> int guarded(F &&f)
+  std::string &capi_last_error()
   {
-    try
-      {
-        f();
-        return 0;
-      }
-    catch (const std::exception &e)
-      {
-        g_error = e.what();
-        return 1;
-      }
-    catch (...)
-      {
-        g_error = "unknown exception";
-        return 2;
-      }
+    thread_local std::string e;
+    return e;
   }
-} // namespace
+} // namespace mgb
 
-struct mgb_mesh
-{
-  Mesh m;
-};
-struct mgb_dofmap
-{
-  const DoFMap           *d = nullptr;
-  std::unique_ptr<DoFMap> owned;
-};
-struct mgb_transfer_map
-{
-  TransferMap t;
-  long long   n_fine_cells = 0;
-};
-struct mgb_level_edges
-{
-  LevelEdges e;
-};
-struct mgb_copy_indices
-{
-  CopyIndices c;
-};
-struct mgb_vector
-{
-  int                           type = MGB_DOUBLE;
-  DVec<double>                 *pd   = nullptr;
-  DVec<float>                  *pf   = nullptr;
-  std::unique_ptr<DVec<double>> od;
-  std::unique_ptr<DVec<float>>  of;
-};
-struct mgb_operator
-{
-  int                                type = MGB_DOUBLE;
-  OperatorT<double>                 *pd   = nullptr;
-  OperatorT<float>                  *pf   = nullptr;
-  std::unique_ptr<OperatorT<double>> od;
-  std::unique_ptr<OperatorT<float>>  of;
-};
-struct mgb_chebyshev
-{
-  int                                 type = MGB_DOUBLE;
-  ChebyshevT<double>                 *pd   = nullptr;
-  ChebyshevT<float>                  *pf   = nullptr;
-  std::unique_ptr<ChebyshevT<double>> od;
-  std::unique_ptr<ChebyshevT<float>>  of;
-};
-struct mgb_transfer
-{
-  int                                        type = MGB_DOUBLE;
-  TwoLevelTransferT<double>                 *pd   = nullptr;
-  TwoLevelTransferT<float>                  *pf   = nullptr;
-  std::unique_ptr<TwoLevelTransferT<double>> od;
-  std::unique_ptr<TwoLevelTransferT<float>>  of;
-};
 struct mgb_problem
 {
   std::unique_ptr<ProblemBase>                         p;
@@ -104,11 +35,6 @@ struct mgb_problem
 
 namespace
 {
-  void require_same_type(int a, int b)
-  {
-    if (a != b)
-      throw std::runtime_error("number types of the arguments differ");
-  }
   void fill_result(const Result &r, mgb_result *o)
   {
     std::memset(o, 0, sizeof(*o));
@@ -167,7 +93,7 @@ namespace
 
 extern "C" {
 
-const char *mgb_last_error(void) { return g_error.c_str(); }
+const char *mgb_last_error(void) { return capi_last_error().c_str(); }
 const char *mgb_version(void) { return "mgb200 0.1 (sm_100a)"; }
 
 int mgb_init(int device)

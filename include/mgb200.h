@@ -290,6 +290,50 @@ void mgb_transfer_destroy(mgb_transfer *t);
 int  mgb_transfer_prolongate_and_add(const mgb_transfer *t, mgb_vector *dst_fine, const mgb_vector *src_coarse);
 int  mgb_transfer_restrict_and_add(const mgb_transfer *t, mgb_vector *dst_coarse, const mgb_vector *src_fine);
 
+/* MGTwoLevelTransfer::prolongate / MGTransferMatrixFree::prolongate: dst_fine = P src_coarse (no accumulation) */
+int  mgb_transfer_prolongate(const mgb_transfer *t, mgb_vector *dst_fine, const mgb_vector *src_coarse);
+
+/* ---- local smoothing: MGLevelGlobalTransfer::copy_to_mg / copy_from_mg through copy_indices ------------ *
+ * (MGTransferMatrixFree as built at multigrid_throughput.cc:1800-1802; the double <-> MGNumberType casts of :528-550 happen
+ * here).  One object per level: the device copy of mgb_copy_indices for that level; level_op gives the level vectors'
+ * layout and number type.  On several ranks the owner of the active DoF holds the pair and the exchange goes through an
+ * internal ghosted level vector. */
+typedef struct mgb_level_copy mgb_level_copy;
+int  mgb_level_copy_create(const mgb_copy_indices *ci, const mgb_operator *level_op, mgb_level_copy **out);
+void mgb_level_copy_destroy(mgb_level_copy *c);
+/* dst_level = 0 except the entries of the active DoFs that live on this level (src_active: double, active-mesh layout) */
+int  mgb_level_copy_to_mg(const mgb_level_copy *c, mgb_vector *dst_level, const mgb_vector *src_active);
+/* the active DoFs living on this level receive the level's values; all other entries of dst_active are left alone */
+int  mgb_level_copy_from_mg(const mgb_level_copy *c, mgb_vector *dst_active, const mgb_vector *src_level);
+
+/* ---- Multigrid + PreconditionMG + SolverCG over borrowed handles (mg_solve, multigrid_throughput.cc:1082-1133) ---- *
+ * level_operators[0..n_levels-1] coarse -> fine (mg::Matrix of MGInterfaceOperator: vmult_interface_down / _up),
+ * smoothers[l] and transfers[l] (between l-1 and l) for l >= 1 (entries 0 ignored), the coarse level solved by
+ * SolverCG(ReductionControl(coarse_maxiter, coarse_abstol, coarse_reltol)) with coarse_preconditioner (a Chebyshev
+ * smoother on level 0: CoarseGridSolverType cg_with_chebyshev) or PreconditionIdentity (NULL: cg), :887-944.
+ * All handles are borrowed and must outlive the multigrid object. */
+typedef struct mgb_multigrid mgb_multigrid;
+#define MGB_N_STAGES 7 /* pre-smoothing, residual, restriction, coarse solve, prolongation, edge prolongation, post-smoothing */
+int  mgb_multigrid_create(int n_levels, const mgb_operator *const *level_operators, mgb_chebyshev *const *smoothers,
+                          const mgb_transfer *const *transfers, mgb_chebyshev *coarse_preconditioner, unsigned coarse_maxiter,
+                          double coarse_abstol, double coarse_reltol, mgb_multigrid **out);
+void mgb_multigrid_destroy(mgb_multigrid *m);
+/* Multigrid::set_edge_in_matrix (:1101-1105): after the prolongation defect -= vmult_interface_up(solution) */
+int  mgb_multigrid_set_edge_in(mgb_multigrid *m, int on);
+/* local smoothing: one mgb_level_copy per level (copy_to_mg / copy_from_mg through copy_indices); NULL = global coarsening,
+ * where the top level IS the outer vector (MGTransferGlobalCoarsening) */
+int  mgb_multigrid_set_level_copies(mgb_multigrid *m, const mgb_level_copy *const *copies);
+/* PreconditionMG::vmult: dst = M^-1 src, double vectors of the outer operator's layout */
+int  mgb_multigrid_vcycle(mgb_multigrid *m, mgb_vector *dst, const mgb_vector *src);
+/* the seven stage timers the reference connects to the Multigrid signals (:1163-1234): CUDA-event pairs around every
+ * stage of every level while enabled; collect returns the seconds accumulated since the last call, [level][stage] */
+int  mgb_multigrid_enable_timers(mgb_multigrid *m, int on);
+int  mgb_multigrid_collect_times(mgb_multigrid *m, double *seconds /* n_levels * MGB_N_STAGES */);
+/* SolverCG<Vector>(ReductionControl(maxiter, abstol, reltol)).solve(A, x, b, preconditioner) from x = 0 (:1247-1248, 1625-1635);
+ * preconditioner NULL = PreconditionIdentity; fails (SolverControl::NoConvergence) when maxiter is reached */
+int  mgb_cg_solve(const mgb_operator *A, mgb_multigrid *preconditioner, mgb_vector *x, const mgb_vector *b, unsigned maxiter,
+                  double abstol, double reltol, unsigned *n_iterations, double *final_residual);
+
 /* ---- JSON-driven problem: run() + solve_with_* + mg_solve -------------------------------------------- */
 typedef struct
 {

@@ -269,8 +269,11 @@ def cell_apply_collocation(fe, u):
 class Operator:
     """Operator<3,1,double> restated (include/operator.h).  edge_* only for local-smoothing levels."""
 
-    def __init__(self, maps, edge_constrained=None, edge_cells=None, has_edge_global=False):
+    def __init__(self, maps, edge_constrained=None, edge_cells=None, has_edge_global=False, rnd=None):
         self.maps = maps
+        # rnd: rounding applied to every vector a kernel writes -- identity for FP64 levels, round_f32 models
+        # MGNumberType=float (multigrid_throughput.cc:2432-2433: level vectors and operators in float)
+        self.rnd = rnd if rnd is not None else (lambda v: v)
         self.edge = np.zeros(0, dtype=np.int64) if edge_constrained is None else np.asarray(edge_constrained, dtype=np.int64)
         self.edge_cells = None if edge_cells is None else np.asarray(edge_cells, dtype=np.int64)
         self.has_edge_global = has_edge_global
@@ -299,7 +302,7 @@ class Operator:
     def vmult_interface_down(self, src):
         dst = self.cell_loop(src)
         dst[self.maps.constrained] = src[self.maps.constrained]    # include/operator.h:198-200
-        return dst
+        return self.rnd(dst)
 
     def vmult(self, src):
         src = src.copy()
@@ -308,7 +311,7 @@ class Operator:
         dst = self.cell_loop(src)
         dst[self.maps.constrained] = src[self.maps.constrained]    # :170-172
         dst[self.edge] = saved                                     # :175-182
-        return dst
+        return self.rnd(dst)
 
     Tvmult = vmult
 
@@ -317,7 +320,7 @@ class Operator:
             return np.zeros(self.maps.n_dofs)                      # :206-210
         cpy = np.zeros_like(src)
         cpy[self.edge] = src[self.edge]                            # :216-221
-        return self.cell_loop(cpy, self.edge_cells)                # :224-225
+        return self.rnd(self.cell_loop(cpy, self.edge_cells))      # :224-225
 
     def compute_inverse_diagonal(self):
         """MatrixFreeTools::compute_diagonal + threshold inversion (include/operator.h:228-242; SURVEY.md A.10)"""
@@ -386,11 +389,14 @@ class IterationNumberControl:
         return "iterate"
 
 
-def solver_cg(A, x, b, P, control, lanczos=None):
+def solver_cg(A, x, b, P, control, lanczos=None, rnd=None):
     """SolverCG::solve (SURVEY.md A.6). A, P: callables (P None = PreconditionIdentity). x modified in place.
-    lanczos: optional (diag, offdiag) lists receiving the projected tridiagonal matrix entries."""
+    lanczos: optional (diag, offdiag) lists receiving the projected tridiagonal matrix entries.
+    rnd: rounding of the vectors the solver updates (round_f32 for a solver running on float vectors)"""
+    if rnd is None:
+        rnd = lambda v: v
     if np.any(x != 0):
-        g = A(x) - b
+        g = rnd(A(x) - b)
     else:
         g = -b.copy()
     res = np.sqrt(g @ g)
@@ -409,7 +415,7 @@ def solver_cg(A, x, b, P, control, lanczos=None):
                 h = g
                 gh = res * res
             beta = gh / gh_old
-            d = -h + beta * d
+            d = rnd(-h + beta * d)
             if lanczos is not None:
                 lanczos[0].append(1.0 / prev_alpha + eba)
                 lanczos[1].append(np.sqrt(beta) / prev_alpha)
@@ -425,8 +431,8 @@ def solver_cg(A, x, b, P, control, lanczos=None):
         h = A(d)
         alpha = gh / (d @ h)
         prev_alpha = alpha
-        x += alpha * d
-        g += alpha * h
+        x[:] = rnd(x + alpha * d)
+        g = rnd(g + alpha * h)
         res = np.sqrt(abs(g @ g))
         if control.check(it, res) != "iterate":
             return it
@@ -438,7 +444,8 @@ class PreconditionChebyshev:
 
     def __init__(self, op, degree=3, smoothing_range=20.0, eig_cg_n_iterations=20, owned_begin=0):
         self.op, self.degree, self.smoothing_range, self.eig_its = op, degree, smoothing_range, eig_cg_n_iterations
-        self.dinv = op.compute_inverse_diagonal()
+        self.rnd = getattr(op, "rnd", lambda v: v)
+        self.dinv = self.rnd(op.compute_inverse_diagonal())
         self.owned_begin = owned_begin
         self.done = False
 
@@ -450,7 +457,8 @@ class PreconditionChebyshev:
         z -= z.sum() / n
         diag, off = [], []
         x = np.zeros(n)
-        solver_cg(self.op.vmult, x, z, lambda g: self.dinv * g, IterationNumberControl(self.eig_its, 1e-10), (diag, off))
+        solver_cg(self.op.vmult, x, self.rnd(z), lambda g: self.rnd(self.dinv * g), IterationNumberControl(self.eig_its, 1e-10), (diag, off),
+                  rnd=self.rnd)
         if not diag:
             self.lmin = self.lmax = 1.0
         else:
@@ -463,7 +471,7 @@ class PreconditionChebyshev:
 
     def vmult(self, rhs):
         self.estimate_eigenvalues()
-        x = (1.0 / self.theta) * (self.dinv * rhs)
+        x = self.rnd((1.0 / self.theta) * (self.dinv * rhs))
         if self.degree < 2 or abs(self.delta) < 1e-40:
             return x
         x_old = np.zeros_like(x)
@@ -477,14 +485,14 @@ class PreconditionChebyshev:
                 new = (1.0 + f1) * x + f2 * (self.dinv * (rhs - t))
             else:
                 new = (1.0 + f1) * x - f1 * x_old + f2 * (self.dinv * (rhs - t))
-            x_old, x = x, new
+            x_old, x = x, self.rnd(new)
         return x
 
     def step(self, x, rhs):
         self.estimate_eigenvalues()
         t = self.op.vmult(x)
         new = x + (1.0 / self.theta) * (self.dinv * (rhs - t))
-        x_old, x = x, new
+        x_old, x = x, self.rnd(new)
         if self.degree < 2 or abs(self.delta) < 1e-40:
             return x
         rhok, sigma = self.delta / self.theta, self.theta / self.delta
@@ -494,8 +502,13 @@ class PreconditionChebyshev:
             f1, f2 = rhokp * rhok, 2.0 * rhokp / self.delta
             rhok = rhokp
             new = (1.0 + f1) * x - f1 * x_old + f2 * (self.dinv * (rhs - t))
-            x_old, x = x, new
+            x_old, x = x, self.rnd(new)
         return x
+
+
+def round_f32(v):
+    """round to the nearest float32, keep float64 storage (models vectors stored in MGNumberType=float)"""
+    return np.asarray(v, dtype=np.float32).astype(np.float64)
 
 
 # ----------------------------------------------------------------------------------------- transfers
@@ -538,11 +551,13 @@ class MGTwoLevelTransfer:
         self.P = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))),
                                shape=(fine.n_dofs, coarse.n_dofs)).tocsr()
 
+    rnd = staticmethod(lambda v: v)   # set to round_f32 for transfers between float level vectors
+
     def prolongate_and_add(self, dst_fine, src_coarse):
-        dst_fine += self.P @ src_coarse
+        dst_fine[:] = self.rnd(dst_fine + self.P @ src_coarse)
 
     def restrict_and_add(self, dst_coarse, src_fine):
-        dst_coarse += self.P.T @ src_fine
+        dst_coarse[:] = self.rnd(dst_coarse + self.P.T @ src_fine)
 
 
 def transfer_weights(fine, coarse, fine_first, n_children):
@@ -600,15 +615,17 @@ class Multigrid:
         self.ops, self.smoothers, self.transfers, self.coarse, self.edge_in = operators, smoothers, transfers, coarse, edge_in
         self.copy_indices = copy_indices
         self.max_level = len(operators) - 1
+        self.rnd = getattr(operators[-1], "rnd", lambda v: v)   # round_f32: level vectors in float (the casts of
+                                                                 # multigrid_throughput.cc:528-550 at copy_to_mg / copy_from_mg)
 
     def vmult(self, src):
         """PreconditionMG::vmult: copy_to_mg, V-cycle, copy_from_mg"""
         self.defect = [np.zeros(op.m()) for op in self.ops]
         if self.copy_indices is None:
-            self.defect[-1][:] = src
+            self.defect[-1][:] = self.rnd(src)
         else:
             for l, (ai, li) in enumerate(self.copy_indices):
-                self.defect[l][li] = src[ai]
+                self.defect[l][li] = self.rnd(src[ai])
         self.solution = [np.zeros(op.m()) for op in self.ops]
         self.t = [np.zeros(op.m()) for op in self.ops]
         self.level_v_step(self.max_level)
@@ -624,13 +641,13 @@ class Multigrid:
             self.solution[0] = self.coarse(self.defect[0])
             return
         self.solution[l] = self.smoothers[l].vmult(self.defect[l])
-        self.t[l] = self.defect[l] - self.ops[l].vmult_interface_down(self.solution[l])
+        self.t[l] = self.rnd(self.defect[l] - self.ops[l].vmult_interface_down(self.solution[l]))
         self.transfers[l].restrict_and_add(self.defect[l - 1], self.t[l])
         self.level_v_step(l - 1)
         self.transfers[l].prolongate_and_add(self.solution[l], self.solution[l - 1])
         if self.edge_in:
             self.t[l] = self.ops[l].vmult_interface_up(self.solution[l])
-            self.defect[l] -= self.t[l]
+            self.defect[l] = self.rnd(self.defect[l] - self.t[l])
         self.solution[l] = self.smoothers[l].step(self.solution[l], self.defect[l])
 
 
@@ -646,7 +663,7 @@ class CoarseGridCG:
         x = np.zeros_like(rhs)
         ctl = ReductionControl(*self.ctl_args)
         P = None if self.precond is None else self.precond.vmult
-        self.total_iterations += solver_cg(self.op.vmult, x, rhs, P, ctl)
+        self.total_iterations += solver_cg(self.op.vmult, x, rhs, P, ctl, rnd=getattr(self.op, "rnd", None))
         return x
 
 

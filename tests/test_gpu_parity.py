@@ -431,3 +431,79 @@ def test_general_geometry_operator(gpu, geometry, L, p, deformation, number):
         rhs.from_numpy(b)
         cheb.vmult(dst, rhs)
         assert rel_l2(dst.to_numpy(), ocheb.vmult(b)) < 1e-10
+
+
+# ------------------------------------------------------------------------------------ MGNumberType = float (the reference's default)
+F32 = np.float32
+
+
+@pytest.mark.parametrize("geometry,L,p", [("hypercube", 3, 4), ("quadrant", 4, 2), ("annulus", 5, 3), ("quadrant", 3, 1)])
+def test_float_kernels_against_the_float_oracle(gpu, geometry, L, p):
+    """Cartesian vmult, inverse diagonal, Chebyshev and the two-level transfers of the float instantiation against the
+    oracle with float32-rounded level vectors (oracle/reference.py round_f32): 1e-5 relative"""
+    mg = gpu
+    seq = mesh_sequence(geometry, L)
+    df, dc = mg.DoFMap(seq[-1], p), mg.DoFMap(seq[-2], p)
+    fine, coarse = ref.LevelMaps.from_dofmap(df), ref.LevelMaps.from_dofmap(dc)
+    oracle = ref.Operator(fine, rnd=ref.round_f32)
+    op, opc = mg.Operator(df, number_type=mg.FLOAT), mg.Operator(dc, number_type=mg.FLOAT)
+    x = ref.round_f32(seeded(fine.n_dofs))
+    src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+    src.from_numpy(x.astype(F32))
+    op.vmult(dst, src)
+    assert rel_l2(dst.to_numpy().astype(np.float64), oracle.vmult(x)) < 1e-5
+    diag = op.initialize_dof_vector()
+    op.compute_inverse_diagonal(diag)
+    assert rel_l2(diag.to_numpy().astype(np.float64), oracle.compute_inverse_diagonal()) < 1e-5
+    # Chebyshev: eigenvalue estimate and both entry points
+    cheb_o = ref.PreconditionChebyshev(oracle, 3, 20.0, 20)
+    cheb = mg.PreconditionChebyshev(op, 3, 20.0, 20)
+    cheb_o.estimate_eigenvalues()
+    assert abs(cheb.eigenvalues()[1] - cheb_o.lmax) < 1e-4 * cheb_o.lmax
+    cheb.vmult(dst, src)
+    assert rel_l2(dst.to_numpy().astype(np.float64), cheb_o.vmult(x)) < 1e-4
+    x0 = ref.round_f32(seeded(fine.n_dofs, 5))
+    dst.from_numpy(x0.astype(F32))
+    cheb.step(dst, src)
+    assert rel_l2(dst.to_numpy().astype(np.float64), cheb_o.step(x0.copy(), x)) < 1e-4
+    # h-transfer between float vectors
+    tm = mg.TransferMap(seq[-1], df, seq[-2], dc)
+    T_o = ref.MGTwoLevelTransfer(fine, coarse, tm.fine_first(), tm.n_children())
+    T_o.rnd = ref.round_f32
+    T = mg.MGTwoLevelTransfer(df, dc, tm, op, opc)
+    uc, uf = ref.round_f32(seeded(coarse.n_dofs, 1)), ref.round_f32(seeded(fine.n_dofs, 2))
+    vc, vf = opc.initialize_dof_vector(), op.initialize_dof_vector()
+    vc.from_numpy(uc.astype(F32)), vf.from_numpy(uf.astype(F32))
+    T.prolongate_and_add(vf, vc)
+    e = uf.copy()
+    T_o.prolongate_and_add(e, uc)
+    assert rel_l2(vf.to_numpy().astype(np.float64), e) < 1e-5
+    vc.from_numpy(uc.astype(F32)), vf.from_numpy(uf.astype(F32))
+    T.restrict_and_add(vc, vf)
+    e = uc.copy()
+    T_o.restrict_and_add(e, uf)
+    assert rel_l2(vc.to_numpy().astype(np.float64), e) < 1e-5
+
+
+@pytest.mark.parametrize("geometry,L,p,mg_type", [("hypercube", 3, 4, "HMG-global"), ("quadrant", 4, 2, "HPMG"), ("annulus", 5, 2, "PMG")])
+def test_float_vcycle_and_solve_against_the_float_oracle(gpu, geometry, L, p, mg_type):
+    """MGNumberType=float: the double -> float -> double casts around the V-cycle (multigrid_throughput.cc:528-550), the float
+    V-cycle within 1e-4 of the float32-rounded oracle, and IDENTICAL iteration counts of the double-precision outer CG"""
+    mg = gpu
+    prob = mg.Problem(params(geometry, L, p, mg_type, "cg", number="float"))
+    H = OracleHierarchy(geometry, L, p, mg_type, 3, "cg", number="float")
+    n = H.fine_maps.n_dofs
+    r = seeded(n)
+    r[H.fine_maps.constrained] = 0.0
+    op = prob.fine_operator()                      # double: the outer operator
+    src, dst = op.initialize_dof_vector(), op.initialize_dof_vector()
+    src.from_numpy(r)
+    prob.vcycle(dst, src)                          # double in, double out, float inside
+    y = dst.to_numpy()
+    assert y.dtype == np.float64
+    assert rel_l2(y, H.mg.vmult(r)) < 1e-4
+    np.testing.assert_array_equal(y, ref.round_f32(y))   # the result went through float storage
+    res = prob.solve_once()
+    x, its, _ = H.solve(prob.rhs().to_numpy())
+    assert res["n_iterations"] == its
+    assert rel_l2(prob.solution().to_numpy(), x) < 1e-3

@@ -39,11 +39,14 @@ def gc_hierarchy(geometry, n_ref_global, degree, mg_type="HMG-global"):
 class OracleHierarchy:
     """oracle multigrid built from product-generated maps for a GC hierarchy"""
 
-    def __init__(self, geometry, n_ref_global, degree, mg_type="HMG-global", smoother_degree=3, coarse="cg"):
+    def __init__(self, geometry, n_ref_global, degree, mg_type="HMG-global", smoother_degree=3, coarse="cg", number="double"):
+        """number="float": MGNumberType=float -- every level vector is rounded to float32 when it is written; the outer
+        operator of the CG (self.fine_op) stays in double (multigrid_throughput.cc:2432-2433, 528-550)"""
+        rnd = ref.round_f32 if number == "float" else None
         self.levels = gc_hierarchy(geometry, n_ref_global, degree, mg_type)
         self.dofmaps = [mg.DoFMap(m, d) for m, d in self.levels]
         self.maps = [ref.LevelMaps.from_dofmap(d) for d in self.dofmaps]
-        self.ops = [ref.Operator(m) for m in self.maps]
+        self.ops = [ref.Operator(m, rnd=rnd) for m in self.maps]
         self.tmaps = [None] + [mg.TransferMap(self.levels[l][0], self.dofmaps[l], self.levels[l - 1][0], self.dofmaps[l - 1])
                                for l in range(1, len(self.levels))]
         self.transfers = [None] + [ref.MGTwoLevelTransfer(self.maps[l], self.maps[l - 1], self.tmaps[l].fine_first(),
@@ -53,13 +56,17 @@ class OracleHierarchy:
         cheb = ref.PreconditionChebyshev(self.ops[0], smoother_degree, 20.0, 20) if coarse == "cg_with_chebyshev" else None
         self.coarse = ref.CoarseGridCG(self.ops[0], cheb)
         self.mg = ref.Multigrid(self.ops, self.smoothers, self.transfers, self.coarse)
+        if rnd is not None:
+            for t in self.transfers[1:]:
+                t.rnd = rnd
 
-        self.fine_maps, self.fine_op = self.maps[-1], self.ops[-1]
+        self.fine_maps = self.maps[-1]
+        self.fine_op = ref.Operator(self.maps[-1]) if rnd is not None else self.ops[-1]   # the outer CG runs in double
 
     def solve(self, rhs, reltol=1e-4):
         x = np.zeros_like(rhs)
         ctl = ref.ReductionControl(10000, 1e-20, reltol)
-        its = ref.solver_cg(self.ops[-1].vmult, x, rhs, self.mg.vmult, ctl)
+        its = ref.solver_cg(self.fine_op.vmult, x, rhs, self.mg.vmult, ctl)
         return x, its, ctl
 
 
