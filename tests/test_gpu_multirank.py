@@ -27,7 +27,8 @@ def _run(extra_env, only, port):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(ROOT, "tools", "check_multigpu.py")]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=900)
-    assert r.returncode == 0 and "MULTIGPU PARITY OK" in r.stdout, (r.stdout[-3000:], r.stderr[-3000:])
+    bad = [l for l in (r.stdout + "\n" + r.stderr).splitlines() if any(k in l for k in ("FAIL", "Error", "error", "Traceback", "trap"))]
+    assert r.returncode == 0 and "MULTIGPU PARITY OK" in r.stdout, "\n".join(bad[:12])
     # every rank must hold cells in every case (a case where one rank owns nothing proves nothing about the exchange)
     for line in r.stdout.splitlines():
         if line.startswith("[rank") and "owned=" in line:
