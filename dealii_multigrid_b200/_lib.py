@@ -169,7 +169,9 @@ SIGNATURES = {
     "mgb_operator_vmult": (C.c_int, [P, P, P]),
     "mgb_operator_tvmult": (C.c_int, [P, P, P]),
     "mgb_transfer_prolongate": (C.c_int, [P, P, P]),
+    "mgb_transfer_create_from_arrays": (C.c_int, [P, P, P, PP]),
     "mgb_level_copy_create": (C.c_int, [P, P, PP]),
+    "mgb_level_copy_create_from_arrays": (C.c_int, [C.c_uint32, c_u32p, c_u32p, P, PP]),
     "mgb_level_copy_destroy": (None, [P]),
     "mgb_level_copy_to_mg": (C.c_int, [P, P, P]),
     "mgb_level_copy_from_mg": (C.c_int, [P, P, P]),

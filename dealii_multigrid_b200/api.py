@@ -613,6 +613,10 @@ class MGTwoLevelTransfer:
         self._borrowed = _handle is not None
         if _handle is not None:
             self._h = _handle
+        elif dofs_fine is None:   # plain arrays: the view of the transfer map is passed as the adapter would fill it
+            h = C.c_void_p()
+            _check(self._lib.mgb_transfer_create_from_arrays(C.byref(tmap.view), op_fine._h, op_coarse._h, C.byref(h)))
+            self._h = h
         else:
             h = C.c_void_p()
             _check(self._lib.mgb_transfer_create(dofs_fine._h, dofs_coarse._h, tmap._h, op_fine._h, op_coarse._h, C.byref(h)))

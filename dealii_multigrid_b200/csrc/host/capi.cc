@@ -968,6 +968,56 @@ int mgb_transfer_create(const mgb_dofmap *fine, const mgb_dofmap *coarse, const 
     *out = h.release();
   });
 }
+int mgb_transfer_create_from_arrays(const mgb_transfer_map_view *v, const mgb_operator *opf, const mgb_operator *opc, mgb_transfer **out)
+{
+  return guarded([&] {
+    require_same_type(opf->type, opc->type);
+    if (!v || !v->fine_first || !v->n_children || !v->weight_code || !v->fine_own || v->n_coarse_cells < 0 || v->n_fine_slots < 0)
+      throw std::runtime_error("mgb_transfer_create_from_arrays: fine_first, n_children, weight_code and fine_own are required");
+    TransferMap tm;
+    tm.degree_fine    = v->degree_fine;
+    tm.degree_coarse  = v->degree_coarse;
+    tm.n_coarse_cells = v->n_coarse_cells;
+    tm.fine_first.assign(v->fine_first, v->fine_first + v->n_coarse_cells);
+    tm.n_children.assign(v->n_children, v->n_children + v->n_coarse_cells);
+    tm.n_fine_slots = v->n_fine_slots;
+    tm.weight_code.assign(v->weight_code, v->weight_code + size_t(v->n_fine_slots) * 27);
+    tm.fine_own.assign(v->fine_own, v->fine_own + size_t(v->n_fine_slots) * 27);
+    for (int64_t c = 0; c < v->n_coarse_cells; ++c)
+      if (int64_t(tm.fine_first[c]) + tm.n_children[c] > v->n_fine_slots)
+        throw std::runtime_error("mgb_transfer_create_from_arrays: fine_first + n_children exceeds n_fine_slots");
+    tm.distributed = v->distributed != 0;
+    if (tm.distributed)
+      {
+        Partitioner &pt = tm.part;
+        pt.owned_begin  = v->owned_begin;
+        pt.n_owned      = v->n_owned;
+        pt.n_ghost      = v->n_ghost;
+        pt.ghost_global.assign(v->ghost_global, v->ghost_global + v->n_ghost);
+        pt.ghost_ranks.assign(v->ghost_ranks, v->ghost_ranks + v->n_ghost_ranks);
+        pt.ghost_offsets.assign(v->ghost_offsets, v->ghost_offsets + v->n_ghost_ranks + 1);
+        pt.import_ranks.assign(v->import_ranks, v->import_ranks + v->n_import_ranks);
+        pt.import_offsets.assign(v->import_offsets, v->import_offsets + v->n_import_ranks + 1);
+        pt.import_indices.assign(v->import_indices, v->import_indices + v->n_import_indices);
+      }
+    DoFMap fine, coarse; // only the degrees are read
+    fine.degree   = v->degree_fine;
+    coarse.degree = v->degree_coarse;
+    auto h        = std::make_unique<mgb_transfer>();
+    h->type       = opf->type;
+    if (h->type == MGB_DOUBLE)
+      {
+        h->od = std::make_unique<TwoLevelTransferT<double>>(fine, coarse, tm, *opf->pd, *opc->pd);
+        h->pd = h->od.get();
+      }
+    else
+      {
+        h->of = std::make_unique<TwoLevelTransferT<float>>(fine, coarse, tm, *opf->pf, *opc->pf);
+        h->pf = h->of.get();
+      }
+    *out = h.release();
+  });
+}
 void mgb_transfer_destroy(mgb_transfer *t) { delete t; }
 int  mgb_transfer_prolongate_and_add(const mgb_transfer *t, mgb_vector *dst, const mgb_vector *src)
 {

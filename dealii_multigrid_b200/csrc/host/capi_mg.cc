@@ -198,6 +198,24 @@ int mgb_level_copy_create(const mgb_copy_indices *ci, const mgb_operator *level_
     *out = h.release();
   });
 }
+int mgb_level_copy_create_from_arrays(uint32_t n, const uint32_t *active_idx, const uint32_t *level_idx, const mgb_operator *level_op,
+                                      mgb_level_copy **out)
+{
+  return guarded([&] {
+    if (n && (!active_idx || !level_idx))
+      throw std::runtime_error("mgb_level_copy_create_from_arrays: index arrays required");
+    CopyIndices ci;
+    ci.active_idx.assign(active_idx, active_idx + n);
+    ci.level_idx.assign(level_idx, level_idx + n);
+    auto h  = std::make_unique<mgb_level_copy>();
+    h->type = level_op->type;
+    if (level_op->type == MGB_DOUBLE)
+      h->d = std::make_unique<LevelCopyT<double>>(ci, *level_op->pd);
+    else
+      h->f = std::make_unique<LevelCopyT<float>>(ci, *level_op->pf);
+    *out = h.release();
+  });
+}
 void mgb_level_copy_destroy(mgb_level_copy *c) { delete c; }
 int  mgb_level_copy_to_mg(const mgb_level_copy *c, mgb_vector *dst_level, const mgb_vector *src_active)
 {

@@ -286,6 +286,10 @@ int  mgb_chebyshev_eigenvalues(mgb_chebyshev *c, double *lambda_min_estimate, do
 /* ---- two-level transfer ------------------------------------------------------------------------------ */
 int  mgb_transfer_create(const mgb_dofmap *fine, const mgb_dofmap *coarse, const mgb_transfer_map *map, const mgb_operator *op_fine,
                          const mgb_operator *op_coarse, mgb_transfer **out);
+/* the same from plain arrays (what a deal.II adapter extracts in MGTwoLevelTransfer::reinit): the fields of
+ * mgb_transfer_map_view; n_fine_cells is ignored; the partitioner fields are read only if distributed != 0 */
+int  mgb_transfer_create_from_arrays(const mgb_transfer_map_view *arrays, const mgb_operator *op_fine, const mgb_operator *op_coarse,
+                                     mgb_transfer **out);
 void mgb_transfer_destroy(mgb_transfer *t);
 int  mgb_transfer_prolongate_and_add(const mgb_transfer *t, mgb_vector *dst_fine, const mgb_vector *src_coarse);
 int  mgb_transfer_restrict_and_add(const mgb_transfer *t, mgb_vector *dst_coarse, const mgb_vector *src_fine);
@@ -300,6 +304,9 @@ int  mgb_transfer_prolongate(const mgb_transfer *t, mgb_vector *dst_fine, const 
  * internal ghosted level vector. */
 typedef struct mgb_level_copy mgb_level_copy;
 int  mgb_level_copy_create(const mgb_copy_indices *ci, const mgb_operator *level_op, mgb_level_copy **out);
+/* the same from plain (active-vector local index, level-vector local index) pairs held by this rank, both DoFs local */
+int  mgb_level_copy_create_from_arrays(uint32_t n, const uint32_t *active_idx, const uint32_t *level_idx, const mgb_operator *level_op,
+                                       mgb_level_copy **out);
 void mgb_level_copy_destroy(mgb_level_copy *c);
 /* dst_level = 0 except the entries of the active DoFs that live on this level (src_active: double, active-mesh layout) */
 int  mgb_level_copy_to_mg(const mgb_level_copy *c, mgb_vector *dst_level, const mgb_vector *src_active);
