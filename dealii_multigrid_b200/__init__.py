@@ -10,9 +10,9 @@ _lib.load()
 
 from .api import (  # noqa: E402
     DOUBLE, FLOAT, FLAG_BIT, INDEX_MASK, MgbError, Mesh, DoFMap, TransferMap, LevelEdges, CopyIndices, Vector, Operator,
-    PreconditionChebyshev, MGTwoLevelTransfer, LevelCopy, Multigrid, cg_solve, Problem, init, set_stream, synchronize, launch_count, profile_start, profile_stop,
+    PreconditionChebyshev, MGTwoLevelTransfer, LevelCopy, Multigrid, cg_solve, dot_no_alloc, NO_ALLOC_MAX_N, Problem, init, set_stream, synchronize, launch_count, profile_start, profile_stop,
     comm_unique_id, comm_init, comm_finalize, comm_enable_peer_exchange, partition_sequence, first_child_boundaries, hierarchy_statistics, fe_1d, fe_1d_fdm, fe_p_embedding)
 
 __all__ = ["DOUBLE", "FLOAT", "FLAG_BIT", "INDEX_MASK", "MgbError", "Mesh", "DoFMap", "TransferMap", "LevelEdges", "CopyIndices", "Vector", "Operator",
-           "PreconditionChebyshev", "MGTwoLevelTransfer", "LevelCopy", "Multigrid", "cg_solve", "Problem", "init", "set_stream", "synchronize", "launch_count", "profile_start", "profile_stop",
+           "PreconditionChebyshev", "MGTwoLevelTransfer", "LevelCopy", "Multigrid", "cg_solve", "dot_no_alloc", "NO_ALLOC_MAX_N", "Problem", "init", "set_stream", "synchronize", "launch_count", "profile_start", "profile_stop",
            "comm_unique_id", "comm_init", "comm_finalize", "comm_enable_peer_exchange", "partition_sequence", "first_child_boundaries", "hierarchy_statistics", "fe_1d", "fe_1d_fdm", "fe_p_embedding"]

@@ -183,6 +183,7 @@ SIGNATURES = {
     "mgb_multigrid_enable_timers": (C.c_int, [P, C.c_int]),
     "mgb_multigrid_collect_times": (C.c_int, [P, C.POINTER(C.c_double)]),
     "mgb_cg_solve": (C.c_int, [P, P, P, P, C.c_uint, C.c_double, C.c_double, C.POINTER(C.c_uint), C.POINTER(C.c_double)]),
+    "mgb_vector_dot_no_alloc": (C.c_int, [P, P, C.c_uint64, P, P]),
     "mgb_operator_fused_available": (C.c_int, [P]),
     "mgb_operator_vmult_fused": (C.c_int, [P, P, P, C.c_int, P, P, P, C.c_double, C.c_double]),
     "mgb_operator_vmult_interface_down": (C.c_int, [P, P, P]),

@@ -638,6 +638,16 @@ class MGTwoLevelTransfer:
         self._h = None
 
 
+NO_ALLOC_MAX_N = 16777216  # MGB_NO_ALLOC_MAX_N of include/mgb200.h
+
+
+def dot_no_alloc(x_ptr, y_ptr, n, result_ptr, stream_ptr=None):
+    """mgb_vector_dot_no_alloc: *result_ptr = x . y for FP64 device arrays given as raw device addresses; asynchronous on the
+    stream (None: the library's stream); allocates nothing -- the reduction's scratch is a static __device__ array"""
+    _check(_lib.load().mgb_vector_dot_no_alloc(C.c_void_p(x_ptr), C.c_void_p(y_ptr), n, C.c_void_p(result_ptr),
+                                               C.c_void_p(stream_ptr) if stream_ptr else None))
+
+
 class LevelCopy:
     """device copy of copy_indices[level]: MGLevelGlobalTransfer::copy_to_mg / copy_from_mg for one level"""
 

@@ -222,6 +222,19 @@ int  mgb_vector_add_and_dot(mgb_vector *g, double a, const mgb_vector *h, double
 int  mgb_vector_update_ghost_values(const mgb_vector *v);
 int  mgb_vector_compress_add(mgb_vector *v);
 int  mgb_vector_zero_out_ghost_values(mgb_vector *v);
+/* Dot product that allocates nothing (no counterpart in the reference: added for
+ * callers that cannot call cudaMalloc -- CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * mgb_vector_dot up to the summation order (1e-13 relative), for FP64 device arrays of the CALLER: *result_dev = x . y.
+ * The scratch of the reduction (one partial sum per 4096-element block + a ticket) lives in a static __device__ array of
+ * MGB_NO_ALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; its device address is looked up once per
+ * device with cudaGetSymbolAddress.  n > MGB_NO_ALLOC_MAX_N is rejected (MGB error, mgb_last_error says why).
+ * cuda_stream: the cudaStream_t to enqueue on, NULL = the stream of mgb_set_stream.  The call is asynchronous (no host
+ * synchronisation, no cudaMalloc / cudaFree / allocating library call).  All calls share the scratch array, which keeps the
+ * last call's contents (the ticket is cleared on the stream before each launch): calls that overlap on the GPU -- other
+ * streams, other host threads on the same device -- race on it and must be serialised by the caller. */
+#define MGB_NO_ALLOC_MAX_N         16777216ull /* 4096 partial sums x 4096 elements per block */
+#define MGB_NO_ALLOC_SCRATCH_BYTES 33024       /* (4096 + 32) doubles */
+int  mgb_vector_dot_no_alloc(const double *x_dev, const double *y_dev, uint64_t n, double *result_dev, void *cuda_stream);
 
 /* ---- operator (include/operator.h) ---------------------------------------------------------------- */
 typedef struct
