@@ -16,6 +16,8 @@ Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]` pri
     timed on the host cores on a bounded sample (deal.II itself cannot be built here: SURVEY.md 8(c)).
 Workload: BASELINE.json configs[1] -- 3-D hypercube Poisson, global coarsening, p=4, FP64 V-cycle, coarse CG.
 N>1: one rank per GPU (torchrun), z-order partition of the same mesh (strong scaling), NCCL ghost exchange.
+`--scaling weak` (N = 1 or 8 only: a refinement level multiplies the cell count by 8) keeps the DoFs per GPU fixed instead:
+N = 8 then solves hypercube L = nref+1 (L=8: 1 076 890 625 DoFs, BASELINE.json configs[4]'s "~1B DoFs across 8 B200").
 """
 import argparse
 import json
@@ -320,11 +322,12 @@ def run_ours(args):
         parity = parity_check(mg, M, b_cpu, cpu_nref, args.degree, args.number)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f64" if args.number == "double" else "f64 outer CG / f32 V-cycle", "data": "synthetic",
         "config": {"workload": workload_name(args.nref, args.degree, args.number), "partition": f"z-order, {world} rank(s)",
                    "l2": "inputs larger than L2 (each fine-level vector %.0f MB, >10 vectors touched per iteration)" % (n_owned * 8 / 1e6),
-                   "n_iterations_per_solve": its / args.steps, "setup_s": round(t_setup, 2)},
+                   "n_iterations_per_solve": its / args.steps, "setup_s": round(t_setup, 2), "n_dofs": int(n_dofs),
+                   "n_dofs_per_gpu": int(n_dofs // world)},
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 8 * n_owned, "d2h_bytes_per_step": 8 * n_owned,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
@@ -344,6 +347,16 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def apply_scaling(args):
+    """--scaling weak: one more global refinement per factor 8 in the rank count (fixed DoFs per GPU)"""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.scaling == "weak":
+        extra = {1: 0, 8: 1, 64: 2}.get(world)
+        if extra is None:
+            raise SystemExit("bench.py --scaling weak: the hypercube hierarchy only offers weak-scaling points at 1, 8, 64 ranks")
+        args.nref += extra
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -356,7 +369,10 @@ def main():
     ap.add_argument("--cpu-nref", type=int, default=None,
                     help="NRefGlobal of the CPU runs (default: 6 = 257^3 DoFs for the cpu_baseline sample of the GPU arm, --nref for --impl reference)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong: the same mesh over N ranks (default, what the driver's 1/2/4/8 runs use); weak: nref+1 at 8 ranks")
     args = ap.parse_args()
+    apply_scaling(args)
     if args.impl == "reference":
         run_reference(args)
     else:

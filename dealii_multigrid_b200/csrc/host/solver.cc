@@ -875,7 +875,18 @@ namespace mgb
     const Partitioner &p = op_.partitioner()->host;
     // the level lives entirely on this rank (or this rank owns nothing of it) and is small
     const bool local = p.n_ghost == 0 && p.import_indices.empty() && (p.n_owned == 0 || (long long)p.n_owned == op_.m());
-    if (!local || op_.m() > max_dense_size)
+    bool       use_dense = local && op_.m() <= max_dense_size;
+    if (c.comm && c.comm->size() > 1)
+      {
+        // The decision must be the same on every rank: a rank that owns nothing of the level would otherwise go "dense" and
+        // skip the generic CG whose dot products are collective, while the ranks that share the level wait in them.
+        int              mine = use_dense ? 1 : 0;
+        std::vector<int> all(size_t(c.comm->size()), 0);
+        c.comm->allgather_host(&mine, all.data(), sizeof(int), c.stream);
+        for (const int v : all)
+          use_dense = use_dense && v != 0;
+      }
+    if (!use_dense)
       return;
     dense_ = true;
     dense_its_.alloc(1);

@@ -85,7 +85,12 @@ namespace mgb
     {
       alloc(n_);
       if (n)
-        MGB_CUDA(cudaMemcpy(ptr, h, n * sizeof(T), cudaMemcpyHostToDevice));
+        {
+          // on the library's stream and complete on return: the kernels run on a (possibly non-blocking) user stream that a
+          // copy on the legacy default stream would not be ordered against
+          MGB_CUDA(cudaMemcpyAsync(ptr, h, n * sizeof(T), cudaMemcpyHostToDevice, ctx().stream));
+          MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+        }
     }
   };
 
