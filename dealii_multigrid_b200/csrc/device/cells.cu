@@ -123,6 +123,7 @@ namespace mgb
       }
     DISPATCH_DEGREE(cd.degree, (launch_apply<P, T>(cd, src, dst, cell_list, n_list, s)));
   }
+  bool chunk_atomic_output() { return MGB_CHUNK_ABLATE == 3; }
   template <typename T>
   void cell_laplace_chunked(const CellData &cd, const ChunkDevice &ch, const T *x, T *out, const FusedEpilogue<T> &ep, cudaStream_t s)
   {

@@ -19,6 +19,16 @@ namespace mgb
 {
   constexpr int CHUNK_MAX_DEPS = 96;
 
+  // MGB_CHUNK_ABLATE (experiments with tools/build_variants.sh; 0 = the shipped kernel):
+  //   1: load phase only            (timing only, results wrong by construction)
+  //   2: load + cell arithmetic     (timing only, results wrong by construction)
+  //   3: FUNCTIONAL variant without the hand-off between chunks: after the merge rounds every slot's sum is added to the
+  //      output with atomics (owned range coalesced); no flags, no side buffer, no waiting.  dst must be zero on entry
+  //      (chunk_atomic_output() tells the host), the fused epilogues are not available.
+#ifndef MGB_CHUNK_ABLATE
+#define MGB_CHUNK_ABLATE 0
+#endif
+
   // cell storage layout of the chunk kernel: SlabLayout, except that 5x5 planes of doubles are packed tighter (plane
   // stride 27, cell stride 135: the slab pattern stays conflict free, the column pattern gets a two-way conflict where a
   // half-warp crosses a cell boundary) so that three blocks fit on an SM
@@ -249,7 +259,7 @@ namespace mgb
 
         // ------------------------------------------------------------------ cells
 #pragma unroll 1
-        for (int batch = 0; batch < NB; ++batch)
+        for (int batch = 0; batch < (MGB_CHUNK_ABLATE == 1 ? 0 : NB); ++batch)
           {
             const int       first = (warp * NB + batch) * CW;
             const int       ncw   = max(0, min(CW, int(n_cells) - first));
@@ -383,9 +393,25 @@ namespace mgb
                     u[col_sm(r) + k * PS] = h * res[k];
                 }
           }
-        if (!STAGE && tid == 0)
+        if ((!STAGE || MGB_CHUNK_ABLATE == 1) && tid == 0)
           next_chunk = int(a.n_chunks) - 1 - int(atomicAdd(a.state, 1u));
         __syncthreads();
+        if (MGB_CHUNK_ABLATE == 1 || MGB_CHUNK_ABLATE == 2)
+          {
+            // timing ablation: nothing after the load (1) / the arithmetic (2); keep the arithmetic alive with a store that
+            // never happens
+            if (MGB_CHUNK_ABLATE == 2 && u_all[tid] == T(-1.2345e300))
+              a.out[ob] = u_all[tid];
+            if (staged)
+              {
+                mbar_wait(mbar + 1, parity1);
+                parity1 ^= 1u;
+              }
+            if (tid == 0)
+              *s_chunk = next_chunk;
+            prev_chunk = -1;
+            continue;
+          }
         if (staged)
           {
             mbar_wait(mbar + 1, parity1);
@@ -412,6 +438,29 @@ namespace mgb
           const uint32_t pos = slotpos[s];
           return pos != 0xffffu ? u_all[pos] : T(0);
         };
+        if (MGB_CHUNK_ABLATE == 3)
+          {
+            // every slot's sum goes to the (zeroed) output with an atomic add: owned range coalesced, foreign ones scattered
+            for (uint32_t s = tid; s < n_own; s += THREADS)
+              {
+                const uint32_t pos = slotpos[s];
+                if (pos != 0xffffu)
+                  atomic_add(a.out + ob + s, u_all[pos]);
+              }
+            const uint32_t *fsrc = cb + __ldg(cb + CB_OFF_FSRC);
+            for (uint32_t t = tid; t < n_fp + n_fl; t += THREADS)
+              {
+                const uint32_t w = __ldg(fsrc + t);
+                atomic_add(a.out + s_dep[w >> 16] + (w & 0xffffu), slot_value(n_own + t));
+              }
+            const uint32_t *gi = a.ghost_idx + __ldg(d + CD_GHOST_OFF);
+            for (uint32_t t = tid; t < n_fg; t += THREADS)
+              atomic_add(a.out + __ldg(gi + t), slot_value(n_own + n_fp + n_fl + t));
+            if (tid == 0)
+              *s_chunk = next_chunk;
+            prev_chunk = -1;
+            continue;
+          }
         // ------------------------------------------------------------------ hand-off of the foreign sums
         for (uint32_t t = tid; t < n_fp; t += THREADS)
           __stcg(a.side + size_t(side_off) + t, slot_value(n_own + t));

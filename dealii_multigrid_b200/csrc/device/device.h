@@ -77,7 +77,8 @@ namespace mgb
     unsigned           *ticket     = nullptr; // [2]: last-block detection of the send and the recv kernel
   };
   template <typename T>
-  void halo_exchange(const HaloDir &hd, bool ghost_direction, T *vec, uint32_t n_owned, const uint32_t *import_indices, cudaStream_t s);
+  void halo_exchange(const HaloDir &hd, bool ghost_direction, T *vec, uint32_t n_owned, const uint32_t *import_indices, cudaStream_t s,
+                     bool fused = false); // fused: one kernel (needs the GPU to itself: the grid must be co-resident)
 
   // ---------------------------------------------------------------- cell kernels (operator.cu)
   struct CellData
@@ -117,6 +118,9 @@ namespace mgb
     const T *b = nullptr, *dinv = nullptr, *xold = nullptr;
     T        f1 = T(0), f2 = T(0);
   };
+  // true in the experimental build whose chunk kernel adds its sums atomically (-DMGB_CHUNK_ABLATE=3): dst must be zeroed, no
+  // fused epilogues
+  bool chunk_atomic_output();
   template <typename T>
   void cell_laplace_chunked(const CellData &cd, const ChunkDevice &ch, const T *x, T *out, const FusedEpilogue<T> &ep, cudaStream_t s);
   // out[idx[i]] += coef(idx[i]) * x[idx[i]]: the identity rows of the constrained DoFs after a fused cell loop (coef as the

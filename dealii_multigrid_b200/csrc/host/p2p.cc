@@ -77,9 +77,11 @@ namespace mgb
       }
     const char *env = std::getenv("MGB_P2P");
     const int   R = c.comm->size(), me = c.comm->rank();
-    // opt-in (MGB_P2P=1): measured on 2 and 8 B200 the two-kernel peer exchange (15.5 us per exchange, bounded by the
-    // system-scope fence + flag round trip over NVLink) is not yet faster than pack + grouped ncclSend/ncclRecv (13.7 us)
-    const bool  enabled = (env && env[0] == '1') && R <= HALO_MAX_PEERS;
+    // On by default (MGB_P2P=0 keeps pack + grouped ncclSend/ncclRecv): the fused single-kernel exchange of device/halo.cu
+    // costs 29-33 us per update_ghost_values + compress pair on 8 B200 against 46-67 us for NCCL, 19.6 against 21.7 ms per
+    // solve at L=7 (profiles/r2n_*); the send/recv kernel pair of round 1 (15.5 us per exchange) was not faster than NCCL.
+    // Without peer access between the GPUs the NCCL path stays in use.
+    const bool  enabled = !(env && env[0] == '0') && R <= HALO_MAX_PEERS;
     // every rank must back the same number of partitioners (they are created in the same order everywhere)
     std::vector<long long> counts(R);
     const long long        mine = enabled ? (long long)reg.size() : -1;

@@ -105,6 +105,14 @@ namespace mgb
   // ------------------------------------------------------------------------------------------ vector
   namespace
   {
+    bool p2p_fused()
+    {
+      static const bool on = [] {
+        const char *e = std::getenv("MGB_P2P_FUSED");
+        return !(e && e[0] == '0');
+      }();
+      return on;
+    }
     double finish_reduction()
     {
       Context &c = ctx();
@@ -155,8 +163,11 @@ namespace mgb
       throw std::runtime_error("update_ghost_values: vector has ghosts but no communicator is set");
     if (part->p2p)
       {
-        halo_exchange<T>(part->p2p->ghost, true, data, n_owned, part->import_indices.ptr, stream);
-        c.launches += 2;
+        // one fused kernel on the library's own stream; the send/recv pair when the exchange runs beside cell kernels on
+        // the second stream (MGB_OVERLAP) or with MGB_P2P_FUSED=0
+        const bool fused = on == nullptr && p2p_fused();
+        halo_exchange<T>(part->p2p->ghost, true, data, n_owned, part->import_indices.ptr, stream, fused);
+        c.launches += fused ? 1 : 2;
         return;
       }
     const Partitioner &p   = part->host;
@@ -186,8 +197,9 @@ namespace mgb
     if (part->p2p)
       {
         // the send kernel zeroes the ghost tail after reading it (compress ends with zero_out_ghost_values)
-        halo_exchange<T>(part->p2p->compress, false, data, n_owned, part->import_indices.ptr, stream);
-        c.launches += 2;
+        const bool fused = on == nullptr && p2p_fused();
+        halo_exchange<T>(part->p2p->compress, false, data, n_owned, part->import_indices.ptr, stream, fused);
+        c.launches += fused ? 1 : 2;
         return;
       }
     const Partitioner &p   = part->host;
@@ -413,7 +425,9 @@ namespace mgb
         // chunked cell loop: every owned entry of dst is written once (no zeroing, no atomics); only the contributions to
         // ghost entries are added atomically to the (zeroed) ghost tail
         src.update_ghost_values();
-        if (dst.n_ghost)
+        if (chunk_atomic_output())
+          dst.zero();
+        else if (dst.n_ghost)
           dst.zero_out_ghost_values();
         c.prof_begin(cd_.n_cells);
         cell_laplace_chunked<T>(cd, chd_, src.data, dst.data, FusedEpilogue<T>(), c.stream), ++c.launches;
@@ -455,7 +469,7 @@ namespace mgb
 
   template <typename T> bool OperatorT<T>::fused_available(const DVec<T> &out, const DVec<T> &x) const
   {
-    return chunk_path_ok(out.data, x.data) && edge_.n == 0 && part_->trivial();
+    return chunk_path_ok(out.data, x.data) && edge_.n == 0 && part_->trivial() && !chunk_atomic_output();
   }
 
   template <typename T> void OperatorT<T>::vmult_fused(DVec<T> &out, const DVec<T> &x, const FusedEpilogue<T> &ep) const
