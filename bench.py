@@ -299,10 +299,24 @@ def run_ours(args):
     ev1.record()
     barrier()
     ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
+    # ---- timed region 3: the same K host-buffer solves through the batch entry point (mgb_problem_solve_host_batch): every
+    # step still uploads its right-hand side from pinned memory and downloads its solution inside the timed region, but the
+    # copies of neighbouring steps run on copy streams behind the solves
+    prob.solve_host_batch([rhs_host.data_ptr()] * 2, [sol_host.data_ptr()] * 2)   # creates the staging buffers (untimed)
+    barrier()
+    t_wall = time.perf_counter()
+    ev0.record()
+    rb = prob.solve_host_batch([rhs_host.data_ptr()] * args.steps, [sol_host.data_ptr()] * args.steps)
+    ev1.record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    its_batch = sum(r["n_iterations"] for r in rb)
+    ms_batch = max_over_ranks(max(ev0.elapsed_time(ev1), t_wall * 1e3))   # copies run on other streams: the host clock bounds it too
     clocks = sampler.stop() if sampler else None
 
     value = n_dofs * its / (ms * 1e-3)
-    e2e = n_dofs * its_e2e / (ms_e2e * 1e-3)
+    e2e_single = n_dofs * its_e2e / (ms_e2e * 1e-3)
+    e2e = n_dofs * its_batch / (ms_batch * 1e-3)
     peak, peak_src = measured_peaks()
     k_avg_s = (k_ms / max(k_launches, 1)) * 1e-3
     k_avg_s = max_over_ranks(k_avg_s)
@@ -336,7 +350,11 @@ def run_ours(args):
                    "n_iterations_per_solve": its / args.steps, "setup_s": round(t_setup, 2), "n_dofs": int(n_dofs),
                    "n_dofs_per_gpu": int(n_dofs // world)},
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 8 * n_owned, "d2h_bytes_per_step": 8 * n_owned,
-                "ms_per_step": ms_e2e / args.steps},
+                "ms_per_step": ms_batch / args.steps,
+                "api": "mgb_problem_solve_host_batch: K host-buffer solves in one call, upload of step i+1 and download of step i-1 "
+                       "behind solve i (max of the CUDA-event and the host clock around the call)",
+                "one_call_per_step": {"value": e2e_single, "ms_per_step": ms_e2e / args.steps,
+                                      "api": "mgb_problem_solve_host: H2D, solve, D2H strictly in sequence"}},
         "gpu_launches": launches,
         "roofline": {"kernel": f"k_laplace_apply<{args.degree},{args.number}> (finest level" + ("" if args.number == "double" else "; the outer CG's double-precision launches on the same mesh are timed with it, bytes counted for the float ones") + ")", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.nref, args.degree, args.number, world),

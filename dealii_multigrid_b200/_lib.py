@@ -216,6 +216,7 @@ SIGNATURES = {
     "mgb_problem_vcycle": (C.c_int, [P, P, P]),
     "mgb_problem_solve_once": (C.c_int, [P, C.c_int, C.POINTER(Result)]),
     "mgb_problem_solve_host": (C.c_int, [P, C.c_void_p, C.c_void_p, C.POINTER(Result)]),
+    "mgb_problem_solve_host_batch": (C.c_int, [P, C.c_int, PP, PP, P]),
     "mgb_problem_run": (C.c_int, [P, C.c_int, C.POINTER(Result)]),
 }
 

@@ -789,6 +789,18 @@ class Problem:
         _check(self._lib.mgb_problem_solve_host(self._h, C.c_void_p(rhs_host_ptr), C.c_void_p(solution_host_ptr), C.byref(r)))
         return r.as_dict()
 
+    def solve_host_batch(self, rhs_host_ptrs, solution_host_ptrs):
+        """len(rhs_host_ptrs) solves in a row with HOST buffers (raw addresses, pinned): the upload of the next right-hand
+        side and the download of the previous solution run behind the current solve; returns the list of result dicts"""
+        n = len(rhs_host_ptrs)
+        if n != len(solution_host_ptrs):
+            raise ValueError("one solution buffer per right-hand side")
+        rp = (C.c_void_p * n)(*[C.c_void_p(a) for a in rhs_host_ptrs])
+        sp = (C.c_void_p * n)(*[C.c_void_p(a) for a in solution_host_ptrs])
+        res = (_lib.Result * n)()
+        _check(self._lib.mgb_problem_solve_host_batch(self._h, n, rp, sp, res))
+        return [r.as_dict() for r in res]
+
     def run(self, n_repetitions=5):
         r = _lib.Result()
         _check(self._lib.mgb_problem_run(self._h, n_repetitions, C.byref(r)))

@@ -31,6 +31,23 @@ struct mgb_problem
   std::unique_ptr<mgb_operator>                        fine_op;
   std::unique_ptr<mgb_dofmap>                          fine_dofmap;
   std::unique_ptr<mgb_vector>                          rhs, solution;
+  // mgb_problem_solve_host_batch: staging buffers, copy streams and events (created on first use)
+  double      *stage_rhs = nullptr, *stage_sol = nullptr;
+  cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+  cudaEvent_t  ev_h2d = nullptr, ev_rhs_free = nullptr, ev_sol_ready = nullptr, ev_d2h_done = nullptr;
+  ~mgb_problem()
+  {
+    if (stage_rhs)
+      cudaFree(stage_rhs);
+    if (stage_sol)
+      cudaFree(stage_sol);
+    for (cudaStream_t st : {h2d_stream, d2h_stream})
+      if (st)
+        cudaStreamDestroy(st);
+    for (cudaEvent_t ev : {ev_h2d, ev_rhs_free, ev_sol_ready, ev_d2h_done})
+      if (ev)
+        cudaEventDestroy(ev);
+  }
 };
 
 namespace
@@ -1141,6 +1158,56 @@ int mgb_problem_solve_host(mgb_problem *p, const double *rhs_host, double *solut
     fill_result(p->p->solve_once(false), result);
     MGB_CUDA(cudaMemcpyAsync(solution_host, x.data, size_t(x.n_owned) * sizeof(double), cudaMemcpyDeviceToHost, ctx().stream));
     MGB_CUDA(cudaStreamSynchronize(ctx().stream));
+  });
+}
+int mgb_problem_solve_host_batch(mgb_problem *p, int n, const double *const *rhs_hosts, double *const *solution_hosts, mgb_result *results)
+{
+  return guarded([&] {
+    if (n <= 0)
+      return;
+    if (!rhs_hosts || !solution_hosts)
+      throw std::runtime_error("mgb_problem_solve_host_batch: null pointer arrays");
+    DVec<double> &b     = p->p->rhs();
+    DVec<double> &x     = p->p->solution();
+    const size_t  bytes = size_t(b.n_owned) * sizeof(double);
+    cudaStream_t  main  = ctx().stream;
+    if (!p->h2d_stream)
+      {
+        MGB_CUDA(cudaMalloc((void **)&p->stage_rhs, std::max<size_t>(bytes, 8)));
+        MGB_CUDA(cudaMalloc((void **)&p->stage_sol, std::max<size_t>(bytes, 8)));
+        MGB_CUDA(cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking));
+        MGB_CUDA(cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking));
+        for (cudaEvent_t *ev : {&p->ev_h2d, &p->ev_rhs_free, &p->ev_sol_ready, &p->ev_d2h_done})
+          MGB_CUDA(cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+      }
+    // upload of right-hand side i+1 and download of solution i-1 run on their own streams (both PCIe directions at once)
+    // behind solve i; the staging buffers decouple them from the vectors the solver works on
+    MGB_CUDA(cudaMemcpyAsync(p->stage_rhs, rhs_hosts[0], bytes, cudaMemcpyHostToDevice, p->h2d_stream));
+    MGB_CUDA(cudaEventRecord(p->ev_h2d, p->h2d_stream));
+    for (int i = 0; i < n; ++i)
+      {
+        MGB_CUDA(cudaStreamWaitEvent(main, p->ev_h2d, 0));
+        MGB_CUDA(cudaMemcpyAsync(b.data, p->stage_rhs, bytes, cudaMemcpyDeviceToDevice, main));
+        MGB_CUDA(cudaEventRecord(p->ev_rhs_free, main));
+        if (i + 1 < n)
+          {
+            MGB_CUDA(cudaStreamWaitEvent(p->h2d_stream, p->ev_rhs_free, 0));
+            MGB_CUDA(cudaMemcpyAsync(p->stage_rhs, rhs_hosts[i + 1], bytes, cudaMemcpyHostToDevice, p->h2d_stream));
+            MGB_CUDA(cudaEventRecord(p->ev_h2d, p->h2d_stream));
+          }
+        const Result r = p->p->solve_once(false);
+        if (results)
+          fill_result(r, results + i);
+        if (i > 0)
+          MGB_CUDA(cudaStreamWaitEvent(main, p->ev_d2h_done, 0)); // the staging buffer of the previous solution is free again
+        MGB_CUDA(cudaMemcpyAsync(p->stage_sol, x.data, bytes, cudaMemcpyDeviceToDevice, main));
+        MGB_CUDA(cudaEventRecord(p->ev_sol_ready, main));
+        MGB_CUDA(cudaStreamWaitEvent(p->d2h_stream, p->ev_sol_ready, 0));
+        MGB_CUDA(cudaMemcpyAsync(solution_hosts[i], p->stage_sol, bytes, cudaMemcpyDeviceToHost, p->d2h_stream));
+        MGB_CUDA(cudaEventRecord(p->ev_d2h_done, p->d2h_stream));
+      }
+    MGB_CUDA(cudaStreamSynchronize(p->d2h_stream));
+    MGB_CUDA(cudaStreamSynchronize(main));
   });
 }
 int mgb_problem_run(mgb_problem *p, int n_repetitions, mgb_result *result)

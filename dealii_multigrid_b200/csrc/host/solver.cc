@@ -113,12 +113,23 @@ namespace mgb
       }();
       return on;
     }
+    // Where a reduction kernel writes its scalar.  One rank: straight into the pinned host word (cudaMallocHost memory is
+    // device-accessible under unified addressing), so reading it back needs no copy -- a cudaMemcpyAsync of 8 bytes would
+    // queue on the device-to-host copy engine behind whatever bulk download is in flight (mgb_problem_solve_host_batch).
+    // Several ranks: device memory, because ncclAllReduce works on it.
+    double *reduction_target()
+    {
+      Context &c = ctx();
+      return (c.comm && c.comm->size() > 1) ? c.red_result : c.host_result;
+    }
     double finish_reduction()
     {
       Context &c = ctx();
       if (c.comm && c.comm->size() > 1)
-        c.comm->allreduce_sum(c.red_result, 1, c.stream);
-      MGB_CUDA(cudaMemcpyAsync(c.host_result, c.red_result, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+        {
+          c.comm->allreduce_sum(c.red_result, 1, c.stream);
+          MGB_CUDA(cudaMemcpyAsync(c.host_result, c.red_result, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+        }
       MGB_CUDA(cudaStreamSynchronize(c.stream));
       return c.host_result[0];
     }
@@ -127,28 +138,28 @@ namespace mgb
   template <typename T> double DVec<T>::dot(const DVec &y) const
   {
     Context &c = ctx();
-    vec_dot<T>(data, y.data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    vec_dot<T>(data, y.data, n_owned, reduction_target(), c.red_scratch, c.red_ticket, c.stream);
     ++c.launches;
     return finish_reduction();
   }
   template <typename T> double DVec<T>::add_and_dot(T a, const DVec &h)
   {
     Context &c = ctx();
-    vec_add_and_dot<T>(data, a, h.data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    vec_add_and_dot<T>(data, a, h.data, n_owned, reduction_target(), c.red_scratch, c.red_ticket, c.stream);
     ++c.launches;
     return finish_reduction();
   }
   template <typename T> double DVec<T>::cg_update(DVec &x, T a, const DVec &d, const DVec &h)
   {
     Context &c = ctx();
-    vec_cg_update<T>(x.data, data, a, d.data, h.data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    vec_cg_update<T>(x.data, data, a, d.data, h.data, n_owned, reduction_target(), c.red_scratch, c.red_ticket, c.stream);
     ++c.launches;
     return finish_reduction();
   }
   template <typename T> double DVec<T>::mean_value(long long n_global) const
   {
     Context &c = ctx();
-    vec_sum<T>(data, n_owned, c.red_result, c.red_scratch, c.red_ticket, c.stream);
+    vec_sum<T>(data, n_owned, reduction_target(), c.red_scratch, c.red_ticket, c.stream);
     ++c.launches;
     return finish_reduction() / double(n_global);
   }

@@ -402,6 +402,10 @@ int  mgb_problem_solve_once(mgb_problem *p, int with_stage_timers, mgb_result *r
 /* the same solve with HOST buffers: rhs_host (n_owned doubles) is copied to the device, solved from a zero
  * initial guess, and the solution copied back into solution_host (n_owned doubles) */
 int  mgb_problem_solve_host(mgb_problem *p, const double *rhs_host, double *solution_host, mgb_result *result);
+/* n solves in a row with host buffers (n_owned doubles each; use pinned memory): the upload of right-hand side i+1 and the
+ * download of solution i-1 run on copy streams of their own behind solve i, so that only the first upload and the last
+ * download are exposed.  results: n entries or NULL.  Returns when every solution_hosts[i] is filled. */
+int  mgb_problem_solve_host_batch(mgb_problem *p, int n, const double *const *rhs_hosts, double *const *solution_hosts, mgb_result *results);
 /* the reference's protocol: 1 warm-up + n_repetitions timed solves, best one reported (:1140-1283) */
 int  mgb_problem_run(mgb_problem *p, int n_repetitions, mgb_result *result);
 /* statistics of the problem's partitioned hierarchy; per_level sized mgb_problem_n_meshes()*MGB_STATISTICS_LEVEL_VALUES or NULL */
