@@ -306,10 +306,14 @@ namespace mgb
         }
       ctab_.upload(rec.data(), rec.size());
     }
-    if (any_hanging && std::getenv("MGB_SPLIT_HANGING") && std::string(std::getenv("MGB_SPLIT_HANGING")) == "1")
+    // Cells with hanging-node constraints in a launch of their own: a warp of the cell kernel takes the shared-memory detour
+    // as soon as ONE of its cells has a constrained face or edge, so mixing them in slows the unconstrained majority down
+    // (quadrant L=7 p=4: 66.7 -> 78.8 GDoF/s, profiles/r2a_split_hanging.txt).  On by default for levels large enough that a
+    // second launch does not matter; MGB_SPLIT_HANGING=0 / 1 forces it off / on.
+    const char *split_env = std::getenv("MGB_SPLIT_HANGING");
+    const bool  split     = split_env ? split_env[0] == '1' : s.n_cells >= 8192;
+    if (any_hanging && split)
       {
-        // experiment: two launches per cell loop, the cells without hanging-node constraints on the kernel's fast path
-        // (a warp takes the shared-memory detour as soon as ONE of its cells has a constrained face or edge)
         std::vector<uint32_t> plain, hanging;
         for (long long c = 0; c < s.n_cells; ++c)
           ((s.mask[c] >> 3) ? hanging : plain).push_back(uint32_t(c));

@@ -507,3 +507,21 @@ def test_float_vcycle_and_solve_against_the_float_oracle(gpu, geometry, L, p, mg
     x, its, _ = H.solve(prob.rhs().to_numpy())
     assert res["n_iterations"] == its
     assert rel_l2(prob.solution().to_numpy(), x) < 1e-3
+
+
+@pytest.mark.parametrize("geometry,L,p,mg_type", [("hypercube", 3, 2, "HMG-global"), ("quadrant", 4, 2, "HMG-global"), ("quadrant", 3, 2, "HMG-local")])
+def test_iteration_count_at_a_borderline_tolerance(gpu, geometry, L, p, mg_type):
+    """north_star: CG iteration counts identical.  The relative tolerance is put a hair above and a hair below the residual
+    reduction the oracle reaches after k iterations (ReductionControl, multigrid_throughput.cc:1625-1635): the count must flip
+    from k to k+1 in the GPU solve exactly as in the oracle, although the atomic scatter orders its additions differently."""
+    from util import make_oracle
+    mg = gpu
+    H = make_oracle(geometry, L, p, mg_type, 3, "cg")
+    b = ref.assemble_rhs_constant(H.fine_maps)
+    _, k, ctl = H.solve(b, reltol=1e-4)
+    rho = ctl.last_value / ctl.initial_value
+    for tol, want in ((rho * (1 + 1e-7), k), (rho * (1 - 1e-7), k + 1)):
+        _, its_oracle, _ = H.solve(b, reltol=tol)
+        assert its_oracle == want
+        res = mg.Problem(params(geometry, L, p, mg_type, "cg", reltol=tol)).solve_once()
+        assert res["n_iterations"] == want
