@@ -651,11 +651,21 @@ def dot_no_alloc(x_ptr, y_ptr, n, result_ptr, stream_ptr=None):
 class LevelCopy:
     """device copy of copy_indices[level]: MGLevelGlobalTransfer::copy_to_mg / copy_from_mg for one level"""
 
-    def __init__(self, copy_indices, level_op):
+    def __init__(self, copy_indices, level_op, active_idx=None, level_idx=None):
+        """copy_indices: a CopyIndices object, or None with the (active, level) local index pairs given as arrays (what a
+        deal.II adapter extracts from MGLevelGlobalTransfer::copy_indices)"""
         self._lib = _lib.load()
         self._owner = (copy_indices, level_op)
         h = C.c_void_p()
-        _check(self._lib.mgb_level_copy_create(copy_indices._h, level_op._h, C.byref(h)))
+        if copy_indices is not None:
+            _check(self._lib.mgb_level_copy_create(copy_indices._h, level_op._h, C.byref(h)))
+        else:
+            a = np.ascontiguousarray(active_idx, dtype=np.uint32)
+            l = np.ascontiguousarray(level_idx, dtype=np.uint32)
+            if a.shape != l.shape or a.ndim != 1:
+                raise ValueError("active_idx and level_idx must be 1-D arrays of equal length")
+            _check(self._lib.mgb_level_copy_create_from_arrays(len(a), a.ctypes.data_as(_lib.c_u32p), l.ctypes.data_as(_lib.c_u32p),
+                                                               level_op._h, C.byref(h)))
         self._h = h
 
     def copy_to_mg(self, dst_level, src_active):

@@ -97,6 +97,24 @@ namespace mgb
       {
         // ---- tables
         const int nch = HMODE ? n_children[c] : 1;
+#ifndef MGB_TRANSFER_NO_PREFETCH
+        {
+          // the warp's NEXT coarse cell: pull its record and fine tables into L2 now (no registers held, nothing waits), so
+          // that the serial chain table -> gather -> compute of the next iteration starts from L2 hits instead of DRAM
+          const long long cn = c + (long long)gridDim.x * TRANSFER_WARPS;
+          if (cn < n_coarse)
+            {
+              const size_t   fn      = size_t(fine_first[cn]) * 27;
+              const char    *ptrs[3] = {reinterpret_cast<const char *>(coarse_ctab + cn * 32), reinterpret_cast<const char *>(fine_own + fn),
+                                        reinterpret_cast<const char *>(weight_code + fn)};
+              constexpr int  lines0 = 1, lines1 = (Cfg::NCH * 27 * 4 + 127) / 128 + 1, lines2 = (Cfg::NCH * 27 + 127) / 128 + 1;
+              const int      which  = lane < lines0 ? 0 : (lane < lines0 + lines1 ? 1 : 2);
+              const int      idx    = lane - (which == 0 ? 0 : (which == 1 ? lines0 : lines0 + lines1));
+              if (lane < lines0 + lines1 + lines2)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(ptrs[which] + size_t(idx) * 128));
+            }
+        }
+#endif
         if (HMODE && nch == 0)
           continue; // local smoothing: parent without children on the fine level (warp-uniform)
         srec[lane]    = coarse_ctab[c * 32 + lane];

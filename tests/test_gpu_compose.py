@@ -102,3 +102,39 @@ def test_local_smoothing_composed_from_handles(gpu, geometry, L, p):
     its, _ = mg.cg_solve(active_op, vx, vb, M)
     xo, its_o, _ = H.solve(b)
     assert its == its_o and rel_l2(vx.to_numpy(), xo) < 1e-9
+
+
+def test_transfer_and_level_copy_created_from_plain_arrays(gpu):
+    """mgb_transfer_create_from_arrays / mgb_level_copy_create_from_arrays: what include/mgb200_dealii.h calls with the arrays it
+    extracts from deal.II (MGTwoLevelTransfer::reinit, MGLevelGlobalTransfer::copy_indices) must behave like the objects built from
+    the generator's handles"""
+    mg = gpu
+    H = OracleHierarchyLS("quadrant", 4, 2, "HMG-local", 3, "cg")
+    l = len(H.level_meshes) - 1
+    opf, opc = mg.Operator(H.level_dofmaps[l], edges=H.level_edges[l]), mg.Operator(H.level_dofmaps[l - 1], edges=H.level_edges[l - 1])
+    T_handles = mg.MGTwoLevelTransfer(H.level_dofmaps[l], H.level_dofmaps[l - 1], H.ls_tmaps[l], opf, opc)
+    T_arrays = mg.MGTwoLevelTransfer(None, None, H.ls_tmaps[l], opf, opc)          # the view's plain arrays only
+    uc, uf = seeded(H.level_maps[l - 1].n_dofs, 1), seeded(H.level_maps[l].n_dofs, 2)
+    for T in (T_handles, T_arrays):
+        vc, vf = _vec(opc, uc), _vec(opf, uf)
+        T.prolongate_and_add(vf, vc)
+        e = uf.copy()
+        H.ls_transfers[l].prolongate_and_add(e, uc)
+        assert rel_l2(vf.to_numpy(), e) < 1e-12
+        vc, vf = _vec(opc, uc), _vec(opf, uf)
+        T.restrict_and_add(vc, vf)
+        e = uc.copy()
+        H.ls_transfers[l].restrict_and_add(e, uf)
+        assert rel_l2(vc.to_numpy(), e) < 1e-12
+    active_op = mg.Operator(H.active_dofmaps[-1])
+    x = seeded(H.fine_maps.n_dofs, 3)
+    va = _vec(active_op, x)
+    c = mg.LevelCopy(None, opf, active_idx=H.copy[l].active_idx, level_idx=H.copy[l].level_idx)
+    vl = _vec(opf, seeded(H.level_maps[l].n_dofs, 4))
+    c.copy_to_mg(vl, va)
+    e = np.zeros(H.level_maps[l].n_dofs)
+    e[H.copy[l].level_idx] = x[H.copy[l].active_idx]
+    np.testing.assert_array_equal(vl.to_numpy(), e)
+    back = _vec(active_op)
+    c.copy_from_mg(back, vl)
+    np.testing.assert_array_equal(back.to_numpy()[H.copy[l].active_idx], x[H.copy[l].active_idx])
