@@ -169,7 +169,7 @@ def run_reference(args):
     r = cpu_solve_sample(n_ref, args.degree, steps, warmup)
     steps = r["steps_run"]
     sample = (f"{workload_name(n_ref, args.degree, 'double')}: best of {steps} solve(s) after {warmup} warm-up, threaded C restatement "
-              f"oracle/mgcpu.c ({r['build']}) on {r['cores']} of {r['hw_threads']} hardware threads, {r['cpu']}; setup {r['setup_s']:.0f} s; "
+              f"oracle/mgcpu.c ({r['build']}; cell kernel on 8 cells at once like deal.II's VectorizedArray) on {r['cores']} of {r['hw_threads']} hardware threads, {r['cpu']}; setup {r['setup_s']:.0f} s; "
               "a port, not the deal.II binary (which cannot be built here)")
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "requested_steps": args.steps, "requested_warmup": args.warmup,

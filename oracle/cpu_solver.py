@@ -54,6 +54,8 @@ def load():
     lib.mgcpu_solve.argtypes = [P, P, P, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_long)]
     lib.mgcpu_set_threads.argtypes = [C.c_int]
     lib.mgcpu_num_threads.restype = C.c_int
+    lib.mgcpu_set_batched.argtypes = [C.c_int]
+    lib.mgcpu_vector_lanes.restype = C.c_int
     lib.mgcpu_destroy.argtypes = [P]
     _LIB = lib
     return lib
@@ -127,6 +129,14 @@ class CpuMultigrid:
                 best, best_t = c, dt
         self.lib.mgcpu_set_threads(best)
         return best
+
+    def set_batched(self, on):
+        """cell kernel on mgcpu_vector_lanes() cells at once (default, what deal.II's VectorizedArray does) or cell by cell"""
+        self.lib.mgcpu_set_batched(1 if on else 0)
+
+    @property
+    def vector_lanes(self):
+        return int(self.lib.mgcpu_vector_lanes())
 
     @property
     def n_threads(self):

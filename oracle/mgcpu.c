@@ -13,6 +13,9 @@
  *   transfers        MGTwoLevelTransfer::prolongate_and_add / restrict_and_add, h-transfer
  *   V-cycle, CG      Multigrid::level_v_step, PreconditionMG, SolverCG + ReductionControl,
  *                    coarse solver = CG with reltol 1e-4 (multigrid_throughput.cc:888-921)
+ * SIMD: the cell kernel runs on 8 cells at once, one cell per lane of a 512-bit vector (GCC vector types; two 256-bit
+ * operations on AVX2 hosts) -- deal.II's VectorizedArray<double> over the cells of a MatrixFree batch; lane by lane it is the
+ * scalar kernel, bit for bit (tests/test_oracle.py), and mgcpu_set_batched(0) switches back to it.
  * Threads: OpenMP over cells of one colour (cells of equal coordinate parity share no DoF on a uniform level), the
  * analogue of deal.II's one MPI rank per core; reductions in a fixed static schedule.
  */
@@ -94,6 +97,8 @@ static void zero(double *y, long n)
 }
 
 /* ------------------------------------------------------------------------------------------------ cell kernel */
+static int g_batched = 1; /* mgcpu_set_batched: cell kernel on VL cells at once (default) or one cell at a time */
+
 /* one 1-D sweep along direction d of a n x n x n array: out[.., q, ..] = sum_i M[q*n+i] in[.., i, ..] (or M^T) */
 static inline __attribute__((always_inline)) void sweep(const double *M, const int transpose, const int n, const int d, const double *in,
                                                         double *out)
@@ -154,8 +159,116 @@ static void cell_apply(const Level *L, const double *u, double *r)
     }
 }
 
+/* ---- the same kernel on VL cells at once: lane l of every vector belongs to cell l of the batch (what deal.II's
+ * VectorizedArray<double> does over the cells of a MatrixFree batch).  GCC vector types: AVX-512 or 2 x AVX2 per operation,
+ * chosen by -march; the arithmetic per lane is the scalar kernel's, operation for operation. */
+#define VL 8
+typedef double vd __attribute__((vector_size(VL * sizeof(double)), aligned(64)));
+
+static inline __attribute__((always_inline)) void sweep_v(const double *M, const int transpose, const int n, const int d, const vd *in, vd *out)
+{
+  const int stride = d == 0 ? 1 : (d == 1 ? n : n * n);
+  for (int a = 0; a < n; ++a)
+    for (int b = 0; b < n; ++b)
+      {
+        const int base = d == 0 ? (a * n + b) * n : (d == 1 ? a * n * n + b : a * n + b);
+        for (int q = 0; q < n; ++q)
+          {
+            vd s = {0};
+            for (int i = 0; i < n; ++i)
+              s += (transpose ? M[i * n + q] : M[q * n + i]) * in[base + i * stride];
+            out[base + q * stride] = s;
+          }
+      }
+}
+
+static inline __attribute__((always_inline)) void cell_apply_v_n(const Level *L, const vd *u, vd *r, const int n)
+{
+  const int n3 = n * n * n;
+  vd        v[MAXN * MAXN * MAXN], t1[MAXN * MAXN * MAXN], g[MAXN * MAXN * MAXN], acc[MAXN * MAXN * MAXN];
+  sweep_v(L->B, 0, n, 0, u, t1);
+  sweep_v(L->B, 0, n, 1, t1, v);
+  sweep_v(L->B, 0, n, 2, v, t1);
+  for (int q = 0; q < n3; ++q)
+    acc[q] = (vd){0};
+  for (int d = 0; d < 3; ++d)
+    {
+      sweep_v(L->Dc, 0, n, d, t1, g);
+      for (int c = 0; c < n; ++c)
+        for (int b = 0; b < n; ++b)
+          for (int a = 0; a < n; ++a)
+            g[(c * n + b) * n + a] *= L->w[a] * L->w[b] * L->w[c];
+      sweep_v(L->Dc, 1, n, d, g, v);
+      for (int q = 0; q < n3; ++q)
+        acc[q] += v[q];
+    }
+  sweep_v(L->B, 1, n, 2, acc, v);
+  sweep_v(L->B, 1, n, 1, v, t1);
+  sweep_v(L->B, 1, n, 0, t1, r);
+}
+
+static void cell_apply_v(const Level *L, const vd *u, vd *r)
+{
+  switch (L->n)
+    {
+      case 2: cell_apply_v_n(L, u, r, 2); break;
+      case 3: cell_apply_v_n(L, u, r, 3); break;
+      case 4: cell_apply_v_n(L, u, r, 4); break;
+      case 5: cell_apply_v_n(L, u, r, 5); break;
+      case 6: cell_apply_v_n(L, u, r, 6); break;
+      case 7: cell_apply_v_n(L, u, r, 7); break;
+      default: cell_apply_v_n(L, u, r, L->n);
+    }
+}
+
+/* cells of ONE colour (no two of them share a DoF), VL at a time; the tail goes through the scalar kernel */
+static void cell_range_batched(const Level *L, const uint32_t *cells, long nc, double *dst, const double *src)
+{
+  const int  n3       = L->n3;
+  const long n_batch  = nc / VL;
+#pragma omp parallel for schedule(static)
+  for (long bt = 0; bt < n_batch; ++bt)
+    {
+      vd              u[MAXN * MAXN * MAXN], r[MAXN * MAXN * MAXN];
+      const uint32_t *id[VL];
+      double          h[VL];
+      for (int l = 0; l < VL; ++l)
+        {
+          const long c = cells ? (long)cells[bt * VL + l] : bt * VL + l;
+          id[l]        = L->idx + c * n3;
+          h[l]         = L->h[c];
+        }
+      for (int q = 0; q < n3; ++q)
+        for (int l = 0; l < VL; ++l)
+          u[q][l] = (id[l][q] & FLAG) ? 0.0 : src[id[l][q]];
+      cell_apply_v(L, u, r);
+      for (int l = 0; l < VL; ++l)
+        for (int q = 0; q < n3; ++q)
+          if (!(id[l][q] & FLAG))
+            dst[id[l][q]] += h[l] * r[q][l];
+    }
+}
+
 static void cell_range(const Level *L, const uint32_t *cells, long nc, double *dst, const double *src, int atomic)
 {
+  if (!atomic && g_batched && nc >= VL)
+    {
+      const long done = (nc / VL) * VL;
+      cell_range_batched(L, cells, done, dst, src);
+      if (done == nc)
+        return;
+      cells = cells ? cells + done : NULL;
+      if (!cells)
+        {
+          /* contiguous numbering: run the tail through the scalar loop below with explicit cell numbers */
+          uint32_t tail[VL];
+          for (long k = done; k < nc; ++k)
+            tail[k - done] = (uint32_t)k;
+          cell_range(L, tail, nc - done, dst, src, 0);
+          return;
+        }
+      nc -= done;
+    }
   const int n3 = L->n3;
 #pragma omp parallel for schedule(static)
   for (long k = 0; k < nc; ++k)
@@ -729,6 +842,8 @@ int mgcpu_solve(MG *mg, double *x, const double *b, double reltol, double *final
   return its;
 }
 
+void mgcpu_set_batched(int on) { g_batched = on; }
+int  mgcpu_vector_lanes(void) { return VL; }
 void mgcpu_set_threads(int n)
 {
 #ifdef _OPENMP

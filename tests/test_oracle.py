@@ -190,6 +190,28 @@ def test_c_restatement_matches_numpy_oracle(L, p):
     assert its == itr and rel_l2(xs, xr) < 1e-11 and abs(res - ctl.last_value) < 1e-10 * ctl.initial_value
 
 
+@pytest.mark.parametrize("L,p", [(3, 2), (2, 4), (1, 3)])
+def test_c_restatement_cell_batches_equal_cell_by_cell(L, p):
+    """the host baseline applies the cell kernel to mgcpu_vector_lanes() cells at once (deal.II's VectorizedArray over a
+    MatrixFree cell batch); lane by lane it is the scalar kernel, so vmult and the V-cycle agree BITWISE with the
+    cell-by-cell loop -- also where a colour's cell count is not a multiple of the lane count (L=1: one cell per colour)"""
+    from oracle.cpu_solver import CpuMultigrid
+    from util import OracleHierarchy, seeded
+    H = OracleHierarchy("hypercube", L, p, "HMG-global")
+    M = CpuMultigrid(H.dofmaps, H.tmaps)
+    assert M.vector_lanes == 8
+    top = len(H.maps) - 1
+    x = seeded(H.maps[-1].n_dofs)
+    r = x.copy()
+    r[H.maps[-1].constrained] = 0.0
+    out = []
+    for on in (False, True):
+        M.set_batched(on)
+        out.append((M.vmult(top, x), M.vcycle(r)))
+    M.set_batched(True)
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+
+
 # ------------------------------------------------------------------------------------ general geometry (MappingQ1) oracle
 @pytest.mark.parametrize("p", [1, 2, 3])
 def test_mapped_element_matrix_pins(p):
