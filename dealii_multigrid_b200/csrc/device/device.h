@@ -95,6 +95,10 @@ namespace mgb
     // are axis-aligned cubes of side root_length / 2^level
     const double   *vertices    = nullptr;
     double          scale       = 1.0; // general geometry: dst += scale * A src (the Cartesian kernel folds it into root_length)
+    // Cartesian kernel only: zero_n elements at zero_ptr (16-byte aligned, value type of the operator, not src or dst) are
+    // set to zero by the cell loop on the side -- the destination of the next cell loop (k_laplace_apply<P, T, true>)
+    void           *zero_ptr    = nullptr;
+    long long       zero_n      = 0;
   };
   // dst += A_cells src   (scatter-add with FP atomics); cell_list (optional) restricts to a subset of cells
   template <typename T>

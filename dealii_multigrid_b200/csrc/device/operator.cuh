@@ -210,10 +210,24 @@ namespace mgb
 #ifndef MGB_SLAB_ABLATE
 #define MGB_SLAB_ABLATE 0
 #endif
-  template <int P, typename T>
+  // experiments with the side zeroing of k_laplace_apply<P, T, true>: kind of store (0 plain, 1 st.cs, 2 st.wt) and its place
+  // in the batch (0 before the sweeps, 1 after the scatter)
+#ifndef MGB_ZERO_STORE
+#define MGB_ZERO_STORE 1
+#endif
+#ifndef MGB_ZERO_POS
+#define MGB_ZERO_POS 0
+#endif
+  // ZERO: the kernel also writes zeros to a vector that takes no part in this product (the destination of the NEXT cell loop:
+  // deal.II's cell_loop zeroes dst inside the loop as well, zero_dst_vector = true).  Batch b clears the b-th slice of
+  // zero_per_batch 16-byte words; the kernel is bound by the L1 data pipe, so the stores ride along where a separate memset
+  // costs a full pass at DRAM speed -- that was the idea; measured, a zeroing launch loses 0.19-0.29 ms against 0.17 ms for the
+  // memset (profiles/r2v_zero_in_cell_loop.txt), so ChebyshevT only uses it with MGB_ZERO_IN_CELL_LOOP=1.
+  template <int P, typename T, bool ZERO = false>
   __global__ void __launch_bounds__(SlabCfg<P>::W * 32, SlabCfg<P>::MIN_BLOCKS)
     k_laplace_apply(const uint32_t *__restrict__ ctab, const int any_hanging, const double root_length, const long long n_work,
-                    const uint32_t *__restrict__ cell_list, const T *__restrict__ src, T *__restrict__ dst)
+                    const uint32_t *__restrict__ cell_list, const T *__restrict__ src, T *__restrict__ dst, T *zero_ptr = nullptr,
+                    const long long zero_n = 0, const long long zero_per_batch = 0)
   {
     constexpr int n = P + 1, n2 = n * n;
     constexpr int CW = SlabCfg<P>::CW, W = SlabCfg<P>::W;
@@ -316,6 +330,24 @@ namespace mgb
 #endif
         const uint32_t *tb  = tbuf + (it % 3) * (CW * CTAB_STRIDE);
         const int       ncw = (int)min((long long)CW, n_work - b * CW);
+        const auto zero_slice = [&]() {
+          constexpr long long EPW = 16 / sizeof(T); // elements per 16-byte word
+          const long long     n16 = zero_n / EPW, z1 = min((b + 1) * zero_per_batch, n16);
+          for (long long z = b * zero_per_batch + lane; z < z1; z += 32)
+            {
+#if MGB_ZERO_STORE == 1
+              __stcs(reinterpret_cast<uint4 *>(zero_ptr) + z, make_uint4(0u, 0u, 0u, 0u)); // streaming: evict first
+#elif MGB_ZERO_STORE == 2
+              __stwt(reinterpret_cast<uint4 *>(zero_ptr) + z, make_uint4(0u, 0u, 0u, 0u)); // write through
+#else
+              reinterpret_cast<uint4 *>(zero_ptr)[z] = make_uint4(0u, 0u, 0u, 0u);
+#endif
+            }
+          if (b == 0 && lane < int(zero_n - n16 * EPW))
+            zero_ptr[n16 * EPW + lane] = T(0);
+        };
+        if (ZERO && MGB_ZERO_POS == 0)
+          zero_slice();
         bool            warp_hn = false;
         if (any_hanging)
           {
@@ -444,6 +476,8 @@ namespace mgb
                     atomic_add(dst + idx, h * res[k]);
                 }
             }
+        if (ZERO && MGB_ZERO_POS == 1)
+          zero_slice();
         __syncwarp(); // u is rewritten by the next iteration's columns
       }
   }
@@ -540,7 +574,23 @@ namespace mgb
       }
     const long long n_batches = (n_work + CW - 1) / CW;
     const long long blocks    = std::min<long long>((n_batches + W - 1) / W, (long long)blocks_per_sm * n_sm);
-    k_laplace_apply<P, T><<<(unsigned)blocks, W * 32, smem, s>>>(cd.ctab, cd.any_hanging, cd.root_length, n_work, cell_list, src, dst);
+    if (cd.zero_ptr && cd.zero_n > 0)
+      {
+        if (reinterpret_cast<uintptr_t>(cd.zero_ptr) & 15u)
+          throw std::runtime_error("k_laplace_apply: the vector to be zeroed is not 16-byte aligned");
+        static bool zero_attr = false; // the ZERO instantiation needs its own opt-in to the dynamic shared memory size
+        if (!zero_attr)
+          {
+            MGB_CUDA(cudaFuncSetAttribute(k_laplace_apply<P, T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            zero_attr = true;
+          }
+        const long long n16 = cd.zero_n / (long long)(16 / sizeof(T));
+        k_laplace_apply<P, T, true><<<(unsigned)blocks, W * 32, smem, s>>>(cd.ctab, cd.any_hanging, cd.root_length, n_work, cell_list, src, dst,
+                                                                          static_cast<T *>(cd.zero_ptr), cd.zero_n,
+                                                                          (n16 + n_batches - 1) / n_batches);
+      }
+    else
+      k_laplace_apply<P, T><<<(unsigned)blocks, W * 32, smem, s>>>(cd.ctab, cd.any_hanging, cd.root_length, n_work, cell_list, src, dst);
     MGB_CUDA(cudaGetLastError());
   }
 

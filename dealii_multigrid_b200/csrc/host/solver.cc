@@ -404,12 +404,16 @@ namespace mgb
       }
   }
 
-  template <typename T> void OperatorT<T>::cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_only, double alpha) const
+  template <typename T>
+  void OperatorT<T>::cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_only, double alpha, DVec<T> *also_zero,
+                               bool *did_zero) const
   {
     Context &c  = ctx();
     CellData cd = cd_;
     cd.root_length *= alpha; // the cell matrices are linear in h = root_length / 2^level
     cd.scale = alpha;
+    if (did_zero)
+      *did_zero = false;
     const bool overlap = !edge_only && !c.prof_enabled && boundary_cells_.n > 0 && interior_cells_.n > 0 && c.overlap_ready();
     if (overlap)
       {
@@ -461,16 +465,24 @@ namespace mgb
       }
     else
       {
+        CellData cz = cd; // the first (or only) launch also clears also_zero
+        if (also_zero && !cd.vertices && also_zero->data && also_zero->data != dst.data && also_zero->data != src.data)
+          {
+            cz.zero_ptr = also_zero->data;
+            cz.zero_n   = (long long)also_zero->n_owned + also_zero->n_ghost;
+            if (did_zero)
+              *did_zero = true;
+          }
         c.prof_begin(cd_.n_cells);
         if (plain_cells_.n > 0 && hanging_cells_.n > 0)
           {
-            CellData cp    = cd;
+            CellData cp    = cz;
             cp.any_hanging = 0;
             cell_laplace_apply<T>(cp, src.data, dst.data, plain_cells_.ptr, (long long)plain_cells_.n, c.stream), ++c.launches;
             cell_laplace_apply<T>(cd, src.data, dst.data, hanging_cells_.ptr, (long long)hanging_cells_.n, c.stream), ++c.launches;
           }
         else
-          cell_laplace_apply<T>(cd, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
+          cell_laplace_apply<T>(cz, src.data, dst.data, nullptr, 0, c.stream), ++c.launches;
         c.prof_end(cd_.n_cells);
       }
     dst.compress_add();
@@ -530,6 +542,29 @@ namespace mgb
         idx_scatter<T>(dst.data, edge_src_vals_.ptr, edge_.ptr, ne, c.stream);
         c.launches += 2;
       }
+  }
+
+  template <typename T> bool OperatorT<T>::vmult_zeroing(DVec<T> &dst, const DVec<T> &src, const bool dst_is_zero, DVec<T> *also_zero) const
+  {
+    Context       &c  = ctx();
+    const uint32_t ne = (uint32_t)edge_.n;
+    if (ne) // as vmult
+      {
+        idx_gather<T>(edge_src_vals_.ptr, src.data, edge_.ptr, ne, c.stream);
+        idx_set<T>(const_cast<T *>(src.data), T(0), edge_.ptr, ne, c.stream);
+        c.launches += 2;
+      }
+    bool did_zero = false;
+    cell_loop(dst, src, !dst_is_zero, false, 1.0, also_zero, &did_zero);
+    if (constrained_.n)
+      idx_copy<T>(dst.data, src.data, constrained_.ptr, (uint32_t)constrained_.n, c.stream), ++c.launches;
+    if (ne)
+      {
+        idx_scatter<T>(const_cast<T *>(src.data), edge_src_vals_.ptr, edge_.ptr, ne, c.stream);
+        idx_scatter<T>(dst.data, edge_src_vals_.ptr, edge_.ptr, ne, c.stream);
+        c.launches += 2;
+      }
+    return did_zero;
   }
 
   template <typename T> void OperatorT<T>::vmult_interface_down(DVec<T> &dst, const DVec<T> &src) const
@@ -596,6 +631,8 @@ namespace mgb
   {
     const char *e = std::getenv("MGB_FUSE_CHEB");
     fuse_         = !(e && e[0] == '0');
+    e             = std::getenv("MGB_ZERO_IN_CELL_LOOP"); // opt-in: measured slower than the memset (profiles/r2v_zero_in_cell_loop.txt)
+    zero_in_loop_ = e && e[0] == '1';
     op_.compute_inverse_diagonal(dinv_);
   }
 
@@ -606,6 +643,8 @@ namespace mgb
     Context &c = ctx();
     op_.initialize_dof_vector(solution_old_);
     op_.initialize_dof_vector(temp1_);
+    if (zero_in_loop_ && degree_ > 1)
+      op_.initialize_dof_vector(temp2_); // here and not in iterate(): no allocation while a stream is being captured
     op_.initialize_dof_vector(temp2_);
     // initial guess (i + first_local_range) % 11 minus its mean (PreconditionChebyshev::set_initial_guess)
     {
@@ -714,9 +753,27 @@ namespace mgb
           }
         return;
       }
+    // A x lands alternately in temp1_ / temp2_: the cell loop that fills one clears the other for the next product, so only
+    // the first product of a call needs a memset.  Nothing is remembered between calls (a caller may replay this sequence
+    // from a graph of its own, which the host code would not see).
+    DVec<T> *tt[2] = {&temp1_, &temp2_};
+    if (zero_in_loop_ && n_updates > 1)
+      {
+        if (temp2_.n_owned != dst.n_owned || temp2_.n_ghost != dst.n_ghost)
+          temp2_.reinit_like(dst);
+        temp2_.part = temp1_.part;
+      }
+    bool next_is_clean = false;
     for (int u = 0; u < n_updates; ++u)
       {
-        op_.vmult(temp1_, *x);
+        DVec<T> *t = &temp1_;
+        if (zero_in_loop_ && n_updates > 1)
+          {
+            t             = tt[u & 1];
+            next_is_clean = op_.vmult_zeroing(*t, *x, next_is_clean, u + 1 < n_updates ? tt[(u + 1) & 1] : nullptr);
+          }
+        else
+          op_.vmult(temp1_, *x);
         double f1, f2;
         if (!zero_guess && u == 0)
           {
@@ -732,7 +789,7 @@ namespace mgb
           }
         const bool last = u == n_updates - 1;
         DVec<T>   *out  = last ? &dst : xo;
-        cheb_update<T>(have_old ? 2 : 1, T(f1), T(f2), rhs.data, dinv_.data, temp1_.data, x->data, xo->data, out->data, n, c.stream);
+        cheb_update<T>(have_old ? 2 : 1, T(f1), T(f2), rhs.data, dinv_.data, t->data, x->data, xo->data, out->data, n, c.stream);
         ++c.launches;
         if (!last)
           {

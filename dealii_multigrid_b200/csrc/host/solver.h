@@ -396,6 +396,11 @@ namespace mgb
     void      initialize_dof_vector(DVec<T> &v) const { v.reinit(part_->host.n_owned, part_->host.n_ghost, part_); }
     void      vmult(DVec<T> &dst, const DVec<T> &src) const;                // include/operator.h:152-183
     void      Tvmult(DVec<T> &dst, const DVec<T> &src) const { vmult(dst, src); }
+    // vmult for callers that own a pair of temporaries (the Chebyshev loop): dst_is_zero = the caller knows that dst holds
+    // zeros (owned entries and ghost tail), so the memset is skipped; also_zero (may be null; neither dst nor src, same
+    // layout) is cleared by the cell loop itself where the Cartesian atomic kernel runs (k_laplace_apply<P, T, true>).
+    // Returns whether also_zero now holds zeros.
+    bool      vmult_zeroing(DVec<T> &dst, const DVec<T> &src, bool dst_is_zero, DVec<T> *also_zero) const;
     void      vmult_interface_down(DVec<T> &dst, const DVec<T> &src) const; // :191-201
     // dst = b - A src with A = vmult_interface_down: Multigrid::level_v_step's residual (matrix->vmult followed by
     // t.sadd(-1, 1, defect)) in one cell loop
@@ -419,7 +424,9 @@ namespace mgb
     const uint32_t *constrained_dev() const { return constrained_.ptr; }
 
   private:
-    void cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_cells_only, double alpha = 1.0) const;
+    // also_zero: a vector (not dst, not src) that the cell loop may clear on the side; *did_zero tells whether it did
+    void cell_loop(DVec<T> &dst, const DVec<T> &src, bool zero_dst, bool edge_cells_only, double alpha = 1.0, DVec<T> *also_zero = nullptr,
+                   bool *did_zero = nullptr) const;
     CellData                           cd_;
     DeviceBuffer<uint32_t>             etab_, ctab_;
     DeviceBuffer<uint16_t>             mask_;
@@ -469,6 +476,9 @@ namespace mgb
     bool                fuse_     = true; // vector updates inside the cell loop (MGB_FUSE_CHEB=0: separate pass)
     double              lambda_max_ = 0, lambda_min_est_ = 0, theta_ = 1, delta_ = 1;
     DVec<T>             dinv_, solution_old_, temp1_, temp2_;
+    // the unfused loop alternates its A x between temp1_ and temp2_; the cell loop that fills one clears the other
+    // (opt-in MGB_ZERO_IN_CELL_LOOP=1; the default is a memset before every cell loop, which is faster)
+    bool                zero_in_loop_ = false;
     CGWork<T>           cgw_;
   };
 

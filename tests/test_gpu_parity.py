@@ -111,6 +111,35 @@ def test_chebyshev(gpu, geometry, L, p, degree):
     assert rel_l2(x.to_numpy(), oracle.step(x0.copy(), b)) < 1e-11
 
 
+@pytest.mark.parametrize("geometry,L,p,degree,number", [("hypercube", 3, 4, 3, "double"), ("quadrant", 4, 3, 4, "double"),
+                                                       ("quadrant", 3, 4, 3, "float"), ("hypercube", 3, 1, 5, "double")])
+def test_chebyshev_zeroing_inside_the_cell_loop(gpu, monkeypatch, geometry, L, p, degree, number):
+    """the smoother keeps A x alternately in two temporaries and lets the cell loop that fills one clear the other
+    (k_laplace_apply<P,T,true>; split plain / hanging launches on the quadrant); MGB_ZERO_IN_CELL_LOOP=0 is the memset before
+    every cell loop.  Both against the oracle, several calls in a row (the temporaries carry old products), odd vector
+    lengths included (the 16-byte zeroing has a scalar tail)"""
+    mg = gpu
+    d = mg.DoFMap(mg.Mesh(geometry, L), p)
+    maps = ref.LevelMaps.from_dofmap(d)
+    oracle = ref.PreconditionChebyshev(ref.Operator(maps), degree, 20.0, 20)
+    oracle.estimate_eigenvalues()
+    ntype, dt, tol = (mg.DOUBLE, np.float64, 1e-11) if number == "double" else (mg.FLOAT, np.float32, 1e-4)
+    b, x0 = seeded(maps.n_dofs), seeded(maps.n_dofs, 5)
+    want_vmult, want_step = oracle.vmult(b), oracle.step(x0.copy(), b)
+    for env in ("1", "0"):
+        monkeypatch.setenv("MGB_ZERO_IN_CELL_LOOP", env)
+        op = mg.Operator(d, ntype)
+        cheb = mg.PreconditionChebyshev(op, degree, 20.0, 20)
+        rhs, x = op.initialize_dof_vector(), op.initialize_dof_vector()
+        rhs.from_numpy(b.astype(dt))
+        for _ in range(3):
+            cheb.vmult(x, rhs)
+            assert rel_l2(x.to_numpy().astype(np.float64), want_vmult) < tol
+            x.from_numpy(x0.astype(dt))
+            cheb.step(x, rhs)
+            assert rel_l2(x.to_numpy().astype(np.float64), want_step) < tol
+
+
 TRANSFER_CASES = [("hypercube", 2, 1, "h"), ("hypercube", 3, 4, "h"), ("quadrant", 4, 2, "h"), ("annulus", 5, 3, "h"), ("circle", 4, 4, "h"),
                   ("quadrant", 3, 4, "p"), ("annulus", 5, 2, "p"), ("hypercube", 2, 3, "p"), ("quadrant", 3, 6, "p")]
 
