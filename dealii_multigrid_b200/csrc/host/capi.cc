@@ -108,6 +108,55 @@ namespace
   }
 } // namespace
 
+namespace mgb
+{
+  // The index arrays of the array-based entry points come from another program (the deal.II adapter); every one of them ends
+  // up as an address inside a kernel, so they are checked here, on the host, before anything is uploaded.
+  void check_index_list(const char *what, const uint32_t *idx, uint64_t n, uint64_t bound)
+  {
+    if (n && !idx)
+      throw std::runtime_error(std::string(what) + ": null pointer for a non-empty index list");
+    for (uint64_t i = 0; i < n; ++i)
+      if (idx[i] >= bound)
+        throw std::runtime_error(std::string(what) + ": entry " + std::to_string(i) + " = " + std::to_string(idx[i]) +
+                                 " is outside [0, " + std::to_string(bound) + ")");
+  }
+  // 27 entity bases per cell: an unflagged entity of s DoFs occupies [base, base + s) of the local vector
+  void check_entity_table(const char *what, const uint32_t *table, int64_t n_cells, int degree, uint64_t n_local)
+  {
+    uint32_t esize[27];
+    for (int e = 0; e < 27; ++e)
+      {
+        esize[e] = 1;
+        for (int k = 0; k < entity_dim(e); ++k)
+          esize[e] *= uint32_t(degree - 1);
+      }
+    for (int64_t c = 0; c < n_cells; ++c)
+      for (int e = 0; e < 27; ++e)
+        {
+          const uint32_t t = table[size_t(c) * 27 + e];
+          if (esize[e] == 0 || (t & FLAG_BIT))
+            continue;
+          if (uint64_t(t) + esize[e] > n_local)
+            throw std::runtime_error(std::string(what) + ": cell " + std::to_string(c) + ", entity " + std::to_string(e) + ": DoFs [" +
+                                     std::to_string(t) + ", " + std::to_string(uint64_t(t) + esize[e]) + ") exceed the local vector of " +
+                                     std::to_string(n_local) + " entries (owned + ghost)");
+        }
+  }
+  void check_offsets(const char *what, const uint32_t *off, uint32_t n_ranks, uint64_t total)
+  {
+    if (n_ranks == 0)
+      return;
+    if (!off)
+      throw std::runtime_error(std::string(what) + ": offsets required");
+    if (off[0] != 0 || off[n_ranks] != total)
+      throw std::runtime_error(std::string(what) + ": offsets must run from 0 to " + std::to_string(total));
+    for (uint32_t r = 0; r < n_ranks; ++r)
+      if (off[r] > off[r + 1])
+        throw std::runtime_error(std::string(what) + ": offsets must ascend");
+  }
+} // namespace mgb
+
 extern "C" {
 
 const char *mgb_last_error(void) { return capi_last_error().c_str(); }
@@ -729,10 +778,33 @@ namespace
 int mgb_operator_create(const mgb_operator_desc *d, mgb_operator **out)
 {
   return guarded([&] {
+    if (!d || !out)
+      throw std::runtime_error("mgb_operator_create: null argument");
     if ((d->entity_table == nullptr) == (d->dof_indices == nullptr))
       throw std::runtime_error("exactly one of entity_table / dof_indices must be given");
     if (d->degree < 1 || d->degree > MAX_DEGREE)
       throw std::runtime_error("degree out of range");
+    if (d->n_cells < 0 || (d->n_cells > 0 && !d->cell_level))
+      throw std::runtime_error("mgb_operator_create: n_cells >= 0 and cell_level are required");
+    const uint64_t n_local = uint64_t(d->n_owned) + d->n_ghost;
+    if (n_local >= uint64_t(INDEX_MASK))
+      throw std::runtime_error("mgb_operator_create: more than 2^31 local DoFs");
+    check_index_list("mgb_operator_create: constrained", d->constrained, d->n_constrained, d->n_owned);
+    check_index_list("mgb_operator_create: edge_constrained", d->edge_constrained, d->n_edge_constrained, d->n_owned);
+    check_index_list("mgb_operator_create: edge_cells", d->edge_cells, d->n_edge_cells, uint64_t(d->n_cells));
+    check_offsets("mgb_operator_create: ghost_offsets", d->ghost_offsets, d->n_ghost_ranks, d->n_ghost);
+    if (d->n_ghost && (!d->ghost_global || d->n_ghost_ranks == 0 || !d->ghost_ranks))
+      throw std::runtime_error("mgb_operator_create: ghost entries need ghost_global, ghost_ranks and ghost_offsets");
+    if (d->n_import_ranks)
+      {
+        if (!d->import_offsets || !d->import_ranks)
+          throw std::runtime_error("mgb_operator_create: import_ranks and import_offsets required");
+        check_offsets("mgb_operator_create: import_offsets", d->import_offsets, d->n_import_ranks, d->import_offsets[d->n_import_ranks]);
+        check_index_list("mgb_operator_create: import_indices", d->import_indices, d->import_offsets[d->n_import_ranks], d->n_owned);
+      }
+    for (int64_t c = 0; c < d->n_cells; ++c)
+      if (d->cell_level[c] > 30)
+        throw std::runtime_error("mgb_operator_create: cell_level above 30");
     std::vector<uint32_t> compressed;
     OperatorSetup         s;
     s.degree  = d->degree;
@@ -744,6 +816,7 @@ int mgb_operator_create(const mgb_operator_desc *d, mgb_operator **out)
         compressed     = compress_dof_indices(d->dof_indices, d->n_cells, d->degree);
         s.entity_table = compressed.data();
       }
+    check_entity_table("mgb_operator_create", s.entity_table, d->n_cells, d->degree, n_local);
     s.mask                        = d->mask;
     s.cell_level                  = d->cell_level;
     s.root_length                 = d->root_length;
@@ -1001,8 +1074,26 @@ int mgb_transfer_create_from_arrays(const mgb_transfer_map_view *v, const mgb_op
     tm.weight_code.assign(v->weight_code, v->weight_code + size_t(v->n_fine_slots) * 27);
     tm.fine_own.assign(v->fine_own, v->fine_own + size_t(v->n_fine_slots) * 27);
     for (int64_t c = 0; c < v->n_coarse_cells; ++c)
-      if (int64_t(tm.fine_first[c]) + tm.n_children[c] > v->n_fine_slots)
-        throw std::runtime_error("mgb_transfer_create_from_arrays: fine_first + n_children exceeds n_fine_slots");
+      {
+        if (int64_t(tm.fine_first[c]) + tm.n_children[c] > v->n_fine_slots)
+          throw std::runtime_error("mgb_transfer_create_from_arrays: fine_first + n_children exceeds n_fine_slots");
+        if (tm.n_children[c] != 0 && tm.n_children[c] != 1 && tm.n_children[c] != 8)
+          throw std::runtime_error("mgb_transfer_create_from_arrays: n_children must be 0, 1 or 8");
+      }
+    if (v->degree_fine < 1 || v->degree_fine > MAX_DEGREE || v->degree_coarse < 1 || v->degree_coarse > v->degree_fine)
+      throw std::runtime_error("mgb_transfer_create_from_arrays: degrees out of range");
+    {
+      // fine_own addresses the fine operator's vector, or (distributed) the transfer's own ghosted fine vector
+      const Partitioner &fp      = (opf->type == MGB_DOUBLE ? opf->pd->partitioner() : opf->pf->partitioner())->host;
+      const uint64_t     n_local = v->distributed ? uint64_t(v->n_owned) + v->n_ghost : uint64_t(fp.n_owned) + fp.n_ghost;
+      check_entity_table("mgb_transfer_create_from_arrays: fine_own", v->fine_own, v->n_fine_slots, v->degree_fine, n_local);
+      if (v->distributed)
+        {
+          check_offsets("mgb_transfer_create_from_arrays: ghost_offsets", v->ghost_offsets, v->n_ghost_ranks, v->n_ghost);
+          check_offsets("mgb_transfer_create_from_arrays: import_offsets", v->import_offsets, v->n_import_ranks, v->n_import_indices);
+          check_index_list("mgb_transfer_create_from_arrays: import_indices", v->import_indices, v->n_import_indices, v->n_owned);
+        }
+    }
     tm.distributed = v->distributed != 0;
     if (tm.distributed)
       {

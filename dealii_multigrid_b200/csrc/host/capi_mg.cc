@@ -127,9 +127,14 @@ namespace
   };
 } // namespace
 
+namespace mgb
+{
+  void check_index_list(const char *what, const uint32_t *idx, uint64_t n, uint64_t bound); // capi.cc
+}
 struct mgb_level_copy
 {
   int                                 type = MGB_DOUBLE;
+  uint64_t                            active_size_needed = 0, level_size_needed = 0; // 1 + largest index of either side
   std::unique_ptr<LevelCopyT<double>> d;
   std::unique_ptr<LevelCopyT<float>>  f;
 };
@@ -204,11 +209,18 @@ int mgb_level_copy_create_from_arrays(uint32_t n, const uint32_t *active_idx, co
   return guarded([&] {
     if (n && (!active_idx || !level_idx))
       throw std::runtime_error("mgb_level_copy_create_from_arrays: index arrays required");
+    const Partitioner &lp = (level_op->type == MGB_DOUBLE ? level_op->pd->partitioner() : level_op->pf->partitioner())->host;
+    check_index_list("mgb_level_copy_create_from_arrays: level_idx", level_idx, n, uint64_t(lp.n_owned) + lp.n_ghost);
     CopyIndices ci;
     ci.active_idx.assign(active_idx, active_idx + n);
     ci.level_idx.assign(level_idx, level_idx + n);
     auto h  = std::make_unique<mgb_level_copy>();
     h->type = level_op->type;
+    for (uint32_t i = 0; i < n; ++i)
+      {
+        h->active_size_needed = std::max<uint64_t>(h->active_size_needed, uint64_t(active_idx[i]) + 1);
+        h->level_size_needed  = std::max<uint64_t>(h->level_size_needed, uint64_t(level_idx[i]) + 1);
+      }
     if (level_op->type == MGB_DOUBLE)
       h->d = std::make_unique<LevelCopyT<double>>(ci, *level_op->pd);
     else
@@ -222,6 +234,10 @@ int  mgb_level_copy_to_mg(const mgb_level_copy *c, mgb_vector *dst_level, const 
   return guarded([&] {
     require_same_type(c->type, dst_level->type);
     require_same_type(MGB_DOUBLE, src_active->type);
+    if (c->active_size_needed > uint64_t(src_active->pd->n_owned) + src_active->pd->n_ghost)
+      throw std::runtime_error("mgb_level_copy_to_mg: the copy indices address entry " + std::to_string(c->active_size_needed - 1) +
+                               " of an active-mesh vector with " + std::to_string(uint64_t(src_active->pd->n_owned) + src_active->pd->n_ghost) +
+                               " local entries");
     if (c->type == MGB_DOUBLE)
       c->d->to_mg(*dst_level->pd, *src_active->pd);
     else
@@ -233,6 +249,10 @@ int mgb_level_copy_from_mg(const mgb_level_copy *c, mgb_vector *dst_active, cons
   return guarded([&] {
     require_same_type(c->type, src_level->type);
     require_same_type(MGB_DOUBLE, dst_active->type);
+    if (c->active_size_needed > uint64_t(dst_active->pd->n_owned) + dst_active->pd->n_ghost)
+      throw std::runtime_error("mgb_level_copy_from_mg: the copy indices address entry " + std::to_string(c->active_size_needed - 1) +
+                               " of an active-mesh vector with " + std::to_string(uint64_t(dst_active->pd->n_owned) + dst_active->pd->n_ghost) +
+                               " local entries");
     if (c->type == MGB_DOUBLE)
       c->d->from_mg(*dst_active->pd, *src_level->pd);
     else

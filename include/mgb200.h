@@ -261,6 +261,11 @@ typedef struct
   const uint32_t *import_indices;
 } mgb_operator_desc;
 
+/* Every index of the descriptor is checked on the host before anything is uploaded (entity bases + entity sizes against
+ * n_owned + n_ghost, the index lists against n_owned / n_cells, the offset arrays for 0 ... total, ascending): a map that
+ * would address memory outside the vectors fails here with a message naming the entry, not inside a kernel.  The same holds
+ * for mgb_transfer_create_from_arrays (fine_own) and mgb_level_copy_create_from_arrays (level_idx at creation, active_idx
+ * against the active-mesh vector of every copy_to_mg / copy_from_mg call). */
 int  mgb_operator_create(const mgb_operator_desc *desc, mgb_operator **out);
 int  mgb_operator_create_from_dofmap(const mgb_dofmap *d, int number_type, mgb_operator **out);
 /* level operator of the local-smoothing hierarchy: Operator::reinit(..., mg_level) with its refinement-edge data */

@@ -138,3 +138,38 @@ def test_transfer_and_level_copy_created_from_plain_arrays(gpu):
     back = _vec(active_op)
     c.copy_from_mg(back, vl)
     np.testing.assert_array_equal(back.to_numpy()[H.copy[l].active_idx], x[H.copy[l].active_idx])
+
+
+def test_array_based_creation_rejects_indices_outside_the_vectors(gpu):
+    """fine_own, level_idx and active_idx become addresses in k_transfer / k_idx_pair_copy: checked on the host against the vectors
+    they address (csrc/host/capi.cc check_entity_table / check_index_list)"""
+    import ctypes as C
+    mg = gpu
+    H = OracleHierarchyLS("quadrant", 4, 2, "HMG-local", 3, "cg")
+    l = len(H.level_meshes) - 1
+    opf, opc = mg.Operator(H.level_dofmaps[l], edges=H.level_edges[l]), mg.Operator(H.level_dofmaps[l - 1], edges=H.level_edges[l - 1])
+    tm = H.ls_tmaps[l]
+    view = type(tm.view)()
+    C.pointer(view)[0] = tm.view
+    bad = tm.fine_own().copy()
+    flat = bad.reshape(-1)
+    flat[np.flatnonzero((flat & 0x80000000) == 0)[-1]] = H.level_maps[l].n_dofs - 1   # a vertex would fit; edges and faces do not
+    flat[np.flatnonzero((flat & 0x80000000) == 0)[0]] = H.level_maps[l].n_dofs
+    view.fine_own = bad.ctypes.data_as(C.POINTER(C.c_uint32))
+
+    class BadMap:
+        pass
+    BadMap.view = view
+    with pytest.raises(mg.MgbError, match="fine_own: cell"):
+        mg.MGTwoLevelTransfer(None, None, BadMap, opf, opc)
+    idx = H.copy[l].level_idx.copy()
+    idx[0] = H.level_maps[l].n_dofs
+    with pytest.raises(mg.MgbError, match="level_idx: entry 0"):
+        mg.LevelCopy(None, opf, active_idx=H.copy[l].active_idx, level_idx=idx)
+    c = mg.LevelCopy(None, opf, active_idx=H.copy[l].active_idx, level_idx=H.copy[l].level_idx)
+    short = mg.Vector(int(H.copy[l].active_idx.max()))                                # one entry too short
+    vl = _vec(opf)
+    with pytest.raises(mg.MgbError, match="copy indices address entry"):
+        c.copy_to_mg(vl, short)
+    with pytest.raises(mg.MgbError, match="copy indices address entry"):
+        c.copy_from_mg(short, vl)
