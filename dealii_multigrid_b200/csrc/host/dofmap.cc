@@ -3,6 +3,9 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <functional>
+#include <string>
+#include <thread>
 #include "partition.h"
 
 #include <algorithm>
@@ -158,6 +161,42 @@ namespace mgb
     return out;
   }
 
+  // worker threads of the host setup: MGB_SETUP_THREADS, else the hardware threads divided among the ranks of this node
+  // (torchrun starts one process per GPU and every one of them builds its maps at the same time), at most 16; small jobs
+  // stay on the calling thread
+  int setup_threads(int64_t n_items)
+  {
+    if (n_items < 4096)
+      return 1;
+    static const int n = [] {
+      if (const char *e = std::getenv("MGB_SETUP_THREADS"))
+        return std::max(1, std::atoi(e));
+      int         world = 1;
+      const char *w     = std::getenv("LOCAL_WORLD_SIZE");
+      if (!w)
+        w = std::getenv("WORLD_SIZE");
+      if (w)
+        world = std::max(1, std::atoi(w));
+      const int hw = std::max(1u, std::thread::hardware_concurrency());
+      return std::max(1, std::min(16, hw / world));
+    }();
+    return n;
+  }
+  void run_threads(int n, const std::function<void(int)> &fn)
+  {
+    if (n <= 1)
+      {
+        fn(0);
+        return;
+      }
+    std::vector<std::thread> pool;
+    for (int t = 1; t < n; ++t)
+      pool.emplace_back(fn, t);
+    fn(0);
+    for (std::thread &th : pool)
+      th.join();
+  }
+
   DoFMap DoFMap::build(const Mesh &mesh, int degree, int n_ranks, int rank, int64_t min_cells_per_rank)
   {
     const int64_t nc = (int64_t)mesh.cells.size();
@@ -192,8 +231,22 @@ namespace mgb
     const auto T0 = std::chrono::steady_clock::now();
     // pass 1: global numbering, Morton first touch; the bases of the local cells' own entities are kept (g_own) so that
     // pass 2 does not look them up again
+    static const int PREFETCH_AHEAD = [] {
+      const char *e = std::getenv("MGB_SETUP_PREFETCH");
+      return e ? std::max(1, std::atoi(e)) : 1;
+    }();
     FlatMap ent;
     ent.reserve(size_t(nc) * (degree > 1 ? 9 : 2) + 64);
+    // direct-mapped cache of the entities seen last (256 KB, stays in L2) in front of the big table: a hit costs a few
+    // cycles where the table costs a memory access
+    struct Recent
+    {
+      uint64_t key;
+      int64_t  base;
+    };
+    constexpr int       RECENT_BITS = 14;
+    long long           n_recent_hits = 0;
+    std::vector<Recent> recent(size_t(1) << RECENT_BITS, Recent{~uint64_t(0), -1});
     std::vector<int64_t> dof_begin(n_ranks + 1, 0);
     std::vector<int64_t> g_eval(size_t(dm.n_cells) * 27), g_own(size_t(dm.n_cells) * 27, -1);
     int64_t              next = 0;
@@ -206,25 +259,33 @@ namespace mgb
             dof_begin[r++] = next;
           const Cell &c     = mesh.cells[i];
           int64_t    *local = (i >= l_begin && i < l_end) ? &g_own[size_t(i - l_begin) * 27] : nullptr;
-          if (i + 1 < nc) // the next cell's slots arrive while this cell is numbered
+          if (i + PREFETCH_AHEAD < nc) // slots of a cell further on arrive while this one is numbered
             {
-              const Cell &cn = mesh.cells[i + 1];
+              const Cell &cn = mesh.cells[i + PREFETCH_AHEAD];
               for (int e = 0; e < 27; ++e)
                 if (esize[e] != 0)
-                  ent.prefetch(K(cn.level, cn.x, cn.y, cn.z, e));
+                  {
+                    const uint64_t key = K(cn.level, cn.x, cn.y, cn.z, e);
+                    if (recent[(key * 0x9e3779b97f4a7c15ULL) >> (64 - RECENT_BITS)].key != key)
+                      ent.prefetch(key);
+                  }
             }
           for (int k = 0; k < 27; ++k)
             {
               const int e = ENTITY_ORDER[k];
               if (esize[e] == 0)
                 continue;
-              const uint64_t key  = K(c.level, c.x, c.y, c.z, e);
-              int64_t        base = ent.find(key);
-              if (base < 0)
+              const uint64_t key = K(c.level, c.x, c.y, c.z, e);
+              Recent        &rc  = recent[(key * 0x9e3779b97f4a7c15ULL) >> (64 - RECENT_BITS)];
+              int64_t        base;
+              if (rc.key == key)
+                ++n_recent_hits, base = rc.base; // numbered by one of the last few cells: most entities of a cell in Morton order
+              else
                 {
-                  base = next;
-                  ent.insert(key, next);
-                  next += esize[e];
+                  base = ent.find_or_insert(key, next);
+                  if (base == next)
+                    next += esize[e]; // first touch: the entity's DoFs are numbered now
+                  rc = Recent{key, base};
                 }
               if (local)
                 local[e] = base;
@@ -284,70 +345,110 @@ namespace mgb
           return false;
       return true;
     };
-    int q = 0;
-    for (int64_t i = pass_begin; i < pass_end; ++i)
-      {
-        while (cell_begin[q + 1] <= i)
-          ++q;
-        const Cell &c = mesh.cells[i];
-        if (q != rank && (dm.n_cells == 0 || !may_touch_local(c)))
-          continue;
-        uint64_t    own[27], eval[27];
-        uint16_t    mask;
-        analyse_cell(mesh, K, c, own, eval, mask);
-        if (q == rank)
-          {
-            const int64_t l = i - cell_begin[rank];
-            dm.mask[l]      = mask;
-            if (mask >> 3)
-              ++dm.n_cells_hanging;
-            dm.cell_level[l]       = c.level;
-            dm.cell_xyz[3 * l + 0] = c.x;
-            dm.cell_xyz[3 * l + 1] = c.y;
-            dm.cell_xyz[3 * l + 2] = c.z;
-            for (int e = 0; e < 27; ++e)
-              {
-                if (esize[e] == 0)
-                  {
-                    g_eval[l * 27 + e] = g_own[l * 27 + e] = my_begin;
-                    f_eval[l * 27 + e] = f_own[l * 27 + e] = 0;
+    // The cells are independent in this pass (the entity map is only read): contiguous slices of the cell range go to
+    // worker threads; everything that is appended is sorted afterwards, so the maps do not depend on the thread count.
+    const int n_threads = setup_threads(pass_end - pass_begin);
+    struct Partial
+    {
+      std::vector<Ent>              ghosts, constrained_ents;
+      std::vector<std::vector<Ent>> imports;
+      int64_t                       n_hanging = 0;
+      std::string                   error;
+    };
+    std::vector<Partial> partial(n_threads);
+    const auto           pass2 = [&](const int t) {
+      Partial &P = partial[t];
+      P.imports.resize(n_ranks);
+      const int64_t span = pass_end - pass_begin, i0 = pass_begin + span * t / n_threads, i1 = pass_begin + span * (t + 1) / n_threads;
+      int           q = int(std::upper_bound(cell_begin.begin(), cell_begin.end(), i0) - cell_begin.begin()) - 1;
+      q               = std::min(std::max(q, 0), n_ranks - 1);
+      for (int64_t i = i0; i < i1; ++i)
+        {
+          while (cell_begin[q + 1] <= i)
+            ++q;
+          const Cell &c = mesh.cells[i];
+          if (q != rank && (dm.n_cells == 0 || !may_touch_local(c)))
+            continue;
+          uint64_t own[27], eval[27];
+          uint16_t mask;
+          analyse_cell(mesh, K, c, own, eval, mask);
+          if (q == rank)
+            {
+              const int64_t l = i - cell_begin[rank];
+              dm.mask[l]      = mask;
+              if (mask >> 3)
+                ++P.n_hanging;
+              dm.cell_level[l]       = c.level;
+              dm.cell_xyz[3 * l + 0] = c.x;
+              dm.cell_xyz[3 * l + 1] = c.y;
+              dm.cell_xyz[3 * l + 2] = c.z;
+              for (int e = 0; e < 27; ++e)
+                {
+                  if (esize[e] == 0)
+                    {
+                      g_eval[l * 27 + e] = g_own[l * 27 + e] = my_begin;
+                      f_eval[l * 27 + e] = f_own[l * 27 + e] = 0;
+                      continue;
+                    }
+                  const int64_t bo = g_own[l * 27 + e]; // from pass 1
+                  const int64_t be = (eval[e] == own[e]) ? bo : ent.find(eval[e]);
+                  if (bo < 0 || be < 0)
+                    {
+                      P.error = "DoFMap: entity lookup failed (mesh not 2:1 balanced?)";
+                      return;
+                    }
+                  const bool dir_o = K.on_boundary(own[e]), dir_e = K.on_boundary(eval[e]);
+                  const bool hang  = eval[e] != own[e];
+                  g_own[l * 27 + e]  = bo;
+                  g_eval[l * 27 + e] = be;
+                  f_own[l * 27 + e]  = (dir_o || hang) ? 1 : 0;
+                  f_eval[l * 27 + e] = dir_e ? 1 : 0;
+                  if (bo < my_begin || bo >= my_end)
+                    P.ghosts.push_back(Ent{bo, esize[e]});
+                  else if (dir_o || hang)
+                    P.constrained_ents.push_back(Ent{bo, esize[e]});
+                  if (hang && (be < my_begin || be >= my_end))
+                    P.ghosts.push_back(Ent{be, esize[e]});
+                }
+            }
+          else
+            {
+              for (int e = 0; e < 27; ++e)
+                {
+                  if (esize[e] == 0)
                     continue;
-                  }
-                const int64_t bo = g_own[l * 27 + e]; // from pass 1
-                const int64_t be = (eval[e] == own[e]) ? bo : ent.find(eval[e]);
-                if (bo < 0 || be < 0)
-                  throw std::runtime_error("DoFMap: entity lookup failed (mesh not 2:1 balanced?)");
-                const bool dir_o = K.on_boundary(own[e]), dir_e = K.on_boundary(eval[e]);
-                const bool hang  = eval[e] != own[e];
-                g_own[l * 27 + e]  = bo;
-                g_eval[l * 27 + e] = be;
-                f_own[l * 27 + e]  = (dir_o || hang) ? 1 : 0;
-                f_eval[l * 27 + e] = dir_e ? 1 : 0;
-                if (bo < my_begin || bo >= my_end)
-                  ghosts.push_back(Ent{bo, esize[e]});
-                else if (dir_o || hang)
-                  constrained_ents.push_back(Ent{bo, esize[e]});
-                if (hang && (be < my_begin || be >= my_end))
-                  ghosts.push_back(Ent{be, esize[e]});
-              }
-          }
-        else
-          {
-            for (int e = 0; e < 27; ++e)
-              {
-                if (esize[e] == 0)
-                  continue;
-                const int64_t bo = ent.find(own[e]);
-                if (bo >= my_begin && bo < my_end)
-                  imports[q].push_back(Ent{bo, esize[e]});
-                if (eval[e] != own[e])
-                  {
-                    const int64_t be = ent.find(eval[e]);
-                    if (be >= my_begin && be < my_end)
-                      imports[q].push_back(Ent{be, esize[e]});
-                  }
-              }
-          }
+                  const int64_t bo = ent.find(own[e]);
+                  if (bo >= my_begin && bo < my_end)
+                    P.imports[q].push_back(Ent{bo, esize[e]});
+                  if (eval[e] != own[e])
+                    {
+                      const int64_t be = ent.find(eval[e]);
+                      if (be >= my_begin && be < my_end)
+                        P.imports[q].push_back(Ent{be, esize[e]});
+                    }
+                }
+            }
+        }
+    };
+    run_threads(n_threads, [&](const int t) {
+      try
+        {
+          pass2(t);
+        }
+      catch (const std::exception &e) // an exception must not leave a worker thread
+        {
+          partial[t].error = e.what();
+        }
+    });
+    for (Partial &P : partial)
+      {
+        if (!P.error.empty())
+          throw std::runtime_error(P.error);
+        dm.n_cells_hanging += P.n_hanging;
+        ghosts.insert(ghosts.end(), P.ghosts.begin(), P.ghosts.end());
+        constrained_ents.insert(constrained_ents.end(), P.constrained_ents.begin(), P.constrained_ents.end());
+        for (int r = 0; r < n_ranks; ++r)
+          imports[r].insert(imports[r].end(), P.imports[r].begin(), P.imports[r].end());
       }
     // a constrained entity owned by us may only be touched by cells of other ranks' ... no: the first
     // touching cell is ours by construction of ownership, so the loop above has seen it.
@@ -404,17 +505,23 @@ namespace mgb
     };
     dm.eval_table.resize(g_eval.size());
     dm.own_table.resize(g_own.size());
-    for (size_t k = 0; k < g_eval.size(); ++k)
-      {
-        dm.eval_table[k] = to_local(g_eval[k]) | (f_eval[k] ? FLAG_BIT : 0u);
-        dm.own_table[k]  = to_local(g_own[k]) | (f_own[k] ? FLAG_BIT : 0u);
-      }
+    {
+      const int nt = setup_threads(dm.n_cells);
+      run_threads(nt, [&](const int t) {
+        for (size_t k = g_eval.size() * t / nt; k < g_eval.size() * (t + 1) / nt; ++k)
+          {
+            dm.eval_table[k] = to_local(g_eval[k]) | (f_eval[k] ? FLAG_BIT : 0u);
+            dm.own_table[k]  = to_local(g_own[k]) | (f_own[k] ? FLAG_BIT : 0u);
+          }
+      });
+    }
     for (const Ent &en : constrained_ents)
       for (int k = 0; k < en.size; ++k)
         dm.constrained.push_back(uint32_t(en.base - my_begin + k));
     const auto T3 = std::chrono::steady_clock::now();
     if (std::getenv("MGB_SETUP_TIMING"))
-      std::fprintf(stderr, "DoFMap::build %lld cells: pass1 %.3f s, pass2 %.3f s, tables %.3f s\n", (long long)nc,
+      std::fprintf(stderr, "DoFMap::build %lld cells: %lld entities, %lld lookups answered by the recent-entity cache; pass1 %.3f s, pass2 %.3f s, tables %.3f s\n",
+                   (long long)nc, (long long)ent.size(), n_recent_hits,
                    std::chrono::duration<double>(T1 - T0).count(), std::chrono::duration<double>(T2 - T1).count(),
                    std::chrono::duration<double>(T3 - T2).count());
     if (n_ranks > 1)
@@ -492,29 +599,36 @@ namespace mgb
     int esize[27];
     for (int e = 0; e < 27; ++e)
       esize[e] = ipow(df.degree - 1, entity_dim(e));
-    std::vector<uint8_t>  valence(size_t(df.part.n_owned) + df.part.n_ghost + 1, 0);
-    std::vector<uint32_t> patch;
-    for (int64_t c = 0; c < dc.n_cells; ++c)
-      {
-        patch.clear();
-        for (unsigned ch = 0; ch < tm.n_children[c]; ++ch)
-          for (int e = 0; e < 27; ++e)
-            if (esize[e] > 0)
-              patch.push_back(df.own_table[(size_t(tm.fine_first[c]) + ch) * 27 + e] & INDEX_MASK);
-        std::sort(patch.begin(), patch.end());
-        patch.erase(std::unique(patch.begin(), patch.end()), patch.end());
-        for (uint32_t b : patch)
-          ++valence[b];
-      }
-    tm.weight_code.assign(size_t(df.n_cells) * 27, 0);
-    for (size_t k = 0; k < tm.weight_code.size(); ++k)
-      {
-        const uint32_t t = df.own_table[k];
-        if (esize[k % 27] == 0 || (t & FLAG_BIT))
-          tm.weight_code[k] = 0;
-        else
-          tm.weight_code[k] = valence[t & INDEX_MASK];
-      }
+    std::vector<uint8_t> valence(size_t(df.part.n_owned) + df.part.n_ghost + 1, 0);
+    {
+      // coarse cells are independent; a fine entity on the boundary of two patches is counted by both, possibly from two
+      // threads: relaxed atomic increments (a sum does not depend on the order)
+      const int nt = setup_threads(dc.n_cells);
+      run_threads(nt, [&](const int t) {
+        std::vector<uint32_t> patch;
+        for (int64_t c = dc.n_cells * t / nt; c < dc.n_cells * (t + 1) / nt; ++c)
+          {
+            patch.clear();
+            for (unsigned ch = 0; ch < tm.n_children[c]; ++ch)
+              for (int e = 0; e < 27; ++e)
+                if (esize[e] > 0)
+                  patch.push_back(df.own_table[(size_t(tm.fine_first[c]) + ch) * 27 + e] & INDEX_MASK);
+            std::sort(patch.begin(), patch.end());
+            patch.erase(std::unique(patch.begin(), patch.end()), patch.end());
+            for (uint32_t b : patch)
+              __atomic_fetch_add(&valence[b], uint8_t(1), __ATOMIC_RELAXED);
+          }
+      });
+      tm.weight_code.assign(size_t(df.n_cells) * 27, 0);
+      run_threads(nt, [&](const int t) {
+        const size_t n = tm.weight_code.size();
+        for (size_t k = n * t / nt; k < n * (t + 1) / nt; ++k)
+          {
+            const uint32_t tab = df.own_table[k];
+            tm.weight_code[k]  = (esize[k % 27] == 0 || (tab & FLAG_BIT)) ? 0 : valence[tab & INDEX_MASK];
+          }
+      });
+    }
     tm.fine_own     = df.own_table;
     tm.n_fine_slots = df.n_cells;
     tm.distributed  = false;

@@ -2,11 +2,35 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
+#include <new>
 #include <stdexcept>
+
+#include <sys/mman.h>
 
 namespace mgb
 {
   // ------------------------------------------------------------------ FlatMap
+  void *huge_alloc(size_t bytes)
+  {
+    void *p = nullptr;
+    if (bytes >= (size_t(4) << 20))
+      {
+        const size_t two_mb = size_t(2) << 20, rounded = (bytes + two_mb - 1) / two_mb * two_mb;
+        if (posix_memalign(&p, two_mb, rounded) != 0)
+          throw std::bad_alloc();
+        madvise(p, rounded, MADV_HUGEPAGE); // advice only: without huge pages the table is merely slower
+      }
+    else
+      {
+        p = std::malloc(bytes ? bytes : 1);
+        if (!p)
+          throw std::bad_alloc();
+      }
+    return p;
+  }
+  void huge_free(void *p) { std::free(p); }
+
   uint64_t FlatMap::hash(uint64_t k)
   {
     k ^= k >> 33;
@@ -31,7 +55,7 @@ namespace mgb
       cap <<= 1;
     if (cap <= slots_.size())
       return;
-    std::vector<Slot> old;
+    std::vector<Slot, HugeAllocator<Slot>> old;
     old.swap(slots_);
     slots_.assign(cap, Slot{~uint64_t(0), -1});
     mask_ = cap - 1;
@@ -53,6 +77,22 @@ namespace mgb
     if (slots_[i].key != key)
       ++n_;
     slots_[i] = Slot{key, value};
+  }
+
+  int64_t FlatMap::find_or_insert(uint64_t key, int64_t value)
+  {
+    if (slots_.empty() || 3 * (n_ + 1) > 2 * slots_.size())
+      grow();
+    size_t i = hash(key) & mask_;
+    while (slots_[i].key != ~uint64_t(0))
+      {
+        if (slots_[i].key == key)
+          return slots_[i].val;
+        i = (i + 1) & mask_;
+      }
+    slots_[i] = Slot{key, value};
+    ++n_;
+    return value;
   }
 
   int64_t FlatMap::find(uint64_t key) const

@@ -8,12 +8,29 @@
 // Leaves are stored in Morton (z-) order, child c at offsets
 // (c&1, (c>>1)&1, (c>>2)&1) -- the deal.II / p4est child order.
 #pragma once
+#include <cstddef>
 #include <cstdint>
 #include <string>
 #include <vector>
 
 namespace mgb
 {
+  // Allocator of the big random-access tables of the host setup: blocks of 4 MB and more are 2 MB-aligned and advised to
+  // transparent huge pages (MADV_HUGEPAGE; most hosts only give huge pages on request).  A 64 MB hash table on 4 KB pages
+  // pays a TLB miss and a page walk per lookup, which software prefetch does not hide.
+  void *huge_alloc(size_t bytes);
+  void  huge_free(void *p);
+  template <typename T> struct HugeAllocator
+  {
+    using value_type = T;
+    HugeAllocator() = default;
+    template <typename U> HugeAllocator(const HugeAllocator<U> &) {}
+    T   *allocate(size_t n) { return static_cast<T *>(huge_alloc(n * sizeof(T))); }
+    void deallocate(T *p, size_t) { huge_free(p); }
+    template <typename U> bool operator==(const HugeAllocator<U> &) const { return true; }
+    template <typename U> bool operator!=(const HugeAllocator<U> &) const { return false; }
+  };
+
   // open-addressing hash map uint64 -> int64 (keys never removed)
   class FlatMap
   {
@@ -21,6 +38,8 @@ namespace mgb
     void    reserve(size_t n);
     void    insert(uint64_t key, int64_t value);
     int64_t find(uint64_t key) const; // -1 if absent
+    // the value stored for key; if there is none, value is stored and returned (one probe sequence instead of find + insert)
+    int64_t find_or_insert(uint64_t key, int64_t value);
     size_t  size() const { return n_; }
     void    clear();
     // hint that `key` is looked up or inserted soon: the big tables of the setup are random-access bound, and the 27
@@ -39,8 +58,8 @@ namespace mgb
     };
     static uint64_t   hash(uint64_t k);
     void              grow();
-    std::vector<Slot> slots_;
-    size_t            n_    = 0;
+    std::vector<Slot, HugeAllocator<Slot>> slots_;
+    size_t                                 n_    = 0;
     size_t            mask_ = 0;
   };
 

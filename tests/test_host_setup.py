@@ -560,3 +560,43 @@ def test_hierarchy_statistics_local_smoothing(n_ranks):
     for k in ("workload_eff", "workload_path_max", "vertical_eff", "horizontal_eff"):
         assert st[k] == pytest.approx(ref_[k], rel=1e-14), k
     assert st["workload_eff"] < 1.0   # local smoothing: the refined region's owners carry the fine levels alone
+
+
+def test_dofmap_does_not_depend_on_the_number_of_setup_threads():
+    """DoFMap::build analyses the cells on worker threads (MGB_SETUP_THREADS; csrc/host/dofmap.cc) and sorts what they append,
+    TransferMap::build counts the valences with atomic increments: the maps are bitwise the same for 1, 3 and 7 threads, on meshes above the threading threshold, with hanging nodes and
+    on several ranks (thread count is fixed per process, hence subprocesses)"""
+    import hashlib
+    import os
+    import subprocess
+    import sys
+    script = r'''
+import hashlib, sys
+import numpy as np
+import dealii_multigrid_b200 as mg
+h = hashlib.sha256()
+for geometry, L, p, n_ranks, rank in (("annulus", 6, 2, 1, 0), ("quadrant", 5, 3, 3, 1), ("hypercube", 4, 4, 2, 1), ("quadrant", 5, 1, 4, 0)):
+    d = mg.DoFMap(mg.Mesh(geometry, L), p, n_ranks, rank)
+    assert d.n_cells * n_ranks >= 4096 or geometry == "hypercube"
+    part = d.partitioner()
+    for a in (d.eval_table(), d.own_table(), d.mask(), d.cell_level(), d.cell_xyz(), d.constrained(), d.ghost_global()):
+        h.update(np.ascontiguousarray(a).tobytes())
+    for k in sorted(part):
+        h.update(np.ascontiguousarray(part[k]).tobytes())
+mf = mg.Mesh("hypercube", 5)
+mc = mf.coarsen_global()
+df, dc = mg.DoFMap(mf, 2), mg.DoFMap(mc, 2)
+assert dc.n_cells >= 4096
+tm = mg.TransferMap(mf, df, mc, dc)
+for a in (tm.fine_first(), tm.n_children(), tm.weight_code(), tm.fine_own()):
+    h.update(np.ascontiguousarray(a).tobytes())
+print(h.hexdigest())
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = set()
+    for threads in ("1", "3", "7"):
+        env = dict(os.environ, MGB_SETUP_THREADS=threads, PYTHONPATH=root)
+        out = subprocess.run([sys.executable, "-c", script], env=env, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        digests.add(out.stdout.strip().splitlines()[-1])
+    assert len(digests) == 1
