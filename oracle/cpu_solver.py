@@ -56,6 +56,9 @@ def load():
     lib.mgcpu_num_threads.restype = C.c_int
     lib.mgcpu_set_batched.argtypes = [C.c_int]
     lib.mgcpu_vector_lanes.restype = C.c_int
+    lib.mgcpu_set_even_odd.argtypes = [C.c_int]
+    lib.mgcpu_even_odd_available.restype = C.c_int
+    lib.mgcpu_even_odd_available.argtypes = [P, C.c_int]
     lib.mgcpu_destroy.argtypes = [P]
     _LIB = lib
     return lib
@@ -133,6 +136,13 @@ class CpuMultigrid:
     def set_batched(self, on):
         """cell kernel on mgcpu_vector_lanes() cells at once (default, what deal.II's VectorizedArray does) or cell by cell"""
         self.lib.mgcpu_set_batched(1 if on else 0)
+
+    def set_even_odd(self, on):
+        """1-D sweeps in even-odd form (default; deal.II's evaluate_evenodd) or as full (p+1) x (p+1) products"""
+        self.lib.mgcpu_set_even_odd(1 if on else 0)
+
+    def even_odd_available(self, level):
+        return bool(self.lib.mgcpu_even_odd_available(self.h, level))
 
     @property
     def vector_lanes(self):

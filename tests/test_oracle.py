@@ -210,6 +210,13 @@ def test_c_restatement_cell_batches_equal_cell_by_cell(L, p):
         out.append((M.vmult(top, x), M.vcycle(r)))
     M.set_batched(True)
     assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    # the even-odd form of the 1-D sweeps (deal.II's evaluate_evenodd; default) against the full (p+1) x (p+1) products:
+    # the same numbers up to rounding, and bitwise the same between the batched and the cell-by-cell kernel
+    assert M.even_odd_available(top)
+    M.set_even_odd(False)
+    full = M.vmult(top, x)
+    M.set_even_odd(True)
+    assert np.linalg.norm(full - out[1][0]) < 1e-14 * np.linalg.norm(full)
 
 
 # ------------------------------------------------------------------------------------ general geometry (MappingQ1) oracle
