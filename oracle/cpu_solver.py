@@ -57,6 +57,9 @@ def load():
     lib.mgcpu_set_batched.argtypes = [C.c_int]
     lib.mgcpu_vector_lanes.restype = C.c_int
     lib.mgcpu_set_even_odd.argtypes = [C.c_int]
+    lib.mgcpu_set_blocks.argtypes = [C.c_int]
+    lib.mgcpu_set_vmult_blocks.restype = C.c_int
+    lib.mgcpu_set_vmult_blocks.argtypes = [P, C.c_int, C.c_long, C.c_int, P, P]
     lib.mgcpu_even_odd_available.restype = C.c_int
     lib.mgcpu_even_odd_available.argtypes = [P, C.c_int]
     lib.mgcpu_destroy.argtypes = [P]
@@ -99,6 +102,19 @@ class CpuMultigrid:
             self._keep += [idx, hcell, con, order, begin, B, Dc, w]
             lib.mgcpu_set_level(self.h, l, d.degree, m.n_cells, m.n_dofs, _p(idx), _p(hcell), len(con), _p(con), _p(B), _p(Dc), _p(w),
                                 ncol, _p(begin), _p(order))
+            if uniform:
+                # operator loop: colour Morton-aligned cubes of 8^k cells by the parity of their block coordinates; the largest
+                # k <= 3 that leaves 64 blocks per colour (the cells are in Morton order, so a stable sort keeps blocks whole)
+                k = 3
+                while k > 0 and m.n_cells // 8 ** k < 8 * 64:
+                    k -= 1
+                bcol = ((xyz[:, 0] >> k) & 1) | (((xyz[:, 1] >> k) & 1) << 1) | (((xyz[:, 2] >> k) & 1) << 2)
+                border = np.ascontiguousarray(np.argsort(bcol, kind="stable").astype(np.uint32))
+                bbegin = np.ascontiguousarray(np.searchsorted(bcol[border], np.arange(9)).astype(np.int64))
+                if k >= 1 and m.n_cells >= 8 ** (k + 1):   # k = 0 is the cell colouring above
+                    self._keep += [border, bbegin]
+                    if lib.mgcpu_set_vmult_blocks(self.h, l, 8 ** k, 8, _p(bbegin), _p(border)) != 0:
+                        raise RuntimeError("mgcpu_set_vmult_blocks: colour lists are not whole blocks")
         for l in range(1, len(dofmaps)):
             fine, coarse, tm = self.maps[l], self.maps[l - 1], tmaps[l]
             first = np.ascontiguousarray(tm.fine_first(), dtype=np.uint32)
@@ -136,6 +152,10 @@ class CpuMultigrid:
     def set_batched(self, on):
         """cell kernel on mgcpu_vector_lanes() cells at once (default, what deal.II's VectorizedArray does) or cell by cell"""
         self.lib.mgcpu_set_batched(1 if on else 0)
+
+    def set_blocks(self, on):
+        """operator loop over coloured Morton-aligned blocks of cells (default; one pass over the vectors) or coloured cells"""
+        self.lib.mgcpu_set_blocks(1 if on else 0)
 
     def set_even_odd(self, on):
         """1-D sweeps in even-odd form (default; deal.II's evaluate_evenodd) or as full (p+1) x (p+1) products"""

@@ -15,9 +15,12 @@
  *                    coarse solver = CG with reltol 1e-4 (multigrid_throughput.cc:888-921)
  * SIMD: the cell kernel runs on 8 cells at once, one cell per lane of a 512-bit vector (GCC vector types; two 256-bit
  * operations on AVX2 hosts) -- deal.II's VectorizedArray<double> over the cells of a MatrixFree batch; lane by lane it is the
- * scalar kernel, bit for bit (tests/test_oracle.py), and mgcpu_set_batched(0) switches back to it.
- * Threads: OpenMP over cells of one colour (cells of equal coordinate parity share no DoF on a uniform level), the
- * analogue of deal.II's one MPI rank per core; reductions in a fixed static schedule.
+ * scalar kernel, bit for bit (tests/test_oracle.py), and mgcpu_set_batched(0) switches back to it.  The 1-D sweeps run in
+ * even-odd form (struct EO; deal.II: EvaluatorVariant::evaluate_evenodd), mgcpu_set_even_odd(0) gives the full products.
+ * Threads: the operator loop runs over coloured BLOCKS of cells (Morton-aligned cubes of 8^k cells, coloured by the parity of
+ * the block coordinates: blocks of one colour share no DoF; a thread walks through whole blocks in order) -- one cache-friendly
+ * pass over the vectors per product, the analogue of deal.II's one MPI rank per core working on its contiguous share of the
+ * cells; small levels and the transfers use the 8 colours of the cells themselves.  Reductions in a fixed static schedule.
  */
 #include <math.h>
 #include <stdint.h>
@@ -51,6 +54,10 @@ typedef struct
   int       n_colors;
   long     *color_begin;
   uint32_t *order;
+  /* operator loop: colouring of Morton-aligned blocks of vb_block cells (mgcpu_set_vmult_blocks); a thread takes whole blocks */
+  int       vb_colors;
+  long     *vb_begin, vb_block;
+  uint32_t *vb_order;
   double    B[MAXN * MAXN], Dc[MAXN * MAXN], w[MAXN];
   struct EO eo[4]; /* even-odd forms of B, B^T, Dc, Dc^T */
   int       eo_ok; /* the 1-D matrices have the point symmetry the decomposition needs */
@@ -110,6 +117,7 @@ static void zero(double *y, long n)
 }
 
 /* ------------------------------------------------------------------------------------------------ cell kernel */
+static int g_blocks  = 1; /* mgcpu_set_blocks: operator loop over coloured blocks of cells (default) or coloured cells */
 static int g_batched = 1; /* mgcpu_set_batched: cell kernel on VL cells at once (default) or one cell at a time */
 
 /* one 1-D sweep along direction d of a n x n x n array: out[.., q, ..] = sum_i M[q*n+i] in[.., i, ..] (or M^T) */
@@ -338,32 +346,40 @@ static void cell_apply_v(const Level *L, const vd *u, vd *r)
     }
 }
 
+/* VL cells at once: gather, apply, scatter lane by lane (the lanes may share DoFs: the scatter is sequential) */
+#pragma GCC diagnostic push
+#pragma GCC diagnostic ignored "-Wmaybe-uninitialized" /* only the first n^3 entries of u are used, and they are set */
+static inline void cell_batch(const Level *L, const uint32_t *cells, const long first, double *dst, const double *src)
+{
+  const int       n3 = L->n3;
+  vd              u[MAXN * MAXN * MAXN], r[MAXN * MAXN * MAXN];
+  const uint32_t *id[VL];
+  double          h[VL];
+  for (int l = 0; l < VL; ++l)
+    {
+      const long c = cells ? (long)cells[first + l] : first + l;
+      id[l]        = L->idx + c * n3;
+      h[l]         = L->h[c];
+    }
+  for (int q = 0; q < n3; ++q)
+    for (int l = 0; l < VL; ++l)
+      u[q][l] = (id[l][q] & FLAG) ? 0.0 : src[id[l][q]];
+  cell_apply_v(L, u, r);
+  for (int l = 0; l < VL; ++l)
+    for (int q = 0; q < n3; ++q)
+      if (!(id[l][q] & FLAG))
+        dst[id[l][q]] += h[l] * r[q][l];
+}
+
+#pragma GCC diagnostic pop
+
 /* cells of ONE colour (no two of them share a DoF), VL at a time; the tail goes through the scalar kernel */
 static void cell_range_batched(const Level *L, const uint32_t *cells, long nc, double *dst, const double *src)
 {
-  const int  n3       = L->n3;
-  const long n_batch  = nc / VL;
+  const long n_batch = nc / VL;
 #pragma omp parallel for schedule(static)
   for (long bt = 0; bt < n_batch; ++bt)
-    {
-      vd              u[MAXN * MAXN * MAXN], r[MAXN * MAXN * MAXN];
-      const uint32_t *id[VL];
-      double          h[VL];
-      for (int l = 0; l < VL; ++l)
-        {
-          const long c = cells ? (long)cells[bt * VL + l] : bt * VL + l;
-          id[l]        = L->idx + c * n3;
-          h[l]         = L->h[c];
-        }
-      for (int q = 0; q < n3; ++q)
-        for (int l = 0; l < VL; ++l)
-          u[q][l] = (id[l][q] & FLAG) ? 0.0 : src[id[l][q]];
-      cell_apply_v(L, u, r);
-      for (int l = 0; l < VL; ++l)
-        for (int q = 0; q < n3; ++q)
-          if (!(id[l][q] & FLAG))
-            dst[id[l][q]] += h[l] * r[q][l];
-    }
+    cell_batch(L, cells, bt * VL, dst, src);
 }
 
 static void cell_range(const Level *L, const uint32_t *cells, long nc, double *dst, const double *src, int atomic)
@@ -411,11 +427,46 @@ static void cell_range(const Level *L, const uint32_t *cells, long nc, double *d
     }
 }
 
+/* Blocks of ONE colour: `block` consecutive entries of `cells` are a Morton-aligned cube of cells; two blocks of a colour
+ * share no DoF, the cells inside a block do, so a block is the unit of work of a thread and is walked through in order.  This
+ * is the cache-friendly schedule (one pass over the vectors per product instead of one per cell colour), what an MPI rank of
+ * the reference does on its contiguous share of the cells. */
+static void cell_range_blocks(const Level *L, const uint32_t *cells, long nc, long block, double *dst, const double *src)
+{
+  const long n_blocks = nc / block;
+#pragma omp parallel for schedule(static)
+  for (long blk = 0; blk < n_blocks; ++blk)
+    {
+      if (g_batched && block % VL == 0)
+        for (long c = blk * block; c < (blk + 1) * block; c += VL)
+          cell_batch(L, cells, c, dst, src);
+      else
+        {
+          const int n3 = L->n3;
+          double    u[MAXN * MAXN * MAXN], r[MAXN * MAXN * MAXN];
+          for (long k = blk * block; k < (blk + 1) * block; ++k)
+            {
+              const long      c  = (long)cells[k];
+              const uint32_t *id = L->idx + c * n3;
+              for (int q = 0; q < n3; ++q)
+                u[q] = (id[q] & FLAG) ? 0.0 : src[id[q]];
+              cell_apply(L, u, r);
+              for (int q = 0; q < n3; ++q)
+                if (!(id[q] & FLAG))
+                  dst[id[q]] += L->h[c] * r[q];
+            }
+        }
+    }
+}
+
 /* Operator::vmult (no refinement edges on global-coarsening levels) */
 static void vmult(const Level *L, double *dst, const double *src)
 {
   zero(dst, L->n_dofs);
-  if (L->n_colors > 0)
+  if (g_blocks && L->vb_colors > 0)
+    for (int col = 0; col < L->vb_colors; ++col)
+      cell_range_blocks(L, L->vb_order + L->vb_begin[col], L->vb_begin[col + 1] - L->vb_begin[col], L->vb_block, dst, src);
+  else if (L->n_colors > 0)
     for (int col = 0; col < L->n_colors; ++col)
       cell_range(L, L->order + L->color_begin[col], L->color_begin[col + 1] - L->color_begin[col], dst, src, 0);
   else
@@ -962,6 +1013,21 @@ int mgcpu_solve(MG *mg, double *x, const double *b, double reltol, double *final
 }
 
 void mgcpu_set_batched(int on) { g_batched = on; }
+void mgcpu_set_blocks(int on) { g_blocks = on; }
+/* order: the cells grouped by block colour, every block (block_cells consecutive entries) a Morton-aligned cube of cells */
+int mgcpu_set_vmult_blocks(void *h, int level, long block_cells, int n_colors, const long *begin, const uint32_t *order)
+{
+  Level *L = &((MG *)h)->L[level];
+  for (int c = 0; c < n_colors; ++c)
+    if ((begin[c + 1] - begin[c]) % block_cells != 0)
+      return 1;
+  free(L->vb_begin), free(L->vb_order);
+  L->vb_colors = n_colors;
+  L->vb_block  = block_cells;
+  L->vb_begin  = dup_mem(begin, sizeof(long) * (n_colors + 1));
+  L->vb_order  = dup_mem(order, sizeof(uint32_t) * L->n_cells);
+  return 0;
+}
 void mgcpu_set_even_odd(int on) { g_even_odd = on; }
 int  mgcpu_even_odd_available(void *h, int level) { return ((MG *)h)->L[level].eo_ok; }
 int  mgcpu_vector_lanes(void) { return VL; }
@@ -988,7 +1054,7 @@ void mgcpu_destroy(MG *mg)
   for (int l = 0; l < mg->nl; ++l)
     {
       Level *L = &mg->L[l];
-      free(L->idx), free(L->h), free(L->con), free(L->color_begin), free(L->order), free(L->dinv), free(L->fine_first), free(L->nch);
+      free(L->idx), free(L->h), free(L->con), free(L->color_begin), free(L->order), free(L->vb_begin), free(L->vb_order), free(L->dinv), free(L->fine_first), free(L->nch);
       free(L->wfine), free(L->own), free(L->defect), free(L->sol), free(L->t), free(L->tmp), free(L->xold);
     }
   free(mg->L);
