@@ -14,6 +14,7 @@ _LIB = None
 
 
 _NATIVE = None
+_NATIVE_TAG = ""
 
 
 def build_native():
@@ -22,19 +23,40 @@ def build_native():
     global _NATIVE
     if _LIB is not None:
         return _NATIVE or "-march=x86-64-v3 build"
+    global _NATIVE_TAG
+    _NATIVE_TAG = _cpu_tag()
     try:
-        subprocess.check_call(["make", "-C", _HERE, "native"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        subprocess.check_call(["make", "-C", _HERE, "native", "NATIVE_TAG=" + _NATIVE_TAG], stdout=subprocess.DEVNULL,
+                              stderr=subprocess.DEVNULL)
         _NATIVE = "-O3 -march=native build of this machine"
     except (OSError, subprocess.CalledProcessError):
         _NATIVE = None
     return _NATIVE or "-march=x86-64-v3 build"
 
 
+def _cpu_tag():
+    """names the -march=native library after this CPU's model and feature flags: the directory travels between machines"""
+    import hashlib
+    model = flags = ""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name") and not model:
+                    model = line
+                elif line.startswith("flags") and not flags:
+                    flags = line
+                if model and flags:
+                    break
+    except OSError:
+        pass
+    return "_" + hashlib.sha1((model + flags).encode()).hexdigest()[:10]
+
+
 def load():
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = os.path.join(_HERE, "_build", "libmgcpu_native.so" if _NATIVE else "libmgcpu.so")
+    path = os.path.join(_HERE, "_build", f"libmgcpu_native{_NATIVE_TAG}.so" if _NATIVE else "libmgcpu.so")
     if not os.path.exists(path):
         subprocess.check_call(["make", "-C", _HERE])
         path = os.path.join(_HERE, "_build", "libmgcpu.so")
